@@ -1,0 +1,132 @@
+/* jbonsai_b200 — C ABI of the B200-native hot path of jbonsai (MLPG solve + mel-cepstral vocoder).
+ *
+ * This is the drop-in boundary: every entry point replaces one item of the reference's public
+ * Rust API (jbonsai v0.4.2; the reference has no FFI of its own). A Rust `Engine`
+ * would bind these 1:1. Plain pointers and sizes only; all functions return
+ * 0 on success or a negative jb_status; jb_last_error() gives the message for the calling thread.
+ * There is NO CPU fallback: synthesis entry points return JB_ERR_CUDA when no GPU is usable.
+ */
+#ifndef JBONSAI_B200_H_
+#define JBONSAI_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum jb_status {
+  JB_OK = 0,
+  JB_ERR_EMPTY_VOICE = -1,   /* ModelError::EmptyVoice        src/model/mod.rs:31-46 */
+  JB_ERR_METADATA = -2,      /* ModelError::MetadataError */
+  JB_ERR_IO = -3,            /* ModelError::Io */
+  JB_ERR_PARSE = -4,         /* ModelError::ParserError */
+  JB_ERR_OPTION = -5,        /* EngineError::ParseOptionError src/engine.rs:16-28 */
+  JB_ERR_LABEL_PARSE = -6,   /* LabelError::JLabelParse       src/label.rs:7-19 */
+  JB_ERR_LABEL_MISSING = -7, /* LabelError::MissingLabel */
+  JB_ERR_LABEL_FLOAT = -8,   /* LabelError::FloatParse */
+  JB_ERR_LABEL_LENGTH = -9,  /* LabelError::LengthMismatch */
+  JB_ERR_WEIGHT = -10,       /* WeightError                   src/model/interporation_weight.rs:5-11 */
+  JB_ERR_INDEX = -11,        /* tree/pdf index not found (reference: todo!() panic, voice/model.rs:78) */
+  JB_ERR_ARGUMENT = -12,     /* bad argument (reference: panic!, e.g. src/speech.rs:32-40,70) */
+  JB_ERR_CUDA = -13,         /* CUDA failure or no device */
+  JB_ERR_UNSUPPORTED = -14   /* outside the built scope (stage != 0, beta > 0, no LPF stream) */
+} jb_status;
+
+typedef struct jb_engine jb_engine;
+typedef struct jb_stream jb_stream;
+
+const char* jb_last_error(void);
+const char* jb_version(void);
+int jb_device_count(void); /* number of usable CUDA devices, 0 if none */
+
+/* Engine::load (src/engine.rs:257) / Engine::load_from_bytes (src/engine.rs:263). */
+int jb_engine_load(const char* const* paths, size_t n_paths, jb_engine** out);
+int jb_engine_load_from_bytes(const uint8_t* const* bufs, const size_t* lens, size_t n,
+                              jb_engine** out);
+void jb_engine_free(jb_engine* e);
+
+/* `engine.condition` (src/engine.rs:32-243). key is one of: "speed", "volume" (dB), "alpha",
+ * "beta", "additional_half_tone", "msd_threshold" (idx = stream), "gv_weight" (idx = stream),
+ * "phoneme_alignment", "sampling_frequency", "fperiod", "stage", "use_log_gain".
+ * Setters clamp exactly like the reference's. */
+int jb_engine_set_condition(jb_engine* e, const char* key, size_t idx, double value);
+int jb_engine_get_condition(const jb_engine* e, const char* key, size_t idx, double* value);
+/* InterporationWeight::{set_duration,set_parameter,set_gv} (interporation_weight.rs:79-113);
+ * kind: 0 duration, 1 parameter (stream), 2 gv (stream). */
+int jb_engine_set_interpolation_weight(jb_engine* e, int kind, size_t stream, const double* w,
+                                       size_t n);
+
+/* CUDA devices used by this engine (default: device 0). A batch is sharded over them by
+ * contiguous utterance ranges balanced by frame count (no collective). */
+int jb_engine_set_devices(jb_engine* e, const int* devices, size_t n);
+/* MLSA kernel variant (-1 = default). For A/B measurements only. */
+int jb_engine_set_mlsa_variant(jb_engine* e, int variant);
+
+/* Engine::synthesize (src/engine.rs:294-296): labels -> raw f64 samples (not clipped).
+ * *out is owned by the library: release with jb_free(). Empty input -> *out_len = 0. */
+int jb_engine_synthesize(const jb_engine* e, const char* const* lines, size_t n_lines, double** out,
+                         size_t* out_len);
+
+/* Batch of utterances (no reference equivalent; BASELINE configs 3-5). Utterance u owns
+ * lines[line_off[u] .. line_off[u+1]). out_off must hold n_utt+1 entries: utterance u's samples
+ * are (*out)[out_off[u] .. out_off[u+1]), in input order. timings (optional, 16 doubles):
+ * [0] host front-end ms [1] pack ms [2] H2D ms [3] kernels ms [4] D2H ms [5] MLPG ms
+ * [6] excitation ms [7] MLSA ms [8] H2D bytes [9] D2H bytes [10] frames [11] samples
+ * [12] voiced samples [13] kernel launches. */
+int jb_engine_synthesize_batch(const jb_engine* e, const char* const* lines, const size_t* line_off,
+                               size_t n_utt, double** out, size_t* out_off, double* timings);
+void jb_free(void* p);
+
+/* Parity taps (tests): MlpgAdjust::create output of every utterance (src/mlpg_adjust/mod.rs:51)
+ * mcp [frames][35], lf0 [frames][1], lpf [frames][31]; the pulse train [samples] and, in *exc,
+ * excitation x gain before the MLSA filter. frame_off: n_utt+1 entries. Buffers: jb_free(). */
+int jb_engine_debug_batch(const jb_engine* e, const char* const* lines, const size_t* line_off,
+                          size_t n_utt, double** mcp, double** lf0, double** lpf, double** pulse,
+                          double** exc, int64_t* frame_off);
+/* First n samples of the global Gaussian excitation sequence (src/vocoder/excitation.rs:197-237). */
+int jb_engine_noise(const jb_engine* e, size_t n, double* out);
+
+/* Host front-end taps (tests of the model lookup / duration goldens). */
+int jb_engine_durations(const jb_engine* e, const char* const* lines, size_t n_lines,
+                        int32_t* durations, size_t cap, size_t* n_states);
+int jb_engine_tree_index(const jb_engine* e, size_t voice, int model /*0 dur,1 stream,2 gv*/,
+                         size_t stream, size_t state_index, const char* label, long* tree_index,
+                         long* pdf_index);
+/* Interpolated state-level parameters: mean/vari [n_states][nwin*dim], msd [n_states]. */
+int jb_engine_stream_parameters(const jb_engine* e, const char* const* lines, size_t n_lines,
+                                size_t stream, double* mean, double* vari, double* msd, size_t cap,
+                                size_t* n_states, size_t* width);
+int jb_engine_duration_parameters(const jb_engine* e, const char* const* lines, size_t n_lines,
+                                  double* mean, double* vari, size_t cap, size_t* n_states);
+int jb_engine_gv_parameters(const jb_engine* e, const char* const* lines, size_t n_lines,
+                            size_t stream, double* mean, double* vari, uint8_t* gv_switch,
+                            size_t cap, size_t* dim, size_t* n_states, int* has_gv);
+
+/* Resident batch: inputs packed and copied to HBM once, kernels timed alone (bench "value"). */
+typedef struct jb_resident jb_resident;
+int jb_resident_prepare(const jb_engine* e, const char* const* lines, const size_t* line_off,
+                        size_t n_utt, int device_index, jb_resident** out);
+/* Runs MLPG + vocoder kernels; device time in ms by CUDA events; timings as above (optional). */
+int jb_resident_run(const jb_engine* e, jb_resident* r, double* device_ms, double* timings);
+int jb_resident_fetch(const jb_engine* e, jb_resident* r, double** out, size_t* out_off);
+void jb_resident_free(const jb_engine* e, jb_resident* r);
+
+/* Engine::generator + SpeechGenerator (src/engine.rs:301, src/speech.rs:25-96), batched:
+ * MLPG runs at open; every step emits up to n_frames frames per utterance. */
+int jb_stream_open(const jb_engine* e, const char* const* lines, const size_t* line_off,
+                   size_t n_utt, int device, jb_stream** out);
+size_t jb_stream_fperiod(const jb_stream* s);            /* SpeechGenerator::fperiod */
+size_t jb_stream_synthesized_frames(const jb_stream* s); /* SpeechGenerator::synthesized_frames */
+/* SpeechGenerator::generate_step for n_frames frames of every utterance. buf holds
+ * n_utt * n_frames * fperiod doubles (cap = its length; too short -> JB_ERR_ARGUMENT, the
+ * reference panics). written[u] = samples produced for utterance u, 0 once it has ended. */
+int jb_stream_step(jb_stream* s, size_t n_frames, double* buf, size_t cap, size_t* written,
+                   double* device_ms);
+void jb_stream_close(jb_stream* s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* JBONSAI_B200_H_ */

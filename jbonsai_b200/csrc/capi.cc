@@ -1,0 +1,327 @@
+// extern "C" layer over jb::Engine (declarations + reference citations: include/jbonsai_b200.h).
+#include <cstring>
+#include <string>
+
+#include <cuda_runtime.h>
+
+#include "../../include/jbonsai_b200.h"
+#include "engine.h"
+
+struct jb_engine {
+  std::unique_ptr<jb::Engine> e;
+};
+struct jb_stream {
+  std::unique_ptr<jb::Stream> s;
+};
+struct jb_resident;  // opaque alias of jb::Engine::Resident
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(const std::exception& ex) {
+  g_err = ex.what();
+  if (auto* je = dynamic_cast<const jb::Error*>(&ex)) return je->code;
+  return JB_ERR_ARGUMENT;
+}
+
+#define JB_TRY try {
+#define JB_CATCH                     \
+  }                                  \
+  catch (const std::exception& ex) { \
+    return fail(ex);                 \
+  }                                  \
+  return JB_OK;
+
+std::vector<std::vector<std::string>> to_utts(const char* const* lines, const size_t* line_off,
+                                              size_t n_utt) {
+  std::vector<std::vector<std::string>> utts(n_utt);
+  for (size_t u = 0; u < n_utt; ++u) {
+    if (line_off[u + 1] < line_off[u]) throw jb::Error(jb::kErrArgument, "line_off must be non-decreasing");
+    utts[u].assign(lines + line_off[u], lines + line_off[u + 1]);
+  }
+  return utts;
+}
+
+void fill_timings(const jb::BatchTimings& t, double* out) {
+  if (!out) return;
+  const double v[16] = {t.host_frontend_ms, t.pack_ms, t.h2d_ms, t.kernels_ms, t.d2h_ms, t.mlpg_ms,
+                        t.excitation_ms, t.mlsa_ms, (double)t.h2d_bytes, (double)t.d2h_bytes,
+                        (double)t.total_frames, (double)t.total_samples, (double)t.voiced_samples,
+                        (double)t.launches, 0, 0};
+  memcpy(out, v, sizeof v);
+}
+
+double* dup_vec(const std::vector<double>& v) {
+  double* p = (double*)malloc(v.size() * 8 + 8);
+  if (!v.empty()) memcpy(p, v.data(), v.size() * 8);
+  return p;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* jb_last_error(void) { return g_err.c_str(); }
+const char* jb_version(void) { return "jbonsai_b200 0.1.0 (reference jbonsai 0.4.2)"; }
+
+int jb_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+int jb_engine_load(const char* const* paths, size_t n, jb_engine** out) {
+  JB_TRY
+  std::vector<std::string> p(paths, paths + n);
+  *out = new jb_engine{jb::Engine::load(p)};
+  JB_CATCH
+}
+
+int jb_engine_load_from_bytes(const uint8_t* const* bufs, const size_t* lens, size_t n, jb_engine** out) {
+  JB_TRY
+  std::vector<std::vector<uint8_t>> b(n);
+  for (size_t i = 0; i < n; ++i) b[i].assign(bufs[i], bufs[i] + lens[i]);
+  *out = new jb_engine{jb::Engine::load_from_bytes(b)};
+  JB_CATCH
+}
+
+void jb_engine_free(jb_engine* e) { delete e; }
+
+int jb_engine_set_condition(jb_engine* e, const char* key, size_t idx, double value) {
+  JB_TRY
+  jb::condition_set(e->e->condition, key, idx, value);
+  JB_CATCH
+}
+
+int jb_engine_get_condition(const jb_engine* e, const char* key, size_t idx, double* value) {
+  JB_TRY
+  *value = jb::condition_get(e->e->condition, key, idx);
+  JB_CATCH
+}
+
+int jb_engine_set_interpolation_weight(jb_engine* e, int kind, size_t stream, const double* w, size_t n) {
+  JB_TRY
+  std::vector<double> v(w, w + n);
+  auto& iw = e->e->condition.interporation_weight;
+  if (kind == 0) iw.set_duration(v);
+  else if (kind == 1) iw.set_parameter(stream, v);
+  else if (kind == 2) iw.set_gv(stream, v);
+  else throw jb::Error(jb::kErrArgument, "kind must be 0, 1 or 2");
+  JB_CATCH
+}
+
+int jb_engine_set_devices(jb_engine* e, const int* devices, size_t n) {
+  JB_TRY
+  e->e->set_devices(std::vector<int>(devices, devices + n));
+  JB_CATCH
+}
+
+int jb_engine_set_mlsa_variant(jb_engine* e, int variant) {
+  e->e->mlsa_variant = variant;
+  return JB_OK;
+}
+
+int jb_engine_synthesize_batch(const jb_engine* e, const char* const* lines, const size_t* line_off,
+                               size_t n_utt, double** out, size_t* out_off, double* timings) {
+  JB_TRY
+  std::vector<size_t> off;
+  jb::BatchTimings tm;
+  e->e->synthesize_batch(to_utts(lines, line_off, n_utt), out, &off, nullptr, &tm);
+  memcpy(out_off, off.data(), off.size() * sizeof(size_t));
+  fill_timings(tm, timings);
+  JB_CATCH
+}
+
+int jb_engine_synthesize(const jb_engine* e, const char* const* lines, size_t n_lines, double** out,
+                         size_t* out_len) {
+  size_t line_off[2] = {0, n_lines}, out_off[2] = {0, 0};
+  int rc = jb_engine_synthesize_batch(e, lines, line_off, 1, out, out_off, nullptr);
+  if (rc == JB_OK) *out_len = out_off[1];
+  return rc;
+}
+
+void jb_free(void* p) {
+  // pool-owned pinned buffers are recycled; anything else came from malloc
+  if (!p) return;
+  cudaPointerAttributes attr;
+  if (cudaPointerGetAttributes(&attr, p) == cudaSuccess && attr.type == cudaMemoryTypeHost) {
+    jb::Engine::free_output((double*)p);
+    return;
+  }
+  cudaGetLastError();
+  free(p);
+}
+
+int jb_engine_debug_batch(const jb_engine* e, const char* const* lines, const size_t* line_off,
+                          size_t n_utt, double** mcp, double** lf0, double** lpf, double** pulse,
+                          double** exc, int64_t* frame_off) {
+  JB_TRY
+  jb::BatchDebug dbg;
+  dbg.want_parameters = true;
+  dbg.want_pulse = true;
+  dbg.stop_after_excitation = true;
+  std::vector<size_t> off;
+  double* w = nullptr;
+  e->e->synthesize_batch(to_utts(lines, line_off, n_utt), &w, &off, &dbg, nullptr);
+  std::vector<double> ex(w, w + off.back());
+  jb::Engine::free_output(w);
+  *mcp = dup_vec(dbg.mcp);
+  *lf0 = dup_vec(dbg.lf0);
+  *lpf = dup_vec(dbg.lpf);
+  *pulse = dup_vec(dbg.pulse);
+  *exc = dup_vec(ex);
+  for (size_t u = 0; u <= n_utt; ++u) frame_off[u] = u < dbg.frame_off.size() ? dbg.frame_off[u] : 0;
+  JB_CATCH
+}
+
+int jb_engine_noise(const jb_engine* e, size_t n, double* out) {
+  JB_TRY
+  std::vector<double> v = e->e->noise_prefix(n);
+  memcpy(out, v.data(), n * 8);
+  JB_CATCH
+}
+
+int jb_engine_durations(const jb_engine* e, const char* const* lines, size_t n_lines,
+                        int32_t* durations, size_t cap, size_t* n_states) {
+  JB_TRY
+  std::vector<std::string> l(lines, lines + n_lines);
+  jb::UtterancePack p = jb::build_utterance(e->e->voices(), e->e->condition, l);
+  *n_states = p.nstates;
+  if (p.nstates > cap) throw jb::Error(jb::kErrArgument, "durations buffer too small");
+  if (p.nstates) memcpy(durations, p.durations.data(), p.nstates * 4);
+  JB_CATCH
+}
+
+int jb_engine_tree_index(const jb_engine* e, size_t voice, int model, size_t stream,
+                         size_t state_index, const char* label, long* tree_index, long* pdf_index) {
+  JB_TRY
+  const jb::VoiceSet& vs = e->e->voices();
+  if (voice >= vs.size()) throw jb::Error(jb::kErrArgument, "voice index out of range");
+  const jb::Voice& v = *vs.voices[voice];
+  const jb::Model* m = nullptr;
+  if (model == 0) m = &v.duration_model;
+  else {
+    if (stream >= v.stream_models.size()) throw jb::Error(jb::kErrArgument, "stream out of range");
+    if (model == 1) m = &v.stream_models[stream].stream_model;
+    else if (v.stream_models[stream].has_gv) m = &v.stream_models[stream].gv_model;
+    else throw jb::Error(jb::kErrArgument, "stream has no GV model");
+  }
+  m->get_index(state_index, label, tree_index, pdf_index);
+  JB_CATCH
+}
+
+int jb_engine_stream_parameters(const jb_engine* e, const char* const* lines, size_t n_lines,
+                                size_t stream, double* mean, double* vari, double* msd, size_t cap,
+                                size_t* n_states, size_t* width) {
+  JB_TRY
+  std::vector<std::string> l(lines, lines + n_lines);
+  jb::UtterancePack p = jb::build_utterance(e->e->voices(), e->e->condition, l);
+  if (stream >= p.streams.size()) throw jb::Error(jb::kErrArgument, "stream out of range");
+  const jb::StreamPack& sp = p.streams[stream];
+  *n_states = p.nstates;
+  *width = sp.dim * sp.nwin;
+  if (sp.mean.size() > cap) throw jb::Error(jb::kErrArgument, "parameter buffer too small");
+  if (!sp.mean.empty()) {
+    memcpy(mean, sp.mean.data(), sp.mean.size() * 8);
+    memcpy(vari, sp.vari.data(), sp.vari.size() * 8);
+    memcpy(msd, sp.msd.data(), sp.msd.size() * 8);
+  }
+  JB_CATCH
+}
+
+int jb_engine_duration_parameters(const jb_engine* e, const char* const* lines, size_t n_lines,
+                                  double* mean, double* vari, size_t cap, size_t* n_states) {
+  JB_TRY
+  std::vector<std::string> l(lines, lines + n_lines);
+  const jb::Condition& c = e->e->condition;
+  jb::Labels labels = jb::Labels::load_from_strings(c.sampling_frequency, c.fperiod, l);
+  jb::Models models{labels.labels, e->e->voices(), c.interporation_weight};
+  std::vector<jb::MeanVari> d = models.duration();
+  *n_states = d.size();
+  if (d.size() > cap) throw jb::Error(jb::kErrArgument, "duration buffer too small");
+  for (size_t i = 0; i < d.size(); ++i) {
+    mean[i] = d[i].mean;
+    vari[i] = d[i].vari;
+  }
+  JB_CATCH
+}
+
+int jb_engine_gv_parameters(const jb_engine* e, const char* const* lines, size_t n_lines,
+                            size_t stream, double* mean, double* vari, uint8_t* gv_switch,
+                            size_t cap, size_t* dim, size_t* n_states, int* has_gv) {
+  JB_TRY
+  std::vector<std::string> l(lines, lines + n_lines);
+  jb::UtterancePack p = jb::build_utterance(e->e->voices(), e->e->condition, l);
+  if (stream >= p.streams.size()) throw jb::Error(jb::kErrArgument, "stream out of range");
+  const jb::StreamPack& sp = p.streams[stream];
+  *has_gv = sp.has_gv;
+  *dim = sp.dim;
+  *n_states = p.nstates;
+  if (sp.has_gv) {
+    if (sp.dim > cap || p.nstates > cap) throw jb::Error(jb::kErrArgument, "gv buffer too small");
+    memcpy(mean, sp.gv_mean.data(), sp.dim * 8);
+    memcpy(vari, sp.gv_vari.data(), sp.dim * 8);
+    memcpy(gv_switch, sp.gv_switch.data(), p.nstates);
+  }
+  JB_CATCH
+}
+
+int jb_resident_prepare(const jb_engine* e, const char* const* lines, const size_t* line_off,
+                        size_t n_utt, int device_index, jb_resident** out) {
+  JB_TRY
+  *out = (jb_resident*)e->e->prepare(to_utts(lines, line_off, n_utt), device_index);
+  JB_CATCH
+}
+
+int jb_resident_run(const jb_engine* e, jb_resident* r, double* device_ms, double* timings) {
+  JB_TRY
+  jb::BatchTimings tm;
+  double ms = e->e->run_resident((jb::Engine::Resident*)r, &tm);
+  if (device_ms) *device_ms = ms;
+  fill_timings(tm, timings);
+  JB_CATCH
+}
+
+int jb_resident_fetch(const jb_engine* e, jb_resident* r, double** out, size_t* out_off) {
+  JB_TRY
+  std::vector<size_t> off;
+  e->e->fetch_resident((jb::Engine::Resident*)r, out, &off);
+  memcpy(out_off, off.data(), off.size() * sizeof(size_t));
+  JB_CATCH
+}
+
+void jb_resident_free(const jb_engine* e, jb_resident* r) {
+  try {
+    e->e->release((jb::Engine::Resident*)r);
+  } catch (...) {
+  }
+}
+
+int jb_stream_open(const jb_engine* e, const char* const* lines, const size_t* line_off,
+                   size_t n_utt, int device, jb_stream** out) {
+  JB_TRY
+  *out = new jb_stream{std::unique_ptr<jb::Stream>(
+      new jb::Stream(e->e.get(), to_utts(lines, line_off, n_utt), device))};
+  JB_CATCH
+}
+
+size_t jb_stream_fperiod(const jb_stream* s) { return s->s->fperiod(); }
+size_t jb_stream_synthesized_frames(const jb_stream* s) { return s->s->synthesized_frames(); }
+
+int jb_stream_step(jb_stream* s, size_t n_frames, double* buf, size_t cap, size_t* written,
+                   double* device_ms) {
+  JB_TRY
+  if (cap < s->s->n_utt() * n_frames * s->s->fperiod())
+    throw jb::Error(jb::kErrArgument, "The length of speech buffer must be larger than fperiod.");
+  double ms = s->s->step(n_frames, buf, written);
+  if (device_ms) *device_ms = ms;
+  JB_CATCH
+}
+
+void jb_stream_close(jb_stream* s) { delete s; }
+
+}  // extern "C"

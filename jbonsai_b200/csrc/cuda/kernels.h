@@ -1,0 +1,123 @@
+// Device-side data layout and kernel launchers for the hot path (sm_100a).
+//
+// Path: MlpgAdjust::create (src/mlpg_adjust/mod.rs:51-95) for the MCP / LF0 /
+// LPF streams of every utterance of a batch, then Vocoder::synthesize (src/vocoder/mod.rs:72-178)
+// over every frame. All launchers are asynchronous on `stream` and return cudaError_t as int.
+#pragma once
+
+#include <cstddef>
+#include <cstdint>
+
+#include <cuda_runtime.h>
+
+namespace jbk {
+
+constexpr int kMaxWin = 4;       // windows per stream (static, delta, delta-delta, +1)
+constexpr int kMaxWinWidth = 5;  // taps per window
+constexpr int kPade = 5;         // MLSA Pade order (N = 6, src/vocoder/mlsa.rs:31)
+
+struct WindowSet {
+  int nwin;
+  int width[kMaxWin];
+  double coef[kMaxWin][kMaxWinWidth];
+  int band_width() const {  // MlpgMatrix width = max_width*2+1 (mlpg.rs:27)
+    int m = 0;
+    for (int i = 0; i < nwin; ++i) m = width[i] > m ? width[i] : m;
+    return (m / 2) * 2 + 1;
+  }
+};
+
+// One batch, all utterances concatenated. "states" = labels * num_states, "frames" = sum of
+// state durations, "samples" = frames * fperiod.
+struct BatchLayout {
+  int n_utt;
+  const int64_t* state_off;  // [n_utt+1]
+  const int64_t* frame_off;  // [n_utt+1]
+  const int32_t* durations;  // [total_states]
+  int32_t* frame_state;      // [total_frames]  (out of expand) state index within the utterance
+};
+
+// Per stream state-level input (A0 contract) + MLPG work arrays.
+struct StreamDev {
+  int dim;
+  int nwin;  // == windows.nwin
+  int is_msd;
+  int has_gv;
+  WindowSet windows;
+  double msd_threshold;
+  double gv_weight;
+  const double* mean;        // [total_states][nwin*dim]
+  const double* vari;        // [total_states][nwin*dim]
+  const double* msd;         // [total_states] (only read when is_msd)
+  const double* gv_mean;     // [n_utt][dim]
+  const double* gv_vari;     // [n_utt][dim]
+  const uint8_t* gv_switch;  // [total_states]
+  // MSD bookkeeping (only when is_msd): all [total_frames] / [n_utt]
+  int32_t* left;     // distance to the left mask edge   (mask.rs:51-82)
+  int32_t* right;    // distance to the right mask edge
+  int32_t* vidx;     // compacted index -> frame (within utterance)
+  int32_t* nvoiced;  // [n_utt] number of unmasked frames
+  // scratch planes, each [total_frames][dim]
+  double* scratch;   // n_scratch_planes(band) planes
+  double* par;       // output [total_frames][dim] (NODATA in masked frames)
+};
+
+inline int mlpg_scratch_planes(int band_width, int has_gv) {
+  // factorised band (bw) + wum/g (2) [+ unfactorised band (bw) + wum copy is shared + grad (1)]
+  return band_width + 2 + (has_gv ? band_width + 1 : 0);
+}
+
+struct StreamSet {
+  int n;
+  StreamDev s[3];
+};
+
+int launch_expand(const BatchLayout& b, const StreamSet& streams, cudaStream_t stream);
+int launch_mlpg(const BatchLayout& b, const StreamDev& s, int64_t total_frames, cudaStream_t stream);
+
+struct VocoderParams {
+  int nmcp;     // 35
+  int nlpf;     // 31 (0 = no LPF stream)
+  int fperiod;  // 240
+  double rate;  // 48000
+  double alpha;
+  double volume;
+};
+
+// Per-utterance vocoder state carried between chunked launches (streaming, speech.rs:65-83).
+// Layout: [n_utt][kVocStateDoubles].
+//   [0..170)   d21[5][34]  (taps d[1..34] of each Pade stage; d[0] is write-only in the reference)
+//   [170..176) d11, [176..182) d12, [182..188) d22   (mlsa.rs:5-10)
+//   [188..223) coefficients[35]                      (vocoder/mod.rs Stage::Zero)
+//   [223] pitch_of_curr_point [224] pitch_counter    (excitation.rs:2-10)
+constexpr int kVocStateDoubles = 232;
+
+struct VocoderDev {
+  const double* mcp;    // [total_frames][nmcp] MLPG output
+  const double* lf0;    // [total_frames]
+  const double* lpf;    // [total_frames][nlpf]
+  const double* noise;  // [>= max samples per utterance] global Gaussian sequence
+  double* b;            // [total_frames][nmcp]  mc2b(mcp)   (out of frame_prep)
+  double* pitch;        // [total_frames]        p per frame (out of frame_prep)
+  double* pulse;        // [total_samples]       pulse amplitude or 0 (out of pitch kernel)
+  double* wave;         // [total_samples]       excitation*gain, then filtered in place
+  double* state;        // [n_utt][kVocStateDoubles] or nullptr (whole-utterance synthesis)
+  int frame_begin;      // first frame (per utterance) processed by this launch
+  int frame_count;      // frames processed per utterance by this launch (clipped to its length)
+};
+
+int launch_frame_prep(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,
+                      int64_t total_frames, cudaStream_t stream);
+int launch_pulse(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, cudaStream_t stream);
+int launch_excitation(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,
+                      int64_t total_frames, cudaStream_t stream);
+// variant: 0 = bit-faithful stage-per-lane kernel (v1)
+int launch_mlsa(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, int variant,
+                cudaStream_t stream);
+
+// Streaming: copy frames [frame_begin, frame_begin+frame_count) of every utterance into
+// chunk[n_utt][frame_count*fperiod] (zero padded past the end of an utterance).
+int launch_gather_chunk(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,
+                        double* chunk, cudaStream_t stream);
+
+}  // namespace jbk

@@ -1,0 +1,314 @@
+// MLPG kernel (sm_100a): banded W'U^-1W build, LDL^T factorisation, forward/backward
+// substitution and the GV Newton adjustment — one independent system per
+// (utterance, stream, dimension), one thread per system, time recurrences in-thread.
+//
+// Reference path: MlpgAdjust::create (src/mlpg_adjust/mod.rs:51-95), Mask (mask.rs:18-83),
+// MlpgMatrix / MlpgGlobalVariance (mlpg.rs:22-292), MeanVari::with_ivar (model/mean_vari.rs:21-31).
+//
+// Layout: every per-frame work plane is [frame][dim] so that the threads of a warp
+// (consecutive dims of one utterance) touch consecutive doubles. Compile with -fmad=false:
+// the operation order below is the reference's and no multiply-add may be contracted, which
+// makes the generated parameters bit-identical to the CPU restatement.
+#include "kernels.h"
+
+namespace jbk {
+
+namespace {
+
+constexpr double kNoData = -1e10;
+
+// ---------------------------------------------------------------- expand
+// One thread per utterance: duration expansion (IterExt::duration, mod.rs:105-112), MSD mask
+// (Mask::create, mask.rs:20-28), boundary distances (mask.rs:51-82) and voiced compaction.
+__global__ void k_expand(BatchLayout b, StreamSet set) {
+  const StreamDev* streams = set.s;
+  const int nstream = set.n;
+  int u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= b.n_utt) return;
+  const int64_t soff = b.state_off[u], foff = b.frame_off[u];
+  const int S = (int)(b.state_off[u + 1] - soff);
+  const int T = (int)(b.frame_off[u + 1] - foff);
+  int t = 0;
+  for (int s = 0; s < S; ++s) {
+    int dur = b.durations[soff + s];
+    for (int k = 0; k < dur; ++k) b.frame_state[foff + t++] = s;
+  }
+  for (int si = 0; si < nstream; ++si) {
+    const StreamDev& sd = streams[si];
+    if (!sd.is_msd) continue;
+    int left = 0, nv = 0;
+    for (int f = 0; f < T; ++f) {
+      bool m = sd.msd[soff + b.frame_state[foff + f]] > sd.msd_threshold;
+      if (m) {
+        sd.left[foff + f] = f - left;
+        sd.vidx[foff + nv++] = f;
+      } else {
+        sd.left[foff + f] = -1;  // masked
+        left = f + 1;
+      }
+    }
+    sd.nvoiced[u] = nv;
+    int right = T - 1;
+    for (int f = T - 1; f >= 0; --f) {
+      if (sd.left[foff + f] >= 0) {
+        sd.right[foff + f] = right - f;
+      } else {
+        sd.right[foff + f] = -1;
+        if (f == 0) break;
+        right = f - 1;
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ double with_ivar(double vari) {
+  double a = fabs(vari);
+  if (a > 1e19) return 0.0;
+  if (a < 1e-19) return 1e38;
+  return 1.0 / vari;
+}
+
+// ---------------------------------------------------------------- solve (+GV)
+template <int BW>
+__global__ void __launch_bounds__(128) k_mlpg(BatchLayout b, StreamDev s, int64_t plane) {
+  const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int u = gid / s.dim, d = gid - u * s.dim;
+  if (u >= b.n_utt) return;
+  const int64_t soff = b.state_off[u], foff = b.frame_off[u];
+  const int T = (int)(b.frame_off[u + 1] - foff);
+  const int dim = s.dim, L = s.dim * s.nwin;
+  const int Tp = s.is_msd ? s.nvoiced[u] : T;
+  const bool msd = s.is_msd != 0;
+
+  // scratch planes, all indexed by compacted frame k
+  double* const base = s.scratch + foff * dim + d;
+  auto F = [&](int j, int k) -> double& { return base[(int64_t)j * plane + (int64_t)k * dim]; };  // factorised band
+  double* const pwum = base + (int64_t)BW * plane;
+  double* const pg = base + (int64_t)(BW + 1) * plane;  // g, then par
+  auto O = [&](int j, int k) -> double& {  // un-factorised band (GV only)
+    return base[(int64_t)(BW + 2 + j) * plane + (int64_t)k * dim];
+  };
+  double* const pgrad = base + (int64_t)(2 * BW + 2) * plane;
+
+  auto frame_of = [&](int k) -> int { return msd ? s.vidx[foff + k] : k; };
+
+  // (mean, ivar) of window w at compacted index k  (mod.rs:57-84)
+  auto param = [&](int w, int k, double& mean, double& ivar) {
+    const int t = frame_of(k);
+    const int st = b.frame_state[foff + t];
+    const int64_t o = (soff + st) * L + dim * w + d;
+    mean = s.mean[o];
+    ivar = with_ivar(s.vari[o]);
+    if (w != 0) {
+      const int l = msd ? s.left[foff + t] : t;
+      const int r = msd ? s.right[foff + t] : T - 1 - t;
+      const int wd = s.windows.width[w];
+      const int lw = wd / 2, rw = wd - lw - 1;
+      if (l < lw || r < rw) ivar = 0.0;
+    }
+  };
+
+  // ---- pass 1: band build (mlpg.rs:31-61), LDL (mlpg.rs:79-92), forward substitution (:98-104)
+  double prev[BW][BW];  // prev[i] = factorised row k-i (i >= 1)
+  double gprev[BW];
+#pragma unroll
+  for (int i = 0; i < BW; ++i) {
+    gprev[i] = 0.0;
+#pragma unroll
+    for (int j = 0; j < BW; ++j) prev[i][j] = 0.0;
+  }
+  for (int k = 0; k < Tp; ++k) {
+    double row[BW];
+#pragma unroll
+    for (int j = 0; j < BW; ++j) row[j] = 0.0;
+    double wum = 0.0;
+    for (int w = 0; w < s.nwin; ++w) {
+      const int wd = s.windows.width[w];
+      for (int index = wd - 1; index >= 0; --index) {
+        const double coef = s.windows.coef[w][index];
+        if (coef == 0.0) continue;
+        const int idx = k - (index - wd / 2);
+        if (idx < 0 || idx >= Tp) continue;
+        double mean, ivar;
+        param(w, idx, mean, ivar);
+        const double wu = coef * ivar;
+        wum += wu * mean;
+        for (int inner = wd - 1; inner >= index; --inner) {
+          const double c2 = s.windows.coef[w][inner];
+          if (c2 == 0.0) continue;
+          const int j = inner - index;
+          if (k + j >= Tp) break;
+#pragma unroll
+          for (int jj = 0; jj < BW; ++jj)
+            if (jj == j) row[jj] += wu * c2;
+        }
+      }
+    }
+    if (s.has_gv) {
+#pragma unroll
+      for (int j = 0; j < BW; ++j) O(j, k) = row[j];
+    }
+    pwum[(int64_t)k * dim] = wum;
+#pragma unroll
+    for (int i = 1; i < BW; ++i)
+      if (i < k + 1) row[0] -= prev[i][i] * prev[i][i] * prev[i][0];
+#pragma unroll
+    for (int i = 1; i < BW; ++i) {
+#pragma unroll
+      for (int j = 1; j < BW; ++j)
+        if (j < BW - i && j < k + 1) row[i] -= prev[j][j] * prev[j][i + j] * prev[j][0];
+      row[i] /= row[0];
+    }
+    double g = wum;
+#pragma unroll
+    for (int i = 1; i < BW; ++i)
+      if (i < k + 1) g -= prev[i][i] * gprev[i];
+#pragma unroll
+    for (int j = 0; j < BW; ++j) F(j, k) = row[j];
+    pg[(int64_t)k * dim] = g;
+#pragma unroll
+    for (int i = BW - 1; i >= 2; --i) {
+      gprev[i] = gprev[i - 1];
+#pragma unroll
+      for (int j = 0; j < BW; ++j) prev[i][j] = prev[i - 1][j];
+    }
+    if (BW > 1) {
+      gprev[1] = g;
+#pragma unroll
+      for (int j = 0; j < BW; ++j) prev[1][j] = row[j];
+    }
+  }
+
+  // ---- pass 2: backward substitution (mlpg.rs:106-113); par overwrites g in place
+  {
+    double pn[BW];  // pn[i] = par[k+i]
+#pragma unroll
+    for (int i = 0; i < BW; ++i) pn[i] = 0.0;
+    for (int k = Tp - 1; k >= 0; --k) {
+      double par = pg[(int64_t)k * dim] / F(0, k);
+#pragma unroll
+      for (int i = 1; i < BW; ++i)
+        if (i < Tp - k) par -= F(i, k) * pn[i];
+      pg[(int64_t)k * dim] = par;
+#pragma unroll
+      for (int i = BW - 1; i >= 2; --i) pn[i] = pn[i - 1];
+      if (BW > 1) pn[1] = par;
+    }
+  }
+  double* const ppar = pg;
+  auto PAR = [&](int k) -> double& { return ppar[(int64_t)k * dim]; };
+
+  // ---- GV (MlpgGlobalVariance::parmgen, mlpg.rs:258-292), reductions in increasing k
+  if (s.has_gv && Tp > 0) {
+    auto sw = [&](int k) -> bool { return s.gv_switch[soff + b.frame_state[foff + frame_of(k)]] != 0; };
+    int gv_length = 0;
+    for (int k = 0; k < Tp; ++k) gv_length += sw(k) ? 1 : 0;
+    if (gv_length > 0) {
+      const double gv_mean = s.gv_mean[(int64_t)u * dim + d] * s.gv_weight;  // mlpg.rs:137-138
+      const double gv_vari = s.gv_vari[(int64_t)u * dim + d];
+      auto calc_gv = [&](double& mean, double& vari) {  // mlpg.rs:168-188
+        double sum = 0.0;
+        for (int k = 0; k < Tp; ++k)
+          if (sw(k)) sum += PAR(k);
+        mean = sum / (double)gv_length;
+        double acc = 0.0;
+        for (int k = 0; k < Tp; ++k)
+          if (sw(k)) {
+            const double p = PAR(k);
+            acc += (p - mean) * (p - mean);
+          }
+        vari = acc / (double)gv_length;
+      };
+      {  // conv_gv (mlpg.rs:191-199)
+        double mean, vari;
+        calc_gv(mean, vari);
+        const double ratio = sqrt(gv_mean / vari);
+        for (int k = 0; k < Tp; ++k)
+          if (sw(k)) PAR(k) = ratio * (PAR(k) - mean) + mean;
+      }
+      const double wnorm = 1.0 / (double)((int64_t)s.nwin * (int64_t)Tp);
+      const double len = (double)Tp;
+      const double len2 = (double)((int64_t)Tp * (int64_t)Tp);
+      const double lenm1 = (double)(Tp - 1);
+      double step = 0.1, prevobj = 0.0;
+      for (int it = 1; it <= 5; ++it) {
+        double mean, vari;
+        calc_gv(mean, vari);
+        const double gvobj = -0.5 * 1.0 * vari * gv_vari * (vari - 2.0 * gv_mean);
+        // calc_hmmobj_derivative (mlpg.rs:200-226)
+        double hmmobj = 0.0;
+        for (int k = 0; k < Tp; ++k) {
+          double g = O(0, k) * PAR(k);
+#pragma unroll
+          for (int i = 1; i < BW; ++i) {
+            if (k + i < Tp) g += O(i, k) * PAR(k + i);
+            if (k + 1 > i) g += O(i, k - i) * PAR(k - i);
+          }
+          pgrad[(int64_t)k * dim] = g;
+        }
+        for (int k = 0; k < Tp; ++k)
+          hmmobj += 1.0 * wnorm * PAR(k) * (pwum[(int64_t)k * dim] - 0.5 * pgrad[(int64_t)k * dim]);
+        const double obj = -(hmmobj + gvobj);
+        if (it > 1) {
+          if (obj > prevobj)
+            step *= 0.5;
+          else if (obj < prevobj)
+            step *= 1.2;
+        }
+        // next_step (mlpg.rs:227-256)
+        const double dv = -2.0 * gv_vari * (vari - gv_mean) / len;
+        for (int k = 0; k < Tp; ++k) {
+          const double p = PAR(k);
+          const double h = -1.0 * wnorm * O(0, k) -
+                           1.0 * 2.0 / len2 *
+                               (lenm1 * gv_vari * (vari - gv_mean) +
+                                2.0 * gv_vari * (p - mean) * (p - mean));
+          const double gk = pgrad[(int64_t)k * dim], wk = pwum[(int64_t)k * dim];
+          double next_g;
+          if (sw(k))
+            next_g = 1.0 / h * (1.0 * wnorm * (-gk + wk) + 1.0 * dv * (p - mean));
+          else
+            next_g = 1.0 / h * (1.0 * wnorm * (-gk + wk));
+          PAR(k) = p + step * next_g;
+        }
+        prevobj = obj;
+      }
+    }
+  }
+
+  // ---- Mask::fill (mask.rs:34-49): scatter back, NODATA elsewhere
+  double* out = s.par + foff * dim + d;
+  if (msd) {
+    for (int t = 0; t < T; ++t)
+      if (s.left[foff + t] < 0) out[(int64_t)t * dim] = kNoData;
+    for (int k = 0; k < Tp; ++k) out[(int64_t)s.vidx[foff + k] * dim] = PAR(k);
+  } else {
+    for (int k = 0; k < Tp; ++k) out[(int64_t)k * dim] = PAR(k);
+  }
+}
+
+}  // namespace
+
+int launch_expand(const BatchLayout& b, const StreamSet& set, cudaStream_t stream) {
+  if (b.n_utt == 0) return 0;
+  int threads = 64, blocks = (b.n_utt + threads - 1) / threads;
+  k_expand<<<blocks, threads, 0, stream>>>(b, set);
+  return (int)cudaGetLastError();
+}
+
+int launch_mlpg(const BatchLayout& b, const StreamDev& s, int64_t total_frames, cudaStream_t stream) {
+  if (b.n_utt == 0 || s.dim == 0) return 0;
+  const int64_t plane = total_frames * s.dim;
+  const int64_t nthreads = (int64_t)b.n_utt * s.dim;
+  const int threads = 128;
+  const int blocks = (int)((nthreads + threads - 1) / threads);
+  switch (s.windows.band_width()) {
+    case 1: k_mlpg<1><<<blocks, threads, 0, stream>>>(b, s, plane); break;
+    case 3: k_mlpg<3><<<blocks, threads, 0, stream>>>(b, s, plane); break;
+    case 5: k_mlpg<5><<<blocks, threads, 0, stream>>>(b, s, plane); break;
+    default: return (int)cudaErrorInvalidValue;
+  }
+  return (int)cudaGetLastError();
+}
+
+}  // namespace jbk

@@ -1,0 +1,743 @@
+// Engine implementation: host batching layer + CUDA pipeline driver (no CPU fallback).
+#include "engine.h"
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <thread>
+
+#include <cuda_runtime.h>
+
+#include "cuda/kernels.h"
+
+namespace jb {
+
+#define JB_CUDA(x)                                                                          \
+  do {                                                                                      \
+    cudaError_t e_ = (x);                                                                   \
+    if (e_ != cudaSuccess)                                                                  \
+      throw Error(kErrCuda, std::string("CUDA error: ") + cudaGetErrorString(e_) + " in " #x); \
+  } while (0)
+#define JB_LAUNCH(x)                                                                        \
+  do {                                                                                      \
+    int e_ = (x);                                                                           \
+    if (e_ != 0)                                                                            \
+      throw Error(kErrCuda, std::string("CUDA launch error: ") +                            \
+                                cudaGetErrorString((cudaError_t)e_) + " in " #x);           \
+  } while (0)
+
+namespace {
+
+double now_ms() {
+  using namespace std::chrono;
+  return duration<double, std::milli>(steady_clock::now().time_since_epoch()).count();
+}
+
+// ---- pinned host pool (process-wide): outputs and staging blobs are recycled, because pinning
+// gigabytes per call would cost more than the kernels.
+struct PinnedPool {
+  std::mutex mu;
+  std::map<void*, size_t> live;                  // handed out
+  std::multimap<size_t, void*> cached;           // free, by capacity
+  size_t cached_bytes = 0;
+  static constexpr size_t kMaxCached = (size_t)24 << 30;
+  void* alloc(size_t bytes) {
+    if (bytes == 0) bytes = 8;
+    {
+      std::lock_guard<std::mutex> g(mu);
+      auto it = cached.lower_bound(bytes);
+      if (it != cached.end() && it->first <= bytes * 2 + (1 << 20)) {
+        void* p = it->second;
+        size_t cap = it->first;
+        cached.erase(it);
+        cached_bytes -= cap;
+        live[p] = cap;
+        return p;
+      }
+    }
+    void* p = nullptr;
+    cudaError_t e = cudaMallocHost(&p, bytes);
+    if (e != cudaSuccess)
+      throw Error(kErrCuda, std::string("cudaMallocHost failed: ") + cudaGetErrorString(e));
+    std::lock_guard<std::mutex> g(mu);
+    live[p] = bytes;
+    return p;
+  }
+  void release(void* p) {
+    if (!p) return;
+    size_t cap = 0;
+    {
+      std::lock_guard<std::mutex> g(mu);
+      auto it = live.find(p);
+      if (it == live.end()) return;
+      cap = it->second;
+      live.erase(it);
+      if (cached_bytes + cap <= kMaxCached) {
+        cached.emplace(cap, p);
+        cached_bytes += cap;
+        return;
+      }
+    }
+    cudaFreeHost(p);
+  }
+};
+PinnedPool& pinned() {
+  static PinnedPool* p = new PinnedPool();  // leaked on purpose: outlives static destructors
+  return *p;
+}
+
+size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+struct Carver {  // carve aligned sections out of one allocation
+  size_t off = 0;
+  size_t take(size_t bytes) {
+    size_t o = off;
+    off = align_up(off + bytes);
+    return o;
+  }
+};
+
+}  // namespace
+
+// ---------------------------------------------------------------- per-GPU context
+class DeviceCtx {
+ public:
+  int device;
+  cudaStream_t stream = nullptr;
+  std::mutex mu;  // one in-flight batch per (engine, device)
+  double* d_noise = nullptr;
+  size_t noise_len = 0;
+  cudaEvent_t ev[8];
+  std::multimap<size_t, void*> cached;  // freed device blocks
+
+  explicit DeviceCtx(int dev) : device(dev) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0)
+      throw Error(kErrCuda, std::string("no CUDA device available (") +
+                                (e != cudaSuccess ? cudaGetErrorString(e) : "device count 0") +
+                                "); jbonsai_b200 has no CPU fallback");
+    if (dev < 0 || dev >= n) throw Error(kErrCuda, "CUDA device index out of range");
+    JB_CUDA(cudaSetDevice(dev));
+    JB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    for (auto& x : ev) JB_CUDA(cudaEventCreate(&x));
+  }
+  ~DeviceCtx() {
+    cudaSetDevice(device);
+    for (auto& kv : cached) cudaFree(kv.second);
+    if (d_noise) cudaFree(d_noise);
+    for (auto& x : ev) cudaEventDestroy(x);
+    if (stream) cudaStreamDestroy(stream);
+  }
+  void* dalloc(size_t bytes, size_t* cap) {
+    if (bytes == 0) bytes = 256;
+    auto it = cached.lower_bound(bytes);
+    if (it != cached.end() && it->first <= bytes * 2 + (1 << 20)) {
+      void* p = it->second;
+      *cap = it->first;
+      cached.erase(it);
+      return p;
+    }
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) {
+      for (auto& kv : cached) cudaFree(kv.second);  // drop the cache and retry once
+      cached.clear();
+      JB_CUDA(cudaMalloc(&p, bytes));
+    }
+    *cap = bytes;
+    return p;
+  }
+  void dfree(void* p, size_t cap) {
+    if (p) cached.emplace(cap, p);
+  }
+};
+
+// ---------------------------------------------------------------- engine basics
+Engine::Engine(VoiceSet v) : voices_(std::move(v)) { condition.load_model(voices_); }
+Engine::~Engine() = default;
+
+std::unique_ptr<Engine> Engine::load(const std::vector<std::string>& paths) {
+  std::vector<std::vector<uint8_t>> bufs;
+  for (const auto& p : paths) bufs.push_back(read_file(p));
+  return load_from_bytes(bufs);
+}
+
+std::unique_ptr<Engine> Engine::load_from_bytes(const std::vector<std::vector<uint8_t>>& bufs) {
+  std::vector<std::shared_ptr<Voice>> voices;
+  for (const auto& b : bufs) voices.push_back(parse_htsvoice(b.data(), b.size()));
+  return std::unique_ptr<Engine>(new Engine(VoiceSet(std::move(voices))));
+}
+
+void Engine::set_devices(const std::vector<int>& devices) {
+  if (devices.empty()) throw Error(kErrArgument, "device list is empty");
+  devices_ = devices;
+}
+
+DeviceCtx* Engine::ctx(int device) const {
+  std::lock_guard<std::mutex> g(ctx_mu_);
+  auto it = ctx_.find(device);
+  if (it == ctx_.end()) it = ctx_.emplace(device, std::unique_ptr<DeviceCtx>(new DeviceCtx(device))).first;
+  return it->second.get();
+}
+
+void Engine::free_output(double* p) { pinned().release(p); }
+
+// Random::{nrandom, fill_queue} + rnd (src/vocoder/excitation.rs:197-237), run on the host so
+// that ln/sqrt come from the same libm the reference uses; extended lazily, 64 values a time.
+const std::vector<double>& Engine::noise_table(size_t n) const {  // caller holds noise_mu_
+  auto rnd = [&]() {
+    rng_next_ = rng_next_ * 1103515245ull + 12345ull;
+    uint64_t r = (rng_next_ / 65536ull) % 32768ull;
+    return (double)r / 32767.0;
+  };
+  if (noise_.capacity() < n) noise_.reserve(n + n / 4 + 64);
+  while (noise_.size() < n) {
+    double q[64], s[32];
+    int i = 0;
+    while (i < 32) {
+      double r1 = 2.0 * rnd() - 1.0;
+      double r2 = 2.0 * rnd() - 1.0;
+      double ss = r1 * r1 + r2 * r2;
+      if (0.0 < ss && ss < 1.0) {
+        q[2 * i] = r1;
+        q[2 * i + 1] = r2;
+        s[i] = ss;
+        ++i;
+      }
+    }
+    for (int k = 0; k < 32; ++k) {
+      double m = std::sqrt(-2.0 * std::log(s[k]) / s[k]);
+      q[2 * k] *= m;
+      q[2 * k + 1] *= m;
+    }
+    noise_.insert(noise_.end(), q, q + 64);
+  }
+  return noise_;
+}
+
+std::vector<double> Engine::noise_prefix(size_t n) const {
+  std::lock_guard<std::mutex> g(noise_mu_);
+  const std::vector<double>& t = noise_table(n);
+  return std::vector<double>(t.begin(), t.begin() + n);
+}
+
+std::vector<UtterancePack> Engine::build_packs(const std::vector<std::vector<std::string>>& utts) const {
+  if (condition.stage != 0)
+    throw Error(kErrUnsupported, "stage != 0 (GAMMA option: LSP/MGLSA vocoder) is not built yet");
+  if (condition.beta > 0.0)
+    throw Error(kErrUnsupported, "beta > 0 (mel-cepstral post-filter) is not built yet");
+  if (voices_.global_metadata().num_streams < 3 || voices_.stream_metadata(2).vector_length == 0)
+    throw Error(kErrUnsupported, "voices without an LPF stream are not built yet");
+  std::vector<UtterancePack> packs(utts.size());
+  size_t nthreads = std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), utts.size());
+  if (nthreads <= 1) {
+    for (size_t u = 0; u < utts.size(); ++u) packs[u] = build_utterance(voices_, condition, utts[u]);
+    return packs;
+  }
+  std::atomic<size_t> next{0};
+  std::mutex emu;
+  std::unique_ptr<Error> err;
+  std::vector<std::thread> th;
+  for (size_t t = 0; t < nthreads; ++t)
+    th.emplace_back([&]() {
+      for (;;) {
+        size_t u = next.fetch_add(1);
+        if (u >= utts.size()) return;
+        try {
+          packs[u] = build_utterance(voices_, condition, utts[u]);
+        } catch (const Error& e) {
+          std::lock_guard<std::mutex> g(emu);
+          if (!err) err.reset(new Error(e));
+        } catch (const std::exception& e) {
+          std::lock_guard<std::mutex> g(emu);
+          if (!err) err.reset(new Error(kErrArgument, e.what()));
+        }
+      }
+    });
+  for (auto& t : th) t.join();
+  if (err) throw *err;
+  return packs;
+}
+
+// ---------------------------------------------------------------- resident batch
+struct Engine::Resident {
+  DeviceCtx* ctx = nullptr;
+  int n_utt = 0;
+  int64_t total_states = 0, total_frames = 0, total_samples = 0, voiced_samples = 0;
+  int64_t max_frames = 0;
+  std::vector<int64_t> frame_off;  // host copy, [n_utt+1]
+  void* d_in = nullptr;
+  size_t in_cap = 0, in_bytes = 0;
+  void* d_work = nullptr;
+  size_t work_cap = 0;
+  jbk::BatchLayout layout{};
+  jbk::StreamSet streams{};
+  jbk::VocoderParams vp{};
+  jbk::VocoderDev vd{};
+  bool streaming = false;
+  double* d_chunk = nullptr;  // streaming gather buffer
+  size_t chunk_cap = 0;
+  int64_t h2d_bytes = 0;
+};
+
+static jbk::WindowSet make_windows(const Windows& w) {
+  jbk::WindowSet ws{};
+  if (w.size() > (size_t)jbk::kMaxWin) throw Error(kErrUnsupported, "more than 4 windows per stream");
+  ws.nwin = (int)w.size();
+  for (size_t i = 0; i < w.size(); ++i) {
+    if (w.windows[i].width() > (size_t)jbk::kMaxWinWidth)
+      throw Error(kErrUnsupported, "window wider than 5 taps");
+    ws.width[i] = (int)w.windows[i].width();
+    for (size_t k = 0; k < w.windows[i].width(); ++k) ws.coef[i][k] = w.windows[i].coefficients[k];
+  }
+  return ws;
+}
+
+// Batching layer: pack the state-level parameters of `packs` into one pinned blob, copy it to
+// the device, and lay out every work array of the pipeline in one arena.
+Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const UtterancePack* packs,
+                                        size_t n_utt, bool streaming, const Condition& cond) {
+  std::unique_ptr<Engine::Resident> r(new Engine::Resident());
+  r->ctx = ctx;
+  r->n_utt = (int)n_utt;
+  r->streaming = streaming;
+  const VoiceSet& vs = e.voices();
+  const size_t nstream = 3;
+  const int fperiod = (int)cond.fperiod;
+
+  std::vector<int64_t> state_off(n_utt + 1, 0);
+  r->frame_off.assign(n_utt + 1, 0);
+  for (size_t u = 0; u < n_utt; ++u) {
+    state_off[u + 1] = state_off[u] + (int64_t)packs[u].nstates;
+    r->frame_off[u + 1] = r->frame_off[u] + (int64_t)packs[u].nframes;
+    r->max_frames = std::max<int64_t>(r->max_frames, (int64_t)packs[u].nframes);
+  }
+  const int64_t TS = r->total_states = state_off[n_utt];
+  const int64_t TF = r->total_frames = r->frame_off[n_utt];
+  r->total_samples = TF * fperiod;
+  if (r->max_frames * (int64_t)fperiod > (int64_t)INT32_MAX)
+    throw Error(kErrUnsupported, "utterance longer than 2^31 samples");
+
+  // ---- input blob layout
+  Carver in;
+  const size_t o_soff = in.take((n_utt + 1) * 8), o_foff = in.take((n_utt + 1) * 8);
+  const size_t o_dur = in.take((size_t)TS * 4);
+  size_t o_mean[3], o_vari[3], o_msd[3], o_gvm[3], o_gvv[3], o_gsw[3];
+  int dim[3], nwin[3], is_msd[3], has_gv[3];
+  for (size_t s = 0; s < nstream; ++s) {
+    const StreamModelMetadata& md = vs.stream_metadata(s);
+    dim[s] = (int)md.vector_length;
+    nwin[s] = (int)vs.stream_windows(s).size();
+    is_msd[s] = md.is_msd;
+    has_gv[s] = md.use_gv;
+    const size_t L = (size_t)dim[s] * nwin[s];
+    o_mean[s] = in.take((size_t)TS * L * 8);
+    o_vari[s] = in.take((size_t)TS * L * 8);
+    o_msd[s] = is_msd[s] ? in.take((size_t)TS * 8) : 0;
+    o_gvm[s] = has_gv[s] ? in.take(n_utt * dim[s] * 8) : 0;
+    o_gvv[s] = has_gv[s] ? in.take(n_utt * dim[s] * 8) : 0;
+    o_gsw[s] = has_gv[s] ? in.take((size_t)TS) : 0;
+  }
+  r->in_bytes = in.off;
+  uint8_t* h = (uint8_t*)pinned().alloc(r->in_bytes);
+  struct Release {
+    void* p;
+    ~Release() { pinned().release(p); }
+  } rel{h};
+  memcpy(h + o_soff, state_off.data(), (n_utt + 1) * 8);
+  memcpy(h + o_foff, r->frame_off.data(), (n_utt + 1) * 8);
+  int64_t voiced_frames = 0;
+  for (size_t u = 0; u < n_utt; ++u) {
+    const UtterancePack& p = packs[u];
+    const size_t so = (size_t)state_off[u];
+    if (p.nstates) memcpy(h + o_dur + so * 4, p.durations.data(), p.nstates * 4);
+    for (size_t s = 0; s < nstream && s < p.streams.size(); ++s) {
+      const StreamPack& sp = p.streams[s];
+      const size_t L = (size_t)dim[s] * nwin[s];
+      if (sp.mean.size() != p.nstates * L) throw Error(kErrArgument, "stream pack has the wrong shape");
+      if (p.nstates) {
+        memcpy(h + o_mean[s] + so * L * 8, sp.mean.data(), p.nstates * L * 8);
+        memcpy(h + o_vari[s] + so * L * 8, sp.vari.data(), p.nstates * L * 8);
+        if (is_msd[s]) memcpy(h + o_msd[s] + so * 8, sp.msd.data(), p.nstates * 8);
+      }
+      if (has_gv[s]) {
+        double* gm = (double*)(h + o_gvm[s]) + u * dim[s];
+        double* gv = (double*)(h + o_gvv[s]) + u * dim[s];
+        for (int d = 0; d < dim[s]; ++d) {
+          gm[d] = sp.has_gv ? sp.gv_mean[d] : 0.0;
+          gv[d] = sp.has_gv ? sp.gv_vari[d] : 0.0;
+        }
+        if (p.nstates) {
+          if (sp.has_gv) memcpy(h + o_gsw[s] + so, sp.gv_switch.data(), p.nstates);
+          else memset(h + o_gsw[s] + so, 0, p.nstates);
+        }
+      }
+      if (s == 1)
+        for (size_t i = 0; i < p.nstates; ++i)
+          if (sp.msd[i] > cond.msd_threshold[1]) voiced_frames += p.durations[i];
+    }
+  }
+  r->voiced_samples = voiced_frames * fperiod;
+
+  JB_CUDA(cudaSetDevice(ctx->device));
+  r->d_in = ctx->dalloc(r->in_bytes, &r->in_cap);
+  JB_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
+  JB_CUDA(cudaMemcpyAsync(r->d_in, h, r->in_bytes, cudaMemcpyHostToDevice, ctx->stream));
+  JB_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
+  r->h2d_bytes = (int64_t)r->in_bytes;
+
+  // ---- work arena
+  Carver wk;
+  const size_t w_fstate = wk.take((size_t)TF * 4);
+  size_t w_left[3] = {0}, w_right[3] = {0}, w_vidx[3] = {0}, w_nv[3] = {0}, w_par[3];
+  size_t scratch_bytes = 0;
+  for (size_t s = 0; s < nstream; ++s) {
+    if (is_msd[s]) {
+      w_left[s] = wk.take((size_t)TF * 4);
+      w_right[s] = wk.take((size_t)TF * 4);
+      w_vidx[s] = wk.take((size_t)TF * 4);
+      w_nv[s] = wk.take(n_utt * 4);
+    }
+    w_par[s] = wk.take((size_t)TF * dim[s] * 8);
+    jbk::WindowSet ws = make_windows(vs.stream_windows(s));
+    scratch_bytes = std::max(scratch_bytes, (size_t)jbk::mlpg_scratch_planes(ws.band_width(), has_gv[s]) *
+                                                (size_t)TF * dim[s] * 8);
+  }
+  const size_t w_scratch = wk.take(scratch_bytes);
+  const size_t w_b = wk.take((size_t)TF * dim[0] * 8);
+  const size_t w_pitch = wk.take((size_t)TF * 8);
+  const size_t w_pulse = wk.take((size_t)r->total_samples * 8);
+  const size_t w_wave = wk.take((size_t)r->total_samples * 8);
+  const size_t w_state = streaming ? wk.take(n_utt * jbk::kVocStateDoubles * 8) : 0;
+  r->d_work = ctx->dalloc(wk.off, &r->work_cap);
+  uint8_t* di = (uint8_t*)r->d_in;
+  uint8_t* dw = (uint8_t*)r->d_work;
+
+  r->layout.n_utt = (int)n_utt;
+  r->layout.state_off = (const int64_t*)(di + o_soff);
+  r->layout.frame_off = (const int64_t*)(di + o_foff);
+  r->layout.durations = (const int32_t*)(di + o_dur);
+  r->layout.frame_state = (int32_t*)(dw + w_fstate);
+  r->streams.n = (int)nstream;
+  for (size_t s = 0; s < nstream; ++s) {
+    jbk::StreamDev& sd = r->streams.s[s];
+    sd.dim = dim[s];
+    sd.nwin = nwin[s];
+    sd.is_msd = is_msd[s];
+    sd.has_gv = has_gv[s];
+    sd.windows = make_windows(vs.stream_windows(s));
+    sd.msd_threshold = cond.msd_threshold[s];
+    sd.gv_weight = cond.gv_weight[s];
+    sd.mean = (const double*)(di + o_mean[s]);
+    sd.vari = (const double*)(di + o_vari[s]);
+    sd.msd = is_msd[s] ? (const double*)(di + o_msd[s]) : nullptr;
+    sd.gv_mean = has_gv[s] ? (const double*)(di + o_gvm[s]) : nullptr;
+    sd.gv_vari = has_gv[s] ? (const double*)(di + o_gvv[s]) : nullptr;
+    sd.gv_switch = has_gv[s] ? (const uint8_t*)(di + o_gsw[s]) : nullptr;
+    sd.left = is_msd[s] ? (int32_t*)(dw + w_left[s]) : nullptr;
+    sd.right = is_msd[s] ? (int32_t*)(dw + w_right[s]) : nullptr;
+    sd.vidx = is_msd[s] ? (int32_t*)(dw + w_vidx[s]) : nullptr;
+    sd.nvoiced = is_msd[s] ? (int32_t*)(dw + w_nv[s]) : nullptr;
+    sd.scratch = (double*)(dw + w_scratch);
+    sd.par = (double*)(dw + w_par[s]);
+  }
+  r->vp.nmcp = dim[0];
+  r->vp.nlpf = dim[2];
+  r->vp.fperiod = fperiod;
+  r->vp.rate = (double)cond.sampling_frequency;
+  r->vp.alpha = cond.alpha;
+  r->vp.volume = cond.volume;
+  r->vd.mcp = r->streams.s[0].par;
+  r->vd.lf0 = r->streams.s[1].par;
+  r->vd.lpf = r->streams.s[2].par;
+  r->vd.b = (double*)(dw + w_b);
+  r->vd.pitch = (double*)(dw + w_pitch);
+  r->vd.pulse = (double*)(dw + w_pulse);
+  r->vd.wave = (double*)(dw + w_wave);
+  r->vd.state = streaming ? (double*)(dw + w_state) : nullptr;
+  r->vd.frame_begin = 0;
+  r->vd.frame_count = -1;
+
+  // ---- global noise table on this device (F7: one sequence shared by every utterance)
+  const size_t need = (size_t)r->max_frames * fperiod;
+  if (need > ctx->noise_len) {
+    std::lock_guard<std::mutex> g(e.noise_mu_);
+    const std::vector<double>& tbl = e.noise_table(need + need / 2);
+    if (ctx->d_noise) JB_CUDA(cudaFree(ctx->d_noise));
+    JB_CUDA(cudaMalloc((void**)&ctx->d_noise, tbl.size() * 8));
+    JB_CUDA(cudaMemcpy(ctx->d_noise, tbl.data(), tbl.size() * 8, cudaMemcpyHostToDevice));
+    ctx->noise_len = tbl.size();
+  }
+  r->vd.noise = ctx->d_noise;
+  // the staging blob may be recycled only once the copy has finished
+  JB_CUDA(cudaEventSynchronize(ctx->ev[1]));
+  return r.release();
+}
+
+static void launch_mlpg_all(Engine::Resident* r) {
+  cudaStream_t st = r->ctx->stream;
+  JB_LAUNCH(jbk::launch_expand(r->layout, r->streams, st));
+  for (int s = 0; s < r->streams.n; ++s)
+    JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[s], r->total_frames, st));
+  JB_LAUNCH(jbk::launch_frame_prep(r->layout, r->vp, r->vd, r->total_frames, st));
+}
+
+static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_excitation,
+                           cudaEvent_t after_exc) {
+  cudaStream_t st = r->ctx->stream;
+  JB_LAUNCH(jbk::launch_pulse(r->layout, r->vp, r->vd, st));
+  JB_LAUNCH(jbk::launch_excitation(r->layout, r->vp, r->vd, r->total_frames, st));
+  if (after_exc) JB_CUDA(cudaEventRecord(after_exc, st));
+  if (!stop_after_excitation) JB_LAUNCH(jbk::launch_mlsa(r->layout, r->vp, r->vd, variant, st));
+}
+
+Engine::Resident* Engine::prepare(const std::vector<std::vector<std::string>>& utts,
+                                  int device_index) const {
+  std::vector<UtterancePack> packs = build_packs(utts);
+  if (device_index < 0 || (size_t)device_index >= devices_.size())
+    throw Error(kErrArgument, "device index out of range");
+  DeviceCtx* c = ctx(devices_[(size_t)device_index]);
+  std::lock_guard<std::mutex> g(c->mu);
+  return make_resident(*this, c, packs.data(), packs.size(), false, condition);
+}
+
+double Engine::run_resident(Resident* r, BatchTimings* tm) const {
+  DeviceCtx* c = r->ctx;
+  std::lock_guard<std::mutex> g(c->mu);
+  JB_CUDA(cudaSetDevice(c->device));
+  JB_CUDA(cudaEventRecord(c->ev[2], c->stream));
+  launch_mlpg_all(r);
+  JB_CUDA(cudaEventRecord(c->ev[3], c->stream));
+  launch_vocoder(r, mlsa_variant, false, c->ev[4]);
+  JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
+  JB_CUDA(cudaEventSynchronize(c->ev[5]));
+  float total = 0, a = 0, b = 0, m = 0;
+  JB_CUDA(cudaEventElapsedTime(&total, c->ev[2], c->ev[5]));
+  JB_CUDA(cudaEventElapsedTime(&a, c->ev[2], c->ev[3]));
+  JB_CUDA(cudaEventElapsedTime(&b, c->ev[3], c->ev[4]));
+  JB_CUDA(cudaEventElapsedTime(&m, c->ev[4], c->ev[5]));
+  if (tm) {
+    tm->kernels_ms = total;
+    tm->mlpg_ms = a;
+    tm->excitation_ms = b;
+    tm->mlsa_ms = m;
+    tm->total_frames = r->total_frames;
+    tm->total_samples = r->total_samples;
+    tm->voiced_samples = r->voiced_samples;
+    tm->h2d_bytes = r->h2d_bytes;
+    tm->launches = 1 + r->streams.n + 1 + 3;
+  }
+  return total;
+}
+
+void Engine::fetch_resident(Resident* r, double** out, std::vector<size_t>* out_off) const {
+  DeviceCtx* c = r->ctx;
+  std::lock_guard<std::mutex> g(c->mu);
+  JB_CUDA(cudaSetDevice(c->device));
+  double* h = (double*)pinned().alloc((size_t)r->total_samples * 8);
+  cudaError_t e = cudaMemcpyAsync(h, r->vd.wave, (size_t)r->total_samples * 8, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  if (e != cudaSuccess) {
+    pinned().release(h);
+    throw Error(kErrCuda, std::string("CUDA error: ") + cudaGetErrorString(e));
+  }
+  out_off->assign((size_t)r->n_utt + 1, 0);
+  for (int u = 0; u <= r->n_utt; ++u) (*out_off)[(size_t)u] = (size_t)(r->frame_off[(size_t)u] * r->vp.fperiod);
+  *out = h;
+}
+
+void Engine::release(Resident* r) const {
+  if (!r) return;
+  DeviceCtx* c = r->ctx;
+  std::lock_guard<std::mutex> g(c->mu);
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  c->dfree(r->d_in, r->in_cap);
+  c->dfree(r->d_work, r->work_cap);
+  if (r->d_chunk) c->dfree(r->d_chunk, r->chunk_cap);
+  delete r;
+}
+
+// Engine::synthesize for a batch (engine.rs:294-296 per utterance). Contiguous utterance ranges,
+// balanced by frame count, go to the engine's GPUs; no collective is involved.
+void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts, double** out,
+                              std::vector<size_t>* out_off, BatchDebug* dbg, BatchTimings* tm) const {
+  const double t0 = now_ms();
+  std::vector<UtterancePack> packs = build_packs(utts);
+  const double t1 = now_ms();
+  const size_t n = packs.size();
+  const int fperiod = (int)condition.fperiod;
+  out_off->assign(n + 1, 0);
+  for (size_t u = 0; u < n; ++u) (*out_off)[u + 1] = (*out_off)[u] + packs[u].nframes * (size_t)fperiod;
+  const size_t total = (*out_off)[n];
+  // touch the device even for an empty batch: there is no CPU path to fall back to
+  std::vector<DeviceCtx*> ctxs;
+  for (int d : devices_) ctxs.push_back(ctx(d));
+  double* host = (double*)pinned().alloc(total * 8);
+
+  // shard boundaries by cumulative frames
+  const size_t ndev = dbg ? 1 : std::min(ctxs.size(), std::max<size_t>(n, 1));
+  std::vector<size_t> cut(ndev + 1, n);
+  cut[0] = 0;
+  {
+    size_t u = 0;
+    for (size_t k = 1; k < ndev; ++k) {
+      const size_t target = total / ndev * k;
+      while (u < n && (*out_off)[u] < target) ++u;
+      cut[k] = u;
+    }
+  }
+  std::vector<BatchTimings> tms(ndev);
+  std::vector<std::unique_ptr<Error>> errs(ndev);
+  auto work = [&](size_t k) {
+    try {
+      const size_t u0 = cut[k], u1 = cut[k + 1];
+      if (u1 <= u0) return;
+      DeviceCtx* c = ctxs[k];
+      std::lock_guard<std::mutex> g(c->mu);
+      const double p0 = now_ms();
+      Resident* r = make_resident(*this, c, packs.data() + u0, u1 - u0, false, condition);
+      struct Guard {
+        DeviceCtx* c;
+        Resident* r;
+        ~Guard() {
+          cudaStreamSynchronize(c->stream);
+          c->dfree(r->d_in, r->in_cap);
+          c->dfree(r->d_work, r->work_cap);
+          delete r;
+        }
+      } guard{c, r};
+      BatchTimings& t = tms[k];
+      t.pack_ms = now_ms() - p0;
+      JB_CUDA(cudaEventRecord(c->ev[2], c->stream));
+      launch_mlpg_all(r);
+      JB_CUDA(cudaEventRecord(c->ev[3], c->stream));
+      launch_vocoder(r, mlsa_variant, dbg && dbg->stop_after_excitation, c->ev[4]);
+      JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
+      if (r->total_samples)
+        JB_CUDA(cudaMemcpyAsync(host + (*out_off)[u0], r->vd.wave, (size_t)r->total_samples * 8,
+                                cudaMemcpyDeviceToHost, c->stream));
+      JB_CUDA(cudaEventRecord(c->ev[6], c->stream));
+      if (dbg) {
+        const jbk::StreamSet& ss = r->streams;
+        const size_t TF = (size_t)r->total_frames;
+        if (dbg->want_parameters) {
+          dbg->mcp.resize(TF * ss.s[0].dim);
+          dbg->lf0.resize(TF * ss.s[1].dim);
+          dbg->lpf.resize(TF * ss.s[2].dim);
+          JB_CUDA(cudaMemcpyAsync(dbg->mcp.data(), ss.s[0].par, dbg->mcp.size() * 8, cudaMemcpyDeviceToHost, c->stream));
+          JB_CUDA(cudaMemcpyAsync(dbg->lf0.data(), ss.s[1].par, dbg->lf0.size() * 8, cudaMemcpyDeviceToHost, c->stream));
+          JB_CUDA(cudaMemcpyAsync(dbg->lpf.data(), ss.s[2].par, dbg->lpf.size() * 8, cudaMemcpyDeviceToHost, c->stream));
+        }
+        if (dbg->want_pulse) {
+          dbg->pulse.resize((size_t)r->total_samples);
+          JB_CUDA(cudaMemcpyAsync(dbg->pulse.data(), r->vd.pulse, dbg->pulse.size() * 8, cudaMemcpyDeviceToHost, c->stream));
+        }
+        dbg->frame_off = r->frame_off;
+      }
+      JB_CUDA(cudaStreamSynchronize(c->stream));
+      float f = 0;
+      JB_CUDA(cudaEventElapsedTime(&f, c->ev[0], c->ev[1])); t.h2d_ms = f;
+      JB_CUDA(cudaEventElapsedTime(&f, c->ev[2], c->ev[5])); t.kernels_ms = f;
+      JB_CUDA(cudaEventElapsedTime(&f, c->ev[2], c->ev[3])); t.mlpg_ms = f;
+      JB_CUDA(cudaEventElapsedTime(&f, c->ev[3], c->ev[4])); t.excitation_ms = f;
+      JB_CUDA(cudaEventElapsedTime(&f, c->ev[4], c->ev[5])); t.mlsa_ms = f;
+      JB_CUDA(cudaEventElapsedTime(&f, c->ev[5], c->ev[6])); t.d2h_ms = f;
+      t.h2d_bytes = r->h2d_bytes;
+      t.d2h_bytes = r->total_samples * 8;
+      t.total_frames = r->total_frames;
+      t.total_samples = r->total_samples;
+      t.voiced_samples = r->voiced_samples;
+      t.launches = 1 + r->streams.n + 1 + 3;
+    } catch (const Error& e) {
+      errs[k].reset(new Error(e));
+    } catch (const std::exception& e) {
+      errs[k].reset(new Error(kErrCuda, e.what()));
+    }
+  };
+  if (ndev == 1) {
+    work(0);
+  } else {
+    std::vector<std::thread> th;
+    for (size_t k = 0; k < ndev; ++k) th.emplace_back(work, k);
+    for (auto& t : th) t.join();
+  }
+  for (auto& e : errs)
+    if (e) {
+      pinned().release(host);
+      throw *e;
+    }
+  if (tm) {
+    *tm = BatchTimings();
+    tm->host_frontend_ms = t1 - t0;
+    for (const auto& t : tms) {
+      tm->pack_ms = std::max(tm->pack_ms, t.pack_ms);
+      tm->h2d_ms = std::max(tm->h2d_ms, t.h2d_ms);
+      tm->kernels_ms = std::max(tm->kernels_ms, t.kernels_ms);
+      tm->mlpg_ms = std::max(tm->mlpg_ms, t.mlpg_ms);
+      tm->excitation_ms = std::max(tm->excitation_ms, t.excitation_ms);
+      tm->mlsa_ms = std::max(tm->mlsa_ms, t.mlsa_ms);
+      tm->d2h_ms = std::max(tm->d2h_ms, t.d2h_ms);
+      tm->h2d_bytes += t.h2d_bytes;
+      tm->d2h_bytes += t.d2h_bytes;
+      tm->total_frames += t.total_frames;
+      tm->total_samples += t.total_samples;
+      tm->voiced_samples += t.voiced_samples;
+      tm->launches += t.launches;
+    }
+  }
+  *out = host;
+}
+
+// ---------------------------------------------------------------- streaming
+Stream::Stream(const Engine* e, const std::vector<std::vector<std::string>>& utts, int device)
+    : e_(e), r_(nullptr) {
+  std::vector<UtterancePack> packs = e->build_packs(utts);
+  DeviceCtx* c = e->ctx(device);
+  std::lock_guard<std::mutex> g(c->mu);
+  r_ = Engine::make_resident(*e, c, packs.data(), packs.size(), true, e->condition);
+  // MLPG for the whole utterance up front, like Engine::generator (engine.rs:333-357)
+  launch_mlpg_all(r_);
+  if (r_->n_utt)
+    JB_CUDA(cudaMemsetAsync(r_->vd.state, 0, (size_t)r_->n_utt * jbk::kVocStateDoubles * 8, c->stream));
+  JB_CUDA(cudaStreamSynchronize(c->stream));
+}
+
+Stream::~Stream() { e_->release(r_); }
+size_t Stream::fperiod() const { return (size_t)r_->vp.fperiod; }
+size_t Stream::n_utt() const { return (size_t)r_->n_utt; }
+const std::vector<int64_t>& Stream::frames() const { return r_->frame_off; }
+
+double Stream::step(size_t n_frames, double* out, size_t* written) {
+  DeviceCtx* c = r_->ctx;
+  std::lock_guard<std::mutex> g(c->mu);
+  JB_CUDA(cudaSetDevice(c->device));
+  const size_t fp = (size_t)r_->vp.fperiod, n = (size_t)r_->n_utt;
+  const size_t chunk = n_frames * fp;
+  if (n == 0 || n_frames == 0) return 0.0;
+  if (r_->chunk_cap < n * chunk * 8) {
+    if (r_->d_chunk) c->dfree(r_->d_chunk, r_->chunk_cap);
+    r_->d_chunk = (double*)c->dalloc(n * chunk * 8, &r_->chunk_cap);
+  }
+  r_->vd.frame_begin = (int)next_;
+  r_->vd.frame_count = (int)n_frames;
+  JB_CUDA(cudaEventRecord(c->ev[2], c->stream));
+  launch_vocoder(r_, e_->mlsa_variant, false, nullptr);
+  JB_LAUNCH(jbk::launch_gather_chunk(r_->layout, r_->vp, r_->vd, r_->d_chunk, c->stream));
+  JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
+  JB_CUDA(cudaMemcpyAsync(out, r_->d_chunk, n * chunk * 8, cudaMemcpyDeviceToHost, c->stream));
+  JB_CUDA(cudaStreamSynchronize(c->stream));
+  for (size_t u = 0; u < n; ++u) {
+    const int64_t T = r_->frame_off[u + 1] - r_->frame_off[u];
+    int64_t left = T - (int64_t)next_;
+    if (left < 0) left = 0;
+    written[u] = (size_t)std::min<int64_t>(left, (int64_t)n_frames) * fp;
+  }
+  next_ += n_frames;
+  float ms = 0;
+  JB_CUDA(cudaEventElapsedTime(&ms, c->ev[2], c->ev[5]));
+  return ms;
+}
+}  // namespace jb

@@ -1,0 +1,115 @@
+// C++ host Engine: the drop-in for jbonsai's `Engine` (src/engine.rs:247-366) whose
+// MlpgAdjust::create + SpeechGenerator::generate_all run as CUDA kernels on B200.
+// Host side = label parsing, tree lookup, durations and the batching layer that packs
+// state-level means/variances into device buffers (north star); there is no CPU fallback:
+// every synthesis call fails with kErrCuda when no device is usable.
+#pragma once
+
+#include <atomic>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "host/frontend.h"
+
+namespace jb {
+
+class DeviceCtx;  // one per GPU (engine.cc)
+
+// Optional per-call taps / counters used by tests and bench.py.
+struct BatchDebug {
+  bool want_parameters = false;  // copy MLPG output back: mcp [TF][35], lf0 [TF], lpf [TF][31]
+  bool want_pulse = false;       // copy the pulse train back: [TS]
+  bool stop_after_excitation = false;  // wave = excitation*gain (no MLSA)
+  std::vector<double> mcp, lf0, lpf, pulse;
+  std::vector<int64_t> frame_off;  // [n_utt+1]
+};
+
+struct BatchTimings {
+  double host_frontend_ms = 0;  // labels -> packs
+  double pack_ms = 0;
+  double h2d_ms = 0, kernels_ms = 0, d2h_ms = 0;  // CUDA-event times on the device stream
+  double mlpg_ms = 0, excitation_ms = 0, mlsa_ms = 0;
+  int64_t h2d_bytes = 0, d2h_bytes = 0;
+  int64_t total_frames = 0, total_samples = 0, voiced_samples = 0;
+  int launches = 0;
+};
+
+class Engine {
+ public:
+  static std::unique_ptr<Engine> load(const std::vector<std::string>& paths);
+  static std::unique_ptr<Engine> load_from_bytes(const std::vector<std::vector<uint8_t>>& bufs);
+  ~Engine();
+
+  Condition condition;  // public like the reference's `engine.condition`
+  const VoiceSet& voices() const { return voices_; }
+
+  // GPUs used by synthesize*/streams. Default: device 0 only.
+  void set_devices(const std::vector<int>& devices);
+  const std::vector<int>& devices() const { return devices_; }
+  int mlsa_variant = -1;  // -1 = default kernel
+
+  // Engine::synthesize for a batch: utterance u = lines[line_off[u] .. line_off[u+1]).
+  // `out` is a pinned host buffer owned by the engine's pool: release with free_output().
+  // out_off has n_utt+1 entries (sample offsets).
+  void synthesize_batch(const std::vector<std::vector<std::string>>& utts, double** out,
+                        std::vector<size_t>* out_off, BatchDebug* dbg = nullptr,
+                        BatchTimings* tm = nullptr) const;
+
+  // Hot path only: packs already built (bench "value": inputs resident on the device is handled
+  // inside by `resident` handles, see prepare/run below).
+  struct Resident;  // a batch whose packed inputs already sit in HBM
+  Resident* prepare(const std::vector<std::vector<std::string>>& utts, int device_index) const;
+  // Runs MLPG + vocoder kernels on the resident batch; waveform stays on the device.
+  // Returns device time in ms (CUDA events on the launching stream).
+  double run_resident(Resident* r, BatchTimings* tm = nullptr) const;
+  // Copies the resident batch's waveform to a pinned host buffer (pool-owned).
+  void fetch_resident(Resident* r, double** out, std::vector<size_t>* out_off) const;
+  void release(Resident* r) const;
+
+  static void free_output(double* p);
+
+  std::vector<double> noise_prefix(size_t n) const;  // first n Gaussians (host table)
+
+ private:
+  friend class DeviceCtx;
+  friend class Stream;
+  explicit Engine(VoiceSet v);
+  VoiceSet voices_;
+  std::vector<int> devices_{0};
+  mutable std::mutex ctx_mu_;
+  mutable std::map<int, std::unique_ptr<DeviceCtx>> ctx_;
+  DeviceCtx* ctx(int device) const;
+  // global white-noise sequence (excitation.rs:178-237; utterance independent)
+  mutable std::mutex noise_mu_;
+  mutable std::vector<double> noise_;
+  mutable uint64_t rng_next_ = 1;
+  const std::vector<double>& noise_table(size_t n) const;
+  std::vector<UtterancePack> build_packs(const std::vector<std::vector<std::string>>& utts) const;
+  static Resident* make_resident(const Engine& e, DeviceCtx* ctx, const UtterancePack* packs,
+                                 size_t n_utt, bool streaming, const Condition& cond);
+};
+
+// SpeechGenerator (src/speech.rs) for many utterances at once: MLPG up front, then the
+// vocoder advanced `n_frames` at a time with its state persisted in device memory.
+class Stream {
+ public:
+  Stream(const Engine* e, const std::vector<std::vector<std::string>>& utts, int device);
+  ~Stream();
+  size_t fperiod() const;
+  size_t n_utt() const;
+  // Generates up to n_frames frames for every utterance. out: [n_utt][n_frames*fperiod] (host),
+  // written[u] = samples produced for utterance u (0 at the end). Returns device ms.
+  double step(size_t n_frames, double* out, size_t* written);
+  const std::vector<int64_t>& frames() const;      // total frames per utterance
+  size_t synthesized_frames() const { return next_; }
+
+ private:
+  const Engine* e_;
+  Engine::Resident* r_;
+  size_t next_ = 0;
+};
+
+}  // namespace jb
