@@ -1,0 +1,382 @@
+"""jbonsai_b200 — ctypes binding of the C ABI in ``include/jbonsai_b200.h``.
+
+The product is the shared library ``jbonsai_b200/libjbonsai_b200.so`` (C++ host engine + CUDA
+kernels for sm_100a).  This module is only the thin Python face of that C ABI, shaped like
+the reference's public API so that tests read like the reference's own
+(``Engine::load`` / ``Engine::synthesize`` / ``Engine::generator``, src/engine.rs:247-366;
+``SpeechGenerator``, src/speech.rs:25-96).  There is no CPU fallback: when the library is
+missing the import raises, and synthesis calls raise ``JbError`` when no GPU is usable.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Iterable, List, Optional, Sequence
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libjbonsai_b200.so")
+
+# every symbol include/jbonsai_b200.h declares (checked by tests/test_capi_symbols.py)
+C_ABI_SYMBOLS = [
+    "jb_last_error", "jb_version", "jb_device_count", "jb_engine_load",
+    "jb_engine_load_from_bytes", "jb_engine_free", "jb_engine_set_condition",
+    "jb_engine_get_condition", "jb_engine_set_interpolation_weight", "jb_engine_set_devices",
+    "jb_engine_set_mlsa_variant", "jb_engine_synthesize", "jb_engine_synthesize_batch", "jb_free",
+    "jb_engine_debug_batch", "jb_engine_noise", "jb_engine_durations", "jb_engine_tree_index",
+    "jb_engine_stream_parameters", "jb_engine_duration_parameters", "jb_engine_gv_parameters",
+    "jb_resident_prepare", "jb_resident_run", "jb_resident_fetch", "jb_resident_free",
+    "jb_stream_open", "jb_stream_fperiod", "jb_stream_synthesized_frames", "jb_stream_step",
+    "jb_stream_close",
+]
+
+STATUS_NAMES = {
+    0: "OK", -1: "EmptyVoice", -2: "MetadataError", -3: "Io", -4: "ParserError",
+    -5: "ParseOptionError", -6: "JLabelParse", -7: "MissingLabel", -8: "FloatParse",
+    -9: "LengthMismatch", -10: "WeightError", -11: "IndexNotFound", -12: "Argument",
+    -13: "Cuda", -14: "Unsupported",
+}
+
+
+class JbError(RuntimeError):
+    """Mirror of EngineError (src/engine.rs:16-28): ``code`` is the jb_status."""
+
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"[{STATUS_NAMES.get(code, code)}] {msg}")
+        self.code = code
+        self.kind = STATUS_NAMES.get(code, str(code))
+
+
+def _load() -> C.CDLL:
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `make -C jbonsai_b200/csrc` "
+            "(or __graft_entry__.build()). jbonsai_b200 has no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    lib.jb_last_error.restype = C.c_char_p
+    lib.jb_version.restype = C.c_char_p
+    lib.jb_stream_fperiod.restype = C.c_size_t
+    lib.jb_stream_fperiod.argtypes = [C.c_void_p]
+    lib.jb_stream_synthesized_frames.restype = C.c_size_t
+    lib.jb_stream_synthesized_frames.argtypes = [C.c_void_p]
+    lib.jb_free.argtypes = [C.c_void_p]
+    lib.jb_free.restype = None
+    lib.jb_engine_free.argtypes = [C.c_void_p]
+    lib.jb_engine_free.restype = None
+    lib.jb_stream_close.argtypes = [C.c_void_p]
+    lib.jb_stream_close.restype = None
+    lib.jb_resident_free.argtypes = [C.c_void_p, C.c_void_p]
+    lib.jb_resident_free.restype = None
+    return lib
+
+
+lib = _load()
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise JbError(rc, (lib.jb_last_error() or b"").decode("utf-8", "replace"))
+
+
+def version() -> str:
+    return lib.jb_version().decode()
+
+
+def device_count() -> int:
+    return int(lib.jb_device_count())
+
+
+def _lines(lines: Sequence[str]):
+    enc = [l.encode("utf-8") if isinstance(l, str) else bytes(l) for l in lines]
+    return (C.c_char_p * max(len(enc), 1))(*enc), len(enc)
+
+
+def _flatten(utts: Sequence[Sequence[str]]):
+    flat: List[str] = []
+    off = [0]
+    for u in utts:
+        flat.extend(u)
+        off.append(len(flat))
+    arr, _ = _lines(flat)
+    offs = (C.c_size_t * len(off))(*off)
+    return arr, offs, len(utts)
+
+
+def _take(ptr, n: int) -> np.ndarray:
+    """Copy n doubles out of a library-owned buffer and release it."""
+    if n:
+        a = np.ctypeslib.as_array(ptr, shape=(n,)).copy()
+    else:
+        a = np.zeros(0, dtype=np.float64)
+    lib.jb_free(ptr)
+    return a
+
+
+TIMING_KEYS = ["host_frontend_ms", "pack_ms", "h2d_ms", "kernels_ms", "d2h_ms", "mlpg_ms",
+               "excitation_ms", "mlsa_ms", "h2d_bytes", "d2h_bytes", "frames", "samples",
+               "voiced_samples", "launches"]
+
+
+class Engine:
+    """``jbonsai::Engine`` (src/engine.rs:247-366) on B200."""
+
+    def __init__(self, handle: C.c_void_p):
+        self._h = handle
+
+    # -- Engine::load / load_from_bytes (src/engine.rs:257-286)
+    @classmethod
+    def load(cls, paths: Iterable[str]) -> "Engine":
+        arr, n = _lines([os.fspath(p) for p in paths])
+        h = C.c_void_p()
+        _check(lib.jb_engine_load(arr, C.c_size_t(n), C.byref(h)))
+        return cls(h)
+
+    @classmethod
+    def load_from_bytes(cls, blobs: Sequence[bytes]) -> "Engine":
+        n = len(blobs)
+        keep = [C.create_string_buffer(bytes(b), len(b)) for b in blobs]
+        ptrs = (C.c_void_p * max(n, 1))(*[C.cast(k, C.c_void_p) for k in keep])
+        lens = (C.c_size_t * max(n, 1))(*[len(b) for b in blobs])
+        h = C.c_void_p()
+        _check(lib.jb_engine_load_from_bytes(ptrs, lens, C.c_size_t(n), C.byref(h)))
+        return cls(h)
+
+    def close(self) -> None:
+        if self._h:
+            lib.jb_engine_free(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- engine.condition (src/engine.rs:32-243)
+    def set(self, key: str, value: float, idx: int = 0) -> None:
+        _check(lib.jb_engine_set_condition(self._h, key.encode(), C.c_size_t(idx), C.c_double(value)))
+
+    def get(self, key: str, idx: int = 0) -> float:
+        v = C.c_double()
+        _check(lib.jb_engine_get_condition(self._h, key.encode(), C.c_size_t(idx), C.byref(v)))
+        return v.value
+
+    def set_interpolation_weight(self, kind: str, stream: int, w: Sequence[float]) -> None:
+        k = {"duration": 0, "parameter": 1, "gv": 2}[kind]
+        arr = (C.c_double * len(w))(*w)
+        _check(lib.jb_engine_set_interpolation_weight(self._h, k, C.c_size_t(stream), arr,
+                                                      C.c_size_t(len(w))))
+
+    def set_devices(self, devices: Sequence[int]) -> None:
+        arr = (C.c_int * len(devices))(*devices)
+        _check(lib.jb_engine_set_devices(self._h, arr, C.c_size_t(len(devices))))
+
+    def set_mlsa_variant(self, v: int) -> None:
+        _check(lib.jb_engine_set_mlsa_variant(self._h, int(v)))
+
+    # -- Engine::synthesize (src/engine.rs:294-296)
+    def synthesize(self, lines: Sequence[str]) -> np.ndarray:
+        arr, n = _lines(lines)
+        out = C.POINTER(C.c_double)()
+        ln = C.c_size_t()
+        _check(lib.jb_engine_synthesize(self._h, arr, C.c_size_t(n), C.byref(out), C.byref(ln)))
+        return _take(out, ln.value)
+
+    def synthesize_batch(self, utts: Sequence[Sequence[str]], timings: Optional[dict] = None):
+        """Returns (samples, out_off): utterance u = samples[out_off[u]:out_off[u+1]]."""
+        arr, offs, n = _flatten(utts)
+        out = C.POINTER(C.c_double)()
+        out_off = (C.c_size_t * (n + 1))()
+        tm = (C.c_double * 16)()
+        _check(lib.jb_engine_synthesize_batch(self._h, arr, offs, C.c_size_t(n), C.byref(out),
+                                              out_off, tm))
+        off = np.array(list(out_off), dtype=np.int64)
+        if timings is not None:
+            timings.update({k: tm[i] for i, k in enumerate(TIMING_KEYS)})
+        return _take(out, int(off[-1])), off
+
+    def synthesize_batch_raw(self, flat):
+        """Timed e2e call for bench.py: pre-flattened (arr, offs, n); returns the library-owned
+        pinned host buffer (release with lib.jb_free) without copying it again."""
+        arr, offs, n = flat
+        out = C.POINTER(C.c_double)()
+        out_off = (C.c_size_t * (n + 1))()
+        tm = (C.c_double * 16)()
+        _check(lib.jb_engine_synthesize_batch(self._h, arr, offs, C.c_size_t(n), C.byref(out),
+                                              out_off, tm))
+        return out, out_off, {k: tm[i] for i, k in enumerate(TIMING_KEYS)}
+
+    # -- parity taps
+    def debug_batch(self, utts: Sequence[Sequence[str]]) -> dict:
+        arr, offs, n = _flatten(utts)
+        P = C.POINTER(C.c_double)
+        mcp, lf0, lpf, pulse, exc = P(), P(), P(), P(), P()
+        foff = (C.c_int64 * (n + 1))()
+        _check(lib.jb_engine_debug_batch(self._h, arr, offs, C.c_size_t(n), C.byref(mcp), C.byref(lf0),
+                                         C.byref(lpf), C.byref(pulse), C.byref(exc), foff))
+        fo = np.array(list(foff), dtype=np.int64)
+        TF = int(fo[-1])
+        fp = int(self.get("fperiod"))
+        return {
+            "frame_off": fo,
+            "mcp": _take(mcp, TF * 35).reshape(TF, 35),
+            "lf0": _take(lf0, TF),
+            "lpf": _take(lpf, TF * 31).reshape(TF, 31),
+            "pulse": _take(pulse, TF * fp),
+            "exc": _take(exc, TF * fp),
+        }
+
+    def noise(self, n: int) -> np.ndarray:
+        out = np.zeros(n, dtype=np.float64)
+        _check(lib.jb_engine_noise(self._h, C.c_size_t(n), out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out
+
+    # -- host front-end taps
+    def durations(self, lines: Sequence[str]) -> np.ndarray:
+        arr, n = _lines(lines)
+        cap = max(n * 16, 16)
+        d = np.zeros(cap, dtype=np.int32)
+        ns = C.c_size_t()
+        _check(lib.jb_engine_durations(self._h, arr, C.c_size_t(n), d.ctypes.data_as(C.POINTER(C.c_int32)),
+                                       C.c_size_t(cap), C.byref(ns)))
+        return d[: ns.value].copy()
+
+    def tree_index(self, voice: int, model: str, stream: int, state_index: int, label: str):
+        m = {"duration": 0, "stream": 1, "gv": 2}[model]
+        t, p = C.c_long(), C.c_long()
+        _check(lib.jb_engine_tree_index(self._h, C.c_size_t(voice), m, C.c_size_t(stream),
+                                        C.c_size_t(state_index), label.encode(), C.byref(t), C.byref(p)))
+        return t.value, p.value
+
+    def stream_parameters(self, lines: Sequence[str], stream: int):
+        arr, n = _lines(lines)
+        cap = max(n, 1) * 16 * 128
+        mean = np.zeros(cap)
+        vari = np.zeros(cap)
+        msd = np.zeros(cap)
+        ns, w = C.c_size_t(), C.c_size_t()
+        D = C.POINTER(C.c_double)
+        _check(lib.jb_engine_stream_parameters(self._h, arr, C.c_size_t(n), C.c_size_t(stream),
+                                               mean.ctypes.data_as(D), vari.ctypes.data_as(D),
+                                               msd.ctypes.data_as(D), C.c_size_t(cap), C.byref(ns), C.byref(w)))
+        S, W = ns.value, w.value
+        return mean[: S * W].reshape(S, W).copy(), vari[: S * W].reshape(S, W).copy(), msd[:S].copy()
+
+    def duration_parameters(self, lines: Sequence[str]):
+        arr, n = _lines(lines)
+        cap = max(n, 1) * 16
+        mean, vari = np.zeros(cap), np.zeros(cap)
+        ns = C.c_size_t()
+        D = C.POINTER(C.c_double)
+        _check(lib.jb_engine_duration_parameters(self._h, arr, C.c_size_t(n), mean.ctypes.data_as(D),
+                                                 vari.ctypes.data_as(D), C.c_size_t(cap), C.byref(ns)))
+        return mean[: ns.value].copy(), vari[: ns.value].copy()
+
+    def gv_parameters(self, lines: Sequence[str], stream: int):
+        arr, n = _lines(lines)
+        cap = max(n * 16, 64)
+        mean, vari = np.zeros(cap), np.zeros(cap)
+        sw = np.zeros(cap, dtype=np.uint8)
+        dim, ns, has = C.c_size_t(), C.c_size_t(), C.c_int()
+        D = C.POINTER(C.c_double)
+        _check(lib.jb_engine_gv_parameters(self._h, arr, C.c_size_t(n), C.c_size_t(stream),
+                                           mean.ctypes.data_as(D), vari.ctypes.data_as(D),
+                                           sw.ctypes.data_as(C.POINTER(C.c_uint8)), C.c_size_t(cap),
+                                           C.byref(dim), C.byref(ns), C.byref(has)))
+        if not has.value:
+            return None
+        return mean[: dim.value].copy(), vari[: dim.value].copy(), sw[: ns.value].astype(bool)
+
+    # -- resident batch (bench "value": inputs already in HBM)
+    def prepare(self, utts: Sequence[Sequence[str]], device_index: int = 0) -> "Resident":
+        arr, offs, n = _flatten(utts)
+        r = C.c_void_p()
+        _check(lib.jb_resident_prepare(self._h, arr, offs, C.c_size_t(n), int(device_index), C.byref(r)))
+        return Resident(self, r, n)
+
+    # -- Engine::generator (src/engine.rs:301-366), batched
+    def generator(self, utts: Sequence[Sequence[str]], device: int = 0) -> "SpeechGenerator":
+        if utts and isinstance(utts[0], str):
+            utts = [utts]  # a single utterance, like the reference's signature
+        arr, offs, n = _flatten(utts)
+        s = C.c_void_p()
+        _check(lib.jb_stream_open(self._h, arr, offs, C.c_size_t(n), int(device), C.byref(s)))
+        return SpeechGenerator(self, s, n)
+
+
+class Resident:
+    def __init__(self, engine: Engine, handle, n_utt: int):
+        self._e, self._h, self.n_utt = engine, handle, n_utt
+
+    def run(self) -> dict:
+        ms = C.c_double()
+        tm = (C.c_double * 16)()
+        _check(lib.jb_resident_run(self._e._h, self._h, C.byref(ms), tm))
+        d = {k: tm[i] for i, k in enumerate(TIMING_KEYS)}
+        d["device_ms"] = ms.value
+        return d
+
+    def fetch(self):
+        out = C.POINTER(C.c_double)()
+        out_off = (C.c_size_t * (self.n_utt + 1))()
+        _check(lib.jb_resident_fetch(self._e._h, self._h, C.byref(out), out_off))
+        off = np.array(list(out_off), dtype=np.int64)
+        return _take(out, int(off[-1])), off
+
+    def close(self):
+        if self._h:
+            lib.jb_resident_free(self._e._h, self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class SpeechGenerator:
+    """``SpeechGenerator`` (src/speech.rs:25-96) for a batch of utterances."""
+
+    def __init__(self, engine: Engine, handle, n_utt: int):
+        self._e, self._h, self.n_utt = engine, handle, n_utt
+
+    def fperiod(self) -> int:
+        return int(lib.jb_stream_fperiod(self._h))
+
+    def synthesized_frames(self) -> int:
+        return int(lib.jb_stream_synthesized_frames(self._h))
+
+    def generate_step(self, n_frames: int = 1, buf: Optional[np.ndarray] = None):
+        """Returns (buf [n_utt, n_frames*fperiod], written [n_utt], device_ms)."""
+        fp = self.fperiod()
+        if buf is None:
+            buf = np.zeros((self.n_utt, n_frames * fp), dtype=np.float64)
+        written = (C.c_size_t * max(self.n_utt, 1))()
+        ms = C.c_double()
+        _check(lib.jb_stream_step(self._h, C.c_size_t(n_frames), buf.ctypes.data_as(C.POINTER(C.c_double)),
+                                  C.c_size_t(buf.size), written, C.byref(ms)))
+        return buf, np.array(list(written)[: self.n_utt], dtype=np.int64), ms.value
+
+    def generate_all(self, n_frames: int = 64) -> List[np.ndarray]:
+        parts: List[List[np.ndarray]] = [[] for _ in range(self.n_utt)]
+        while True:
+            buf, written, _ = self.generate_step(n_frames)
+            if not written.any():
+                break
+            for u in range(self.n_utt):
+                if written[u]:
+                    parts[u].append(buf[u, : written[u]].copy())
+        return [np.concatenate(p) if p else np.zeros(0) for p in parts]
+
+    def close(self):
+        if self._h:
+            lib.jb_stream_close(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,90 @@
+"""Pins the oracle (oracle/, CPU restatement) against every golden the reference's own tests
+hold for the hot path: src/lib.rs:38-160 (seven end-to-end tests, eps 1e-10),
+src/mlpg_adjust/mask.rs:90-159."""
+import numpy as np
+import pytest
+
+from conftest import NITECH, TOHOKU_HAPPY, TOHOKU_NEUTRAL
+from labels import SAMPLE_SENTENCE_1, SAMPLE_SENTENCE_2
+from oracle_lib import Oracle, boundary_distances, noise
+
+EPS = 1.0e-10  # the reference's own epsilon
+
+
+@pytest.fixture(scope="module")
+def nitech():
+    return Oracle([NITECH])
+
+
+@pytest.mark.parametrize("fma", [False, True])
+def test_bonsai(nitech, fma):  # src/lib.rs:39-47 (+ :50, :62 share the numbers)
+    s = nitech.synthesize(SAMPLE_SENTENCE_1, fma)
+    assert len(s) == 66480
+    assert abs(s[2000] - 19.35141137623778) < EPS
+    assert abs(s[30000] - -980.6757547598129) < EPS
+
+
+@pytest.mark.parametrize("fma", [False, True])
+def test_bonsai_multi(fma):  # src/lib.rs:78-91
+    o = Oracle([TOHOKU_NEUTRAL, TOHOKU_HAPPY])
+    o.set_weights("duration", 0, [0.7, 0.3])
+    o.set_weights("parameter", 0, [0.7, 0.3])
+    o.set_weights("parameter", 1, [0.7, 0.3])
+    o.set_weights("parameter", 2, [1.0, 0.0])
+    s = o.synthesize(SAMPLE_SENTENCE_1, fma)
+    assert len(s) == 74880
+    assert abs(s[2000] - 2.3158134981607754e-5) < EPS
+    assert abs(s[30000] - 6459.375032316974) < EPS
+
+
+@pytest.mark.parametrize("fma", [False, True])
+def test_is_this_bonsai(nitech, fma):  # src/lib.rs:123-133
+    s = nitech.synthesize(SAMPLE_SENTENCE_2, fma)
+    assert len(s) == 100800
+    assert abs(s[2000] - 17.15977345625943) < EPS
+    assert abs(s[30000] - 2566.2058730889985) < EPS
+    assert abs(s[70000] - -1898.2890228814217) < EPS
+    assert abs(s[100799] - -13.514971382534956) < EPS
+
+
+@pytest.mark.parametrize("fma", [False, True])
+def test_is_this_bonsai_fast(fma):  # src/lib.rs:136-147
+    o = Oracle([NITECH])
+    o.set("speed", 1.4)
+    s = o.synthesize(SAMPLE_SENTENCE_2, fma)
+    assert len(s) == 72000
+    assert abs(s[2000] - 15.0481014871396) < EPS
+    assert abs(s[30000] - -56.77163803227678) < EPS
+    assert abs(s[70000] - -9.15409432584658) < EPS
+    assert abs(s[71199] - 7.840225089163972) < EPS
+
+
+def test_empty():  # src/lib.rs:150-160
+    o = Oracle([NITECH])
+    assert len(o.synthesize([])) == 0
+    o.set("speed", 1.2)
+    assert len(o.synthesize([])) == 0
+
+
+def test_boundary_distances():  # src/mlpg_adjust/mask.rs:103-159
+    assert boundary_distances([1] * 10) == [(i, 9 - i) for i in range(10)]
+    assert boundary_distances([1, 1, 1, 0, 0, 1, 1, 1, 1, 1]) == [
+        (0, 2), (1, 1), (2, 0), (0, 0), (0, 0), (0, 4), (1, 3), (2, 2), (3, 1), (4, 0)]
+    assert boundary_distances([1, 1, 1, 0, 1, 0, 0, 0, 0, 0]) == [
+        (0, 2), (1, 1), (2, 0), (0, 0), (0, 0), (0, 0), (0, 0), (0, 0), (0, 0), (0, 0)]
+    assert boundary_distances([]) == []
+
+
+def test_noise_sequence_properties():  # src/vocoder/excitation.rs:178-237
+    n = noise(1 << 16)
+    assert np.isfinite(n).all()
+    assert abs(n.mean()) < 0.02 and abs(n.std() - 1.0) < 0.02
+    # deterministic, seed 1: identical prefix on a second draw
+    assert np.array_equal(n[:1000], noise(1000))
+
+
+def test_batch_equals_single(nitech):
+    w, off = nitech.synthesize_batch([SAMPLE_SENTENCE_1, [], SAMPLE_SENTENCE_2], nthreads=2)
+    assert list(off) == [0, 66480, 66480, 66480 + 100800]
+    assert np.array_equal(w[:66480], nitech.synthesize(SAMPLE_SENTENCE_1))
+    assert np.array_equal(w[66480:], nitech.synthesize(SAMPLE_SENTENCE_2))
