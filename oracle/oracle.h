@@ -67,6 +67,8 @@ struct Vocoder {
 
   // optional taps for tests: per-sample excitation before gain (ring-buffer output)
   std::vector<double>* excitation_tap = nullptr;
+  std::vector<double>* pulse_tap = nullptr;   // pulse amplitude (0 when none) per sample
+  std::vector<double>* gained_tap = nullptr;  // excitation * exp(c[0]): the MLSA filter input
 
   size_t nmcp, nlpf, rate, fperiod;
   double alpha, beta, volume;

@@ -60,7 +60,8 @@ void run_mlpg(const OrcEngine& e, const jb::UtterancePack& pack, std::vector<std
 }
 
 std::vector<double> synth(const OrcEngine& e, const std::vector<std::string>& lines, bool fma,
-                          std::vector<double>* exc_tap = nullptr) {
+                          std::vector<double>* exc_tap = nullptr, std::vector<double>* pulse_tap = nullptr,
+                          std::vector<double>* gained_tap = nullptr) {
   jb::UtterancePack pack = jb::build_utterance(e.voices, e.condition, lines);
   std::vector<std::vector<double>> pars;
   size_t T = 0;
@@ -70,6 +71,8 @@ std::vector<double> synth(const OrcEngine& e, const std::vector<std::string>& li
                     e.condition.sampling_frequency, e.condition.alpha, e.condition.beta,
                     e.condition.volume, e.condition.fperiod, fma);
   v.excitation_tap = exc_tap;
+  v.pulse_tap = pulse_tap;
+  v.gained_tap = gained_tap;
   std::vector<double> nolpf;
   return oracle::generate_all(&v, T, pars[0].data(), pars[1].data(),
                               nlpf ? pars[2].data() : nolpf.data());
@@ -140,16 +143,18 @@ int orc_synthesize(void* h, const char* const* lines, size_t n, int fma, double*
   }
 }
 
-// Waveform plus the pre-gain excitation sequence (pulse positions / noise indexing checks).
+// Waveform plus the pre-gain excitation, the pulse train and the gained excitation (MLSA input).
 int orc_synthesize_tap(void* h, const char* const* lines, size_t n, int fma, double** out,
-                       double** exc, size_t* len) {
+                       double** exc, double** pulse, double** gained, size_t* len) {
   try {
     std::vector<std::string> l(lines, lines + n);
-    std::vector<double> tap;
-    std::vector<double> w = synth(*(OrcEngine*)h, l, fma != 0, &tap);
+    std::vector<double> tap, ptap, gtap;
+    std::vector<double> w = synth(*(OrcEngine*)h, l, fma != 0, &tap, &ptap, &gtap);
     *len = w.size();
     *out = dup(w);
     *exc = dup(tap);
+    *pulse = dup(ptap);
+    *gained = dup(gtap);
     return 0;
   } catch (const std::exception& e) {
     return fail(e);

@@ -204,6 +204,7 @@ void Vocoder::synthesize(double lf0, const double* spectrum, const double* lpf, 
   for (size_t i = 0; i < fperiod; ++i) {
     // Excitation::get (excitation.rs:67-100)
     double x;
+    double tap_pulse = 0.0;
     if (nlpf > 0) {
       double noise = random.nrandom();
       size_t anti = (ring_index + (nlpf - 1) / 2) % nlpf;
@@ -216,6 +217,7 @@ void Vocoder::synthesize(double lf0, const double* spectrum, const double* lpf, 
           pitch_counter -= pitch_of_curr_point;
           pulse = std::sqrt(pitch_of_curr_point);
         }
+        tap_pulse = pulse;
         // voiced_frame (excitation.rs:48-64)
         ring[anti] += noise;
         double c = pulse - noise;
@@ -235,6 +237,7 @@ void Vocoder::synthesize(double lf0, const double* spectrum, const double* lpf, 
       if (pitch_counter >= pitch_of_curr_point) {
         pitch_counter -= pitch_of_curr_point;
         x = std::sqrt(pitch_of_curr_point);
+        tap_pulse = x;
       } else {
         x = 0.0;
       }
@@ -242,7 +245,10 @@ void Vocoder::synthesize(double lf0, const double* spectrum, const double* lpf, 
     }
     if (excitation_tap) excitation_tap->push_back(x);
 
+    if (pulse_tap) pulse_tap->push_back(tap_pulse);
+
     if (x != 0.0) x *= std::exp(coefficients[0]);  // mod.rs:129-131
+    if (gained_tap) gained_tap->push_back(x);
 
     // df1 (mlsa.rs:54-66)
     {

@@ -55,9 +55,11 @@ class Oracle:
 
     def synthesize_tap(self, lines, fma=False):
         arr, n = _lines(lines)
-        out, exc, ln = D(), D(), C.c_size_t()
-        _ck(_L.orc_synthesize_tap(self.h, arr, C.c_size_t(n), int(fma), C.byref(out), C.byref(exc), C.byref(ln)))
-        return _take(out, ln.value), _take(exc, ln.value)
+        out, exc, pulse, gained, ln = D(), D(), D(), D(), C.c_size_t()
+        _ck(_L.orc_synthesize_tap(self.h, arr, C.c_size_t(n), int(fma), C.byref(out), C.byref(exc),
+                                  C.byref(pulse), C.byref(gained), C.byref(ln)))
+        return {"wave": _take(out, ln.value), "exc": _take(exc, ln.value),
+                "pulse": _take(pulse, ln.value), "gained": _take(gained, ln.value)}
 
     def parameters(self, lines):
         arr, n = _lines(lines)
