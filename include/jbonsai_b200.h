@@ -41,6 +41,10 @@ const char* jb_last_error(void);
 const char* jb_version(void);
 int jb_device_count(void); /* number of usable CUDA devices, 0 if none */
 
+/* Roofline denominators measured live on `device` (no reference equivalent; bench.py): FP64 FMA
+ * rate of a DFMA micro-kernel in TFLOP/s and read+write bandwidth of a plain copy in GB/s. */
+int jb_device_measure_peaks(int device, double* fp64_fma_tflops, double* hbm_copy_gbs);
+
 /* Engine::load (src/engine.rs:257) / Engine::load_from_bytes (src/engine.rs:263). */
 int jb_engine_load(const char* const* paths, size_t n_paths, jb_engine** out);
 int jb_engine_load_from_bytes(const uint8_t* const* bufs, const size_t* lens, size_t n,

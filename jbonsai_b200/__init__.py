@@ -20,7 +20,7 @@ LIB_PATH = os.path.join(_HERE, "libjbonsai_b200.so")
 
 # every symbol include/jbonsai_b200.h declares (checked by tests/test_capi_symbols.py)
 C_ABI_SYMBOLS = [
-    "jb_last_error", "jb_version", "jb_device_count", "jb_engine_load",
+    "jb_last_error", "jb_version", "jb_device_count", "jb_device_measure_peaks", "jb_engine_load",
     "jb_engine_load_from_bytes", "jb_engine_free", "jb_engine_set_condition",
     "jb_engine_get_condition", "jb_engine_set_interpolation_weight", "jb_engine_set_devices",
     "jb_engine_set_mlsa_variant", "jb_engine_synthesize", "jb_engine_synthesize_batch", "jb_free",
@@ -85,6 +85,13 @@ def version() -> str:
 
 def device_count() -> int:
     return int(lib.jb_device_count())
+
+
+def measure_peaks(device: int = 0):
+    """(FP64 FMA TFLOP/s, HBM copy GB/s) measured live on `device`."""
+    t, g = C.c_double(), C.c_double()
+    _check(lib.jb_device_measure_peaks(int(device), C.byref(t), C.byref(g)))
+    return t.value, g.value
 
 
 def _lines(lines: Sequence[str]):
@@ -380,3 +387,5 @@ class SpeechGenerator:
             self.close()
         except Exception:
             pass
+
+from . import workload  # noqa: E402,F401  (synthetic label batches for bench/tests)

@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 
 #include "../../include/jbonsai_b200.h"
+#include "cuda/kernels.h"
 #include "engine.h"
 
 struct jb_engine {
@@ -72,6 +73,14 @@ int jb_device_count(void) {
     return 0;
   }
   return n;
+}
+
+int jb_device_measure_peaks(int device, double* fp64_fma_tflops, double* hbm_copy_gbs) {
+  JB_TRY
+  cudaError_t e = cudaSetDevice(device);
+  if (e == cudaSuccess) e = (cudaError_t)jbk::measure_peaks(fp64_fma_tflops, hbm_copy_gbs);
+  if (e != cudaSuccess) throw jb::Error(jb::kErrCuda, std::string("CUDA error: ") + cudaGetErrorString(e));
+  JB_CATCH
 }
 
 int jb_engine_load(const char* const* paths, size_t n, jb_engine** out) {

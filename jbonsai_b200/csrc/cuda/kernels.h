@@ -120,4 +120,7 @@ int launch_mlsa(const BatchLayout& b, const VocoderParams& p, const VocoderDev& 
 int launch_gather_chunk(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,
                         double* chunk, cudaStream_t stream);
 
+// Roofline denominators measured on the current device (peaks.cu); not on the synthesis path.
+int measure_peaks(double* fp64_fma_tflops, double* hbm_copy_gbs);
+
 }  // namespace jbk
