@@ -35,6 +35,7 @@ struct BatchLayout {
   const int64_t* frame_off;  // [n_utt+1]
   const int32_t* durations;  // [total_states]
   int32_t* frame_state;      // [total_frames]  (out of expand) state index within the utterance
+  const int32_t* order;      // [n_utt] utterances by decreasing length (block scheduling order) or null
 };
 
 // Per stream state-level input (A0 contract) + MLPG work arrays.
@@ -111,7 +112,7 @@ int launch_frame_prep(const BatchLayout& b, const VocoderParams& p, const Vocode
 int launch_pulse(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, cudaStream_t stream);
 int launch_excitation(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,
                       int64_t total_frames, cudaStream_t stream);
-// variant: 0 = bit-faithful stage-per-lane kernel (v1)
+// variant: 0 = reference operation order, stage-per-lane; 1 (default, -1) = blocked-scan warp kernel
 int launch_mlsa(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, int variant,
                 cudaStream_t stream);
 

@@ -345,6 +345,224 @@ __global__ void __launch_bounds__(32 * WPB) k_mlsa_v0(BatchLayout b, VocoderPara
   }
 }
 
+// ---------------------------------------------------------------- MLSA, variant 1 (default)
+// One warp per utterance; lane = 6*s + b owns taps 6b+1 .. 6b+6 of the warped delay line of Pade
+// stage s+1 (s = 0..4, b = 0..5; taps 35/36 and lanes 30/31 are padding with zero coefficients).
+//
+// Same filter as mlsa.rs:48-163, re-associated for parallelism (waveform parity is the north-star
+// tolerance 1e-6 abs, checked in tests; variant 0 above keeps the reference's operation order):
+//   * all-pass chain in "q form":  t'_j = (t_{j-1} + a t_j) - a t'_{j-1}   (== iaa*rem_j + a*t_j of
+//     mlsa.rs:141-153), so the tap recurrence is a first-order scan over j with ratio -a;
+//   * blocked scan: every lane scans its 6 taps with zero carry-in (z), the block aggregates E are
+//     exchanged through shared memory, the true carry K_b = sum_{m<b} (-a)^(6(b-1-m)) E_m + kappa_b u
+//     is formed per lane and folded back with one FMA per tap: t'_i = z_i + (-a)^(i+1) K_b;
+//   * df1/df2 sign pattern (x += v for odd i, x -= v for even i, then x += sum v):
+//     g0 = (x + A) - B, x' = x + 2A with A = odd-stage sum, B = even-stage sum.
+// Cross-lane traffic goes through double-buffered shared memory (SHFL.64 costs 8 issue cycles per
+// SMSP on B200, an LDS.128 broadcast one wavefront).
+template <int NM>
+__global__ void __launch_bounds__(32) k_mlsa_v1(BatchLayout b, VocoderParams p, VocoderDev d) {
+  constexpr int CH = 16;  // samples per staged chunk
+  __shared__ __align__(16) double sE[2][40];
+  __shared__ __align__(16) double sYP[2][40];
+  __shared__ __align__(16) double sV[2][16];  // [0..5) y_k (df2 stage outputs), [8..13) f_k (df1 sections)
+  __shared__ __align__(16) double sIn[2][CH];
+  __shared__ __align__(16) double sOut[CH];
+
+  const int lane = threadIdx.x;
+  const int u = b.order ? b.order[blockIdx.x] : (int)blockIdx.x;
+  const int64_t foff = b.frame_off[u];
+  const int T = (int)(b.frame_off[u + 1] - foff);
+  int f0 = d.frame_begin, f1 = f0 + d.frame_count;
+  if (f1 > T || f1 < f0) f1 = T;
+  if (f0 >= f1) return;
+
+  const int s = lane / 6, bb = lane - 6 * s;  // s == 5: padding lanes
+  const bool real = s < 5;
+  const int gbase = 6 * s;
+  const double a = p.alpha, ma = -a, iaa = 1.0 - a * a;
+  double P[6], W[5];
+  {
+    double pw = ma;  // (-a)^(i+1)
+#pragma unroll
+    for (int i = 0; i < 6; ++i) { P[i] = pw; pw *= ma; }
+    const double A6 = P[5];  // (-a)^6
+#pragma unroll
+    for (int m = 0; m < 5; ++m) {
+      double w = 0.0;
+      if (m < bb) { w = 1.0; for (int e = 0; e < bb - 1 - m; ++e) w *= A6; }
+      W[m] = w;
+    }
+  }
+  double kap;  // coefficient of the stage input u in K_b
+  {
+    double pw = 1.0;
+    for (int e = 0; e < 6 * bb; ++e) pw *= ma;  // (-a)^(6b)
+    kap = iaa * pw / ma;                         // iaa * (-a)^(6b-1); b = 0: -iaa/a
+  }
+  const double pp1 = c_ppade[1], pp2 = c_ppade[2], pp3 = c_ppade[3], pp4 = c_ppade[4], pp5 = c_ppade[5];
+  const double fper = (double)p.fperiod;
+
+  for (int i = lane; i < 2 * 40; i += 32) { (&sE[0][0])[i] = 0.0; (&sYP[0][0])[i] = 0.0; }
+  if (lane < 32) { (&sV[0][0])[lane] = 0.0; }
+  __syncwarp();
+
+  // ---- state
+  double t[6] = {0, 0, 0, 0, 0, 0}, tm1 = 0.0, c[6] = {0, 0, 0, 0, 0, 0}, c1 = 0.0;
+  double d11 = 0.0, gin = 0.0, uin = 0.0;
+  int jtap[6];
+  bool cvalid[6];
+#pragma unroll
+  for (int i = 0; i < 6; ++i) {
+    jtap[i] = 6 * bb + 1 + i;
+    cvalid[i] = real && jtap[i] >= 2 && jtap[i] < NM;
+  }
+  double* stp = d.state ? d.state + (int64_t)u * kVocStateDoubles : nullptr;
+  const bool resume = stp != nullptr && f0 > 0;
+  if (resume && real) {
+#pragma unroll
+    for (int i = 0; i < 6; ++i) {
+      t[i] = jtap[i] < NM ? stp[s * (NM - 1) + jtap[i] - 1] : 0.0;
+      c[i] = cvalid[i] ? stp[188 + jtap[i]] : 0.0;
+    }
+    tm1 = bb > 0 ? stp[s * (NM - 1) + 6 * bb - 1] : 0.0;
+    c1 = stp[188 + 1];
+    d11 = stp[170 + s + 1];
+    gin = stp[176 + s];  // d12[s]: input of section s+1
+    uin = stp[182 + s];  // d22[s]: input of stage s+1
+  }
+
+  const double* bsrc = d.b + foff * NM;
+  double* wv = d.wave + (foff + f0) * (int64_t)p.fperiod;
+  const int nsamp = (f1 - f0) * p.fperiod;  // multiple of fperiod; fperiod % CH == 0 is checked by the launcher
+  // stage the first chunk
+  if (lane < CH) sIn[0][lane] = wv[lane];
+  __syncwarp();
+
+  int ib = 0;  // chunk buffer
+  int pb = 0;  // exchange buffer parity
+  double cinc[6] = {0, 0, 0, 0, 0, 0}, cc[6] = {0, 0, 0, 0, 0, 0}, c1inc = 0.0, cc1 = 0.0;
+  int left_in_frame = 0, f = f0;
+  for (int i0 = 0; i0 < nsamp; i0 += CH) {
+    if (left_in_frame == 0) {  // frame prologue (mod.rs:116-125)
+      const double* bf = bsrc + (int64_t)f * NM;
+#pragma unroll
+      for (int i = 0; i < 6; ++i) cc[i] = cvalid[i] ? bf[jtap[i]] : 0.0;
+      cc1 = bf[1];
+      if (f == 0) {  // is_first: coefficients = mc2b(first frame)
+#pragma unroll
+        for (int i = 0; i < 6; ++i) c[i] = cc[i];
+        c1 = cc1;
+      }
+#pragma unroll
+      for (int i = 0; i < 6; ++i) cinc[i] = (cc[i] - c[i]) / fper;
+      c1inc = (cc1 - c1) / fper;
+      left_in_frame = p.fperiod;
+    }
+    // prefetch the next chunk while this one is filtered
+    double xnext = 0.0;
+    if (lane < CH && i0 + CH < nsamp) xnext = wv[i0 + CH + lane];
+
+#pragma unroll 1
+    for (int j = 0; j < CH; ++j) {
+      const double e = sIn[ib][j];
+      // df1 section s+1 (mlsa.rs:54-66)
+      d11 = __fma_rn(a, d11, iaa * gin);
+      const double fk = d11 * c1;
+      // all-pass chain, zero carry-in
+      const double q0 = __fma_rn(a, t[0], tm1), q1 = __fma_rn(a, t[1], t[0]), q2 = __fma_rn(a, t[2], t[1]),
+                   q3 = __fma_rn(a, t[3], t[2]), q4 = __fma_rn(a, t[4], t[3]), q5 = __fma_rn(a, t[5], t[4]);
+      const double z0 = q0, z1 = __fma_rn(ma, z0, q1), z2 = __fma_rn(ma, z1, q2), z3 = __fma_rn(ma, z2, q3),
+                   z4 = __fma_rn(ma, z3, q4), z5 = __fma_rn(ma, z4, q5);
+      sE[pb][lane] = z5;
+      if (bb == 0 && real) sV[pb][8 + s] = fk;
+      __syncwarp();
+      const double2 e01 = *reinterpret_cast<const double2*>(&sE[pb][gbase]);
+      const double2 e23 = *reinterpret_cast<const double2*>(&sE[pb][gbase + 2]);
+      const double e4 = sE[pb][gbase + 4];
+      const double ka = __fma_rn(W[4], e4, __fma_rn(W[2], e23.x, W[0] * e01.x));
+      const double kb = __fma_rn(W[3], e23.y, W[1] * e01.y);
+      const double K = __fma_rn(kap, uin, ka + kb);
+      t[0] = __fma_rn(P[0], K, z0);
+      t[1] = __fma_rn(P[1], K, z1);
+      t[2] = __fma_rn(P[2], K, z2);
+      t[3] = __fma_rn(P[3], K, z3);
+      t[4] = __fma_rn(P[4], K, z4);
+      t[5] = __fma_rn(P[5], K, z5);
+      tm1 = bb > 0 ? K : 0.0;
+      const double ya = __fma_rn(c[4], t[4], __fma_rn(c[2], t[2], c[0] * t[0]));
+      const double yb = __fma_rn(c[5], t[5], __fma_rn(c[3], t[3], c[1] * t[1]));
+      sYP[pb][lane] = ya + yb;
+      // df1 combine (independent of the fir)
+      const double2 f12 = *reinterpret_cast<const double2*>(&sV[pb][8]);
+      const double2 f34 = *reinterpret_cast<const double2*>(&sV[pb][10]);
+      const double f5 = sV[pb][12];
+      const double Af = __fma_rn(pp5, f5, __fma_rn(pp3, f34.x, pp1 * f12.x));
+      const double Bf = __fma_rn(pp4, f34.y, pp2 * f12.y);
+      const double g0 = (e + Af) - Bf;
+      const double x1 = __fma_rn(2.0, Af, e);
+#pragma unroll
+      for (int i = 0; i < 6; ++i) c[i] += cinc[i];  // mod.rs:133-135
+      c1 += c1inc;
+      __syncwarp();
+      const double2 r01 = *reinterpret_cast<const double2*>(&sYP[pb][gbase]);
+      const double2 r23 = *reinterpret_cast<const double2*>(&sYP[pb][gbase + 2]);
+      const double2 r45 = *reinterpret_cast<const double2*>(&sYP[pb][gbase + 4]);
+      const double y = ((r01.x + r01.y) + (r23.x + r23.y)) + (r45.x + r45.y);
+      if (bb == 0 && real) sV[pb][s] = y;
+      __syncwarp();
+      const double2 y12 = *reinterpret_cast<const double2*>(&sV[pb][0]);
+      const double2 y34 = *reinterpret_cast<const double2*>(&sV[pb][2]);
+      const double y5 = sV[pb][4];
+      const double Ay = __fma_rn(pp5, y5, __fma_rn(pp3, y34.x, pp1 * y12.x));
+      const double By = __fma_rn(pp4, y34.y, pp2 * y12.y);
+      const double h0 = (x1 + Ay) - By;
+      const double out = __fma_rn(2.0, Ay, x1);
+      // inputs of the next sample: stage s+1 reads d22[s], section s+1 reads d12[s]
+      uin = s == 0 ? h0 : sV[pb][s > 0 ? s - 1 : 0];
+      gin = s == 0 ? g0 : sV[pb][8 + (s > 0 ? s - 1 : 0)];
+      if (lane == 0) sOut[j] = out * p.volume;
+      pb ^= 1;
+    }
+    __syncwarp();
+    if (lane < CH) {
+      wv[i0 + lane] = sOut[lane];
+      sIn[ib ^ 1][lane] = xnext;
+    }
+    __syncwarp();
+    ib ^= 1;
+    left_in_frame -= CH;
+    if (left_in_frame == 0) {  // *coefficients = cc (mod.rs:140)
+#pragma unroll
+      for (int i = 0; i < 6; ++i) c[i] = cc[i];
+      c1 = cc1;
+      ++f;
+    }
+  }
+
+  if (stp) {  // streaming state, same layout as variant 0
+    if (real) {
+#pragma unroll
+      for (int i = 0; i < 6; ++i)
+        if (jtap[i] < NM) {
+          stp[s * (NM - 1) + jtap[i] - 1] = t[i];
+          if (s == 0 && cvalid[i]) stp[188 + jtap[i]] = c[i];
+        }
+      if (bb == 0) {
+        stp[170 + s + 1] = d11;
+        stp[176 + s] = gin;
+        stp[182 + s] = uin;
+      }
+    }
+    if (lane == 0) {
+      stp[188 + 1] = c1;
+      stp[176 + 5] = sV[pb ^ 1][8 + 4];  // d12[5], d22[5] (not inputs of any stage; kept for layout parity)
+      stp[182 + 5] = sV[pb ^ 1][4];
+      stp[188] = bsrc[(int64_t)(f1 - 1) * NM];  // coefficients[0] = cc[0] at a frame end
+    }
+  }
+}
+
 __global__ void k_gather_chunk(BatchLayout b, VocoderParams p, VocoderDev d, double* chunk) {
   const int u = blockIdx.y;
   const int64_t foff = b.frame_off[u];
@@ -395,7 +613,12 @@ int launch_mlsa(const BatchLayout& b, const VocoderParams& p, const VocoderDev& 
                 cudaStream_t stream) {
   if (b.n_utt == 0) return 0;
   if (p.nmcp != 35) return (int)cudaErrorInvalidValue;  // delay lines are register arrays
-  (void)variant;
+  // variant 1 (default): blocked-scan kernel; needs alpha != 0 (kappa_0 = -iaa/alpha) and 16 | fperiod
+  const bool v1_ok = p.alpha > 1e-3 && p.fperiod % 16 == 0;
+  if ((variant < 0 || variant == 1) && v1_ok) {
+    k_mlsa_v1<35><<<b.n_utt, 32, 0, stream>>>(b, p, d);
+    return (int)cudaGetLastError();
+  }
   constexpr int G = 8, WPB = 1;
   const int upb = (32 / G) * WPB;
   k_mlsa_v0<G, 35, WPB><<<(b.n_utt + upb - 1) / upb, 32 * WPB, 0, stream>>>(b, p, d);
