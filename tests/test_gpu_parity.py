@@ -214,3 +214,26 @@ def test_multi_gpu_sharding_matches_single(eng):
     e2.set_devices(list(range(jb.device_count())))
     w2, off2 = e2.synthesize_batch(utts)
     assert list(off) == list(off2) and np.array_equal(w, w2)
+
+
+@pytest.mark.parametrize("variant", [0, 1])
+def test_mlsa_variants_vs_oracle(variant, orc):
+    # variant 0 keeps the reference's operation order; variant 1 (default) is the blocked-scan kernel
+    e = jb.Engine.load([NITECH])
+    e.set_mlsa_variant(variant)
+    w = e.synthesize(SAMPLE_SENTENCE_2)
+    ow = orc.synthesize(SAMPLE_SENTENCE_2, fma=True)
+    err = np.abs(w - ow).max()
+    assert err <= (1e-9 if variant == 0 else WAVE_ATOL), err
+    g = e.generator([SAMPLE_SENTENCE_2])
+    parts = g.generate_all(7)
+    assert np.array_equal(parts[0], w)
+
+
+def test_small_alpha_falls_back_to_reference_order():
+    e, o = jb.Engine.load([NITECH]), Oracle([NITECH])
+    e.set("alpha", 0.0)
+    o.set("alpha", 0.0)
+    w = e.synthesize(SAMPLE_SENTENCE_1)
+    ow = o.synthesize(SAMPLE_SENTENCE_1, fma=True)
+    assert np.abs(w - ow).max() <= WAVE_ATOL
