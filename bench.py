@@ -113,15 +113,17 @@ class ClockSampler:
 
 def build_workload(args, rank):
     from jbonsai_b200 import workload as wl
+    import jbonsai_b200 as jb
     seed = wl.SEED_NITECH if args.voice == "nitech" else wl.SEED_TOHOKU
-    utts = wl.synthetic_batch(args.utts, seed, first=rank * args.utts)
+    eng = jb.Engine.load([wl.VOICES[args.voice]])  # host front-end only: label durations
+    utts = wl.timed_batch(eng, args.utts, seed, first=rank * args.utts)
     return wl.VOICES[args.voice], utts
 
 
 def config_dict(args, world):
     return {
-        "workload": f"BASELINE config 3: batch of {args.utts} synthetic label sequences (~5 s each, "
-                    f"genji.lab slices) per GPU, voice {args.voice}, 48 kHz, fperiod 240",
+        "workload": f"BASELINE config 3: batch of {args.utts} synthetic label sequences (~5 s each: 4-6 s "
+                    f"genji.lab slices between sil labels) per GPU, voice {args.voice}, 48 kHz, fperiod 240",
         "utterances_per_gpu": args.utts, "voice": args.voice, "n_gpus": world,
         "parallelism": f"utterance-sharded x{world}, no collective",
         "l2": "inputs and work arrays (> 4 GB per step) are far larger than the 126 MB L2",

@@ -8,13 +8,18 @@
 #include "cuda/kernels.h"
 #include "engine.h"
 
+// Streams and resident batches keep their engine alive (handles may be released in any order).
 struct jb_engine {
-  std::unique_ptr<jb::Engine> e;
+  std::shared_ptr<jb::Engine> e;
 };
 struct jb_stream {
+  std::shared_ptr<jb::Engine> e;
   std::unique_ptr<jb::Stream> s;
 };
-struct jb_resident;  // opaque alias of jb::Engine::Resident
+struct jb_resident {
+  std::shared_ptr<jb::Engine> e;
+  jb::Engine::Resident* r;
+};
 
 namespace {
 
@@ -86,7 +91,7 @@ int jb_device_measure_peaks(int device, double* fp64_fma_tflops, double* hbm_cop
 int jb_engine_load(const char* const* paths, size_t n, jb_engine** out) {
   JB_TRY
   std::vector<std::string> p(paths, paths + n);
-  *out = new jb_engine{jb::Engine::load(p)};
+  *out = new jb_engine{std::shared_ptr<jb::Engine>(jb::Engine::load(p))};
   JB_CATCH
 }
 
@@ -94,7 +99,7 @@ int jb_engine_load_from_bytes(const uint8_t* const* bufs, const size_t* lens, si
   JB_TRY
   std::vector<std::vector<uint8_t>> b(n);
   for (size_t i = 0; i < n; ++i) b[i].assign(bufs[i], bufs[i] + lens[i]);
-  *out = new jb_engine{jb::Engine::load_from_bytes(b)};
+  *out = new jb_engine{std::shared_ptr<jb::Engine>(jb::Engine::load_from_bytes(b))};
   JB_CATCH
 }
 
@@ -282,14 +287,14 @@ int jb_engine_gv_parameters(const jb_engine* e, const char* const* lines, size_t
 int jb_resident_prepare(const jb_engine* e, const char* const* lines, const size_t* line_off,
                         size_t n_utt, int device_index, jb_resident** out) {
   JB_TRY
-  *out = (jb_resident*)e->e->prepare(to_utts(lines, line_off, n_utt), device_index);
+  *out = new jb_resident{e->e, e->e->prepare(to_utts(lines, line_off, n_utt), device_index)};
   JB_CATCH
 }
 
 int jb_resident_run(const jb_engine* e, jb_resident* r, double* device_ms, double* timings) {
   JB_TRY
   jb::BatchTimings tm;
-  double ms = e->e->run_resident((jb::Engine::Resident*)r, &tm);
+  double ms = r->e->run_resident(r->r, &tm);
   if (device_ms) *device_ms = ms;
   fill_timings(tm, timings);
   JB_CATCH
@@ -298,23 +303,25 @@ int jb_resident_run(const jb_engine* e, jb_resident* r, double* device_ms, doubl
 int jb_resident_fetch(const jb_engine* e, jb_resident* r, double** out, size_t* out_off) {
   JB_TRY
   std::vector<size_t> off;
-  e->e->fetch_resident((jb::Engine::Resident*)r, out, &off);
+  r->e->fetch_resident(r->r, out, &off);
   memcpy(out_off, off.data(), off.size() * sizeof(size_t));
   JB_CATCH
 }
 
 void jb_resident_free(const jb_engine* e, jb_resident* r) {
+  if (!r) return;
   try {
-    e->e->release((jb::Engine::Resident*)r);
+    r->e->release(r->r);
   } catch (...) {
   }
+  delete r;
 }
 
 int jb_stream_open(const jb_engine* e, const char* const* lines, const size_t* line_off,
                    size_t n_utt, int device, jb_stream** out) {
   JB_TRY
-  *out = new jb_stream{std::unique_ptr<jb::Stream>(
-      new jb::Stream(e->e.get(), to_utts(lines, line_off, n_utt), device))};
+  *out = new jb_stream{e->e, std::unique_ptr<jb::Stream>(
+                                new jb::Stream(e->e.get(), to_utts(lines, line_off, n_utt), device))};
   JB_CATCH
 }
 

@@ -91,7 +91,9 @@ struct VocoderParams {
 //   [170..176) d11, [176..182) d12, [182..188) d22   (mlsa.rs:5-10)
 //   [188..223) coefficients[35]                      (vocoder/mod.rs Stage::Zero)
 //   [223] pitch_of_curr_point [224] pitch_counter    (excitation.rs:2-10)
-constexpr int kVocStateDoubles = 232;
+//   [226..251) variant 1 only: carry-in of tap block b = 1..5 of stage s at [226 + 5 s + b - 1]
+//              (== d21[s][6b-1] up to rounding; kept so that chunked == whole-utterance bit for bit)
+constexpr int kVocStateDoubles = 256;
 
 struct VocoderDev {
   const double* mcp;    // [total_frames][nmcp] MLPG output

@@ -425,7 +425,7 @@ __global__ void __launch_bounds__(32) k_mlsa_v1(BatchLayout b, VocoderParams p, 
       t[i] = jtap[i] < NM ? stp[s * (NM - 1) + jtap[i] - 1] : 0.0;
       c[i] = cvalid[i] ? stp[188 + jtap[i]] : 0.0;
     }
-    tm1 = bb > 0 ? stp[s * (NM - 1) + 6 * bb - 1] : 0.0;
+    tm1 = bb > 0 ? stp[226 + 5 * s + bb - 1] : 0.0;
     c1 = stp[188 + 1];
     d11 = stp[170 + s + 1];
     gin = stp[176 + s];  // d12[s]: input of section s+1
@@ -548,6 +548,7 @@ __global__ void __launch_bounds__(32) k_mlsa_v1(BatchLayout b, VocoderParams p, 
           stp[s * (NM - 1) + jtap[i] - 1] = t[i];
           if (s == 0 && cvalid[i]) stp[188 + jtap[i]] = c[i];
         }
+      if (bb > 0) stp[226 + 5 * s + bb - 1] = tm1;
       if (bb == 0) {
         stp[170 + s + 1] = d11;
         stp[176 + s] = gin;

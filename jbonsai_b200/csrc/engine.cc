@@ -324,6 +324,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   Carver in;
   const size_t o_soff = in.take((n_utt + 1) * 8), o_foff = in.take((n_utt + 1) * 8);
   const size_t o_dur = in.take((size_t)TS * 4);
+  const size_t o_order = in.take(n_utt * 4);
   size_t o_mean[3], o_vari[3], o_msd[3], o_gvm[3], o_gvv[3], o_gsw[3];
   int dim[3], nwin[3], is_msd[3], has_gv[3];
   for (size_t s = 0; s < nstream; ++s) {
@@ -348,6 +349,13 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   } rel{h};
   memcpy(h + o_soff, state_off.data(), (n_utt + 1) * 8);
   memcpy(h + o_foff, r->frame_off.data(), (n_utt + 1) * 8);
+  {  // longest utterance first: the per-utterance kernels are scheduled block by block in this order
+    std::vector<int32_t> order(n_utt);
+    for (size_t u = 0; u < n_utt; ++u) order[u] = (int32_t)u;
+    std::stable_sort(order.begin(), order.end(),
+                     [&](int32_t x, int32_t y) { return packs[x].nframes > packs[y].nframes; });
+    if (n_utt) memcpy(h + o_order, order.data(), n_utt * 4);
+  }
   int64_t voiced_frames = 0;
   for (size_t u = 0; u < n_utt; ++u) {
     const UtterancePack& p = packs[u];
@@ -420,6 +428,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   r->layout.frame_off = (const int64_t*)(di + o_foff);
   r->layout.durations = (const int32_t*)(di + o_dur);
   r->layout.frame_state = (int32_t*)(dw + w_fstate);
+  r->layout.order = (const int32_t*)(di + o_order);
   r->streams.n = (int)nstream;
   for (size_t s = 0; s < nstream; ++s) {
     jbk::StreamDev& sd = r->streams.s[s];

@@ -63,3 +63,35 @@ def synthetic_utterance(genji: List[str], seed: int, lmin: int = 30, lmax: int =
 def synthetic_batch(n_utt: int, seed_base: int, first: int = 0, lmin: int = 30, lmax: int = 50):
     g = genji_labels()
     return [synthetic_utterance(g, seed_base + first + u, lmin, lmax) for u in range(n_utt)]
+
+
+def label_frames(engine, labels: List[str]) -> List[int]:
+    """Frames each label contributes at speed 1.0 (state durations are per label then:
+    src/duration.rs:68-73 with rho = 0), from the host front-end of `engine`."""
+    return [int(engine.durations([l]).sum()) for l in labels]
+
+
+def timed_batch(engine, n_utt: int, seed_base: int, first: int = 0, lo: int = 800, hi: int = 1200):
+    """BASELINE "~5 s each": utterance u (seed base + u) = sil, a contiguous slice of genji.lab
+    starting at a uniform random offset and extended label by label until the utterance reaches
+    a target drawn uniformly from [lo, hi] frames (4..6 s at 5 ms), then sil."""
+    g = genji_labels()
+    fr = label_frames(engine, g)
+    edge = sum(label_frames(engine, [SIL_HEAD, SIL_TAIL]))
+    out = []
+    for u in range(n_utt):
+        st, r1 = splitmix64(seed_base + first + u)
+        st, r2 = splitmix64(st)
+        target = lo + r1 % (hi - lo + 1)
+        i = r2 % len(g)
+        while _is_pause(g[i]):
+            i = (i + 1) % len(g)
+        body, total = [], edge
+        while total < target:
+            body.append(g[i])
+            total += fr[i]
+            i = (i + 1) % len(g)
+        while len(body) > 1 and _is_pause(body[-1]):
+            body.pop()
+        out.append([SIL_HEAD] + body + [SIL_TAIL])
+    return out
