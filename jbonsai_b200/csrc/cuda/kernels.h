@@ -114,7 +114,9 @@ int launch_frame_prep(const BatchLayout& b, const VocoderParams& p, const Vocode
 int launch_pulse(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, cudaStream_t stream);
 int launch_excitation(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,
                       int64_t total_frames, cudaStream_t stream);
-// variant: 0 = reference operation order, stage-per-lane; 1 (default, -1) = blocked-scan warp kernel
+// variant: 0 = reference operation order, stage-per-lane; 1 = blocked-scan warp kernel;
+// 2 (default, -1) = software-pipelined blocked scan (mlsa.cu)
+int launch_mlsa_v2(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, cudaStream_t stream);
 int launch_mlsa(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, int variant,
                 cudaStream_t stream);
 

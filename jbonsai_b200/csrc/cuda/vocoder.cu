@@ -616,7 +616,8 @@ int launch_mlsa(const BatchLayout& b, const VocoderParams& p, const VocoderDev& 
   if (p.nmcp != 35) return (int)cudaErrorInvalidValue;  // delay lines are register arrays
   // variant 1 (default): blocked-scan kernel; needs alpha != 0 (kappa_0 = -iaa/alpha) and 16 | fperiod
   const bool v1_ok = p.alpha > 1e-3 && p.fperiod % 16 == 0;
-  if ((variant < 0 || variant == 1) && v1_ok) {
+  if ((variant < 0 || variant == 2) && v1_ok) return launch_mlsa_v2(b, p, d, stream);
+  if (variant == 1 && v1_ok) {
     k_mlsa_v1<35><<<b.n_utt, 32, 0, stream>>>(b, p, d);
     return (int)cudaGetLastError();
   }

@@ -216,7 +216,7 @@ def test_multi_gpu_sharding_matches_single(eng):
     assert list(off) == list(off2) and np.array_equal(w, w2)
 
 
-@pytest.mark.parametrize("variant", [0, 1])
+@pytest.mark.parametrize("variant", [0, 1, 2])
 def test_mlsa_variants_vs_oracle(variant, orc):
     # variant 0 keeps the reference's operation order; variant 1 (default) is the blocked-scan kernel
     e = jb.Engine.load([NITECH])
