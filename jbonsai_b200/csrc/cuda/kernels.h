@@ -111,7 +111,8 @@ struct VocoderDev {
 
 int launch_frame_prep(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,
                       int64_t total_frames, cudaStream_t stream);
-int launch_pulse(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, cudaStream_t stream);
+int launch_pulse(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, int64_t total_samples,
+                 cudaStream_t stream);
 int launch_excitation(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,
                       int64_t total_frames, cudaStream_t stream);
 // variant: 0 = reference operation order, stage-per-lane; 1 = blocked-scan warp kernel;

@@ -15,18 +15,25 @@
 //   * df1/df2 sign pattern (mlsa.rs:54-79): with A = sum over odd stages of pp_k v_k and B = sum
 //     over even stages, d[0] = (x + A) - B and x' = x + 2A.
 //
-// Schedule: a lone warp issues in order, so the two loop-carried chains are interleaved by hand:
-//   region 1  K, t' (6 FMA), dot product with the coefficients -> partial y;  q/z scan of the NEXT
-//             sample from the new t';  coefficient interpolation;  publish partial y and E
+// Schedule: a lone warp issues in order, so the loop-carried chains are interleaved by hand and
+// every shared-memory round trip is covered with independent arithmetic:
+//   region 1  K = KE + kappa u ; partial y = yz + K cp  (yz = sum c_i z_i and cp = sum c_i (-a)^(i+1)
+//             are formed off the critical path) -> publish ; t' = z + P K
 //   sync 1
-//   region 2  lanes of stage s+1 sum the 6 partials of stage s (their next input; stage 1 sums
-//             stage 5) ; next carry K^E from the E's ; df1 section one sample ahead ; publish
+//   region 2  loads in flight: q/z scan of the NEXT sample from t', coefficient interpolation;
+//             then lanes of stage s+1 add the 6 partials of stage s (their next input; stage 1
+//             adds stage 5) ; df1 section one sample ahead ; publish y, f and E
 //   sync 2
-//   region 3  ONE combine for both cascades: lanes 0-17 form d22[0]/output of sample n from the
-//             five y's, lanes 18-31 form d12[0]/x of sample n+1 from the five df1 outputs.
-// Cross-lane traffic is double-buffered shared memory (an LDS.128 broadcast is one wavefront;
-// SHFL.64 costs 8 issue cycles per SMSP on B200). Stores are unconditional (per-lane dump
-// slots) so the loop has no divergent branch. The input chunk ring is filled with cp.async.
+//   region 3  loads in flight: yz of the next sample; then ONE combine for both cascades (lanes 0-17:
+//             d22[0]/output of sample n from the five y's; lanes 18-31: d12[0]/x of sample n+1 from
+//             the five df1 outputs) and the next carry KE from the E's.
+// The loop is unrolled by two so that the two exchange buffers are compile-time addresses; the last
+// sample is peeled (no look-ahead beyond the launch). Cross-lane traffic is shared memory (an
+// LDS.128 broadcast is one wavefront; SHFL.64 costs 8 issue cycles per SMSP on B200). Stores are
+// unconditional (per-lane dump slots): no divergent branch (predicating the traffic down to the lanes
+// that need it was measured: fewer wavefronts, but more registers/instructions and no gain). The input ring is filled by cp.async.
+#include <type_traits>
+
 #include "kernels.h"
 
 namespace jbk {
@@ -98,16 +105,15 @@ __global__ void __launch_bounds__(32) k_mlsa_v2(BatchLayout b, VocoderParams p, 
   const int rE = oE + 6 * s, rYP = oYP + 6 * instage;
   const int wVy = pub ? oV + instage : oDump + 2 * lane;
   const int wVf = pub ? oV + 8 + s : oDump + 2 * lane;
-  const int rV = oV + (R ? 8 : 0);
-  const int rVf = oV + 8 + ((s >= 1 && s < 5) ? s - 1 : 0);
   const int wG = R ? oG : oDump + 2 * lane;
+  const int rGin = (s >= 1 && s < 5) ? oV + 8 + s - 1 : oG;  // d12[s] of the current sample
 
   for (int i = lane; i < 2 * kBufD; i += 32) sBuf[i] = 0.0;
   for (int i = lane; i < kCH * 32; i += 32) sOut[i] = 0.0;
 
   // ---- state (layout: kernels.h)
   double t[6] = {0, 0, 0, 0, 0, 0}, tm1 = 0.0, c[6] = {0, 0, 0, 0, 0, 0}, c1 = 0.0;
-  double d11 = 0.0, ginf = 0.0, uin = 0.0;
+  double d11 = 0.0, gin = 0.0, uin = 0.0;
   int jtap[6];
   bool cvalid[6];
 #pragma unroll
@@ -126,7 +132,7 @@ __global__ void __launch_bounds__(32) k_mlsa_v2(BatchLayout b, VocoderParams p, 
     tm1 = bb > 0 ? stp[226 + 5 * s + bb - 1] : 0.0;
     c1 = stp[188 + 1];
     d11 = stp[170 + s + 1];
-    ginf = stp[176 + s];  // d12[s]: input of section s+1 (s = 0: d12[0])
+    gin = stp[176 + s];   // d12[s]: input of section s+1
     uin = stp[182 + s];   // d22[s]: input of stage s+1
   }
 
@@ -158,12 +164,17 @@ __global__ void __launch_bounds__(32) k_mlsa_v2(BatchLayout b, VocoderParams p, 
   sIn[lane] = lane < N ? wv[lane] : 0.0;  // chunks 0 and 1
   __syncwarp();
 
+  double* const B0 = sBuf;
+  double* const B1 = sBuf + kBufD;
+  const double* const vpE = R ? B1 + oV + 8 : B0 + oV;  // region-3 operands of even / odd samples
+  const double* const vpO = R ? B0 + oV + 8 : B1 + oV;
+
   // ---- prologue: bring the pipeline to the top of sample 0 of this launch
-  //   z, KE: zero-carry scan and carry of sample 0;  (g0n, x1n): df1 result of sample 0;  ginf: d12[s] of sample 0
-  double z[6], KE, g0n, x1n;
+  //   z, KE: zero-carry scan and carry of sample 0; yz, cp: dot-product pieces; buffer 0 holds
+  //   f_1..f_5 and (d12[0], x after df1) of sample 0
+  double z[6], KE, yz, cp, cpinc;
   {
-    double* B1 = sBuf + kBufD;
-    d11 = __fma_rn(a, d11, iaa * ginf);  // df1 section s+1 for sample 0 (mlsa.rs:57-58)
+    d11 = __fma_rn(a, d11, iaa * gin);  // df1 section s+1 for sample 0 (mlsa.rs:57-58)
     const double fk = d11 * c1;
     const double q0 = __fma_rn(a, t[0], tm1), q1 = __fma_rn(a, t[1], t[0]), q2 = __fma_rn(a, t[2], t[1]),
                  q3 = __fma_rn(a, t[3], t[2]), q4 = __fma_rn(a, t[4], t[3]), q5 = __fma_rn(a, t[5], t[4]);
@@ -174,33 +185,38 @@ __global__ void __launch_bounds__(32) k_mlsa_v2(BatchLayout b, VocoderParams p, 
     z[4] = __fma_rn(ma, z[3], q4);
     z[5] = __fma_rn(ma, z[4], q5);
     B1[wE] = z[5];
-    B1[wVf] = fk;
+    B0[wVf] = fk;
     __syncwarp();
     const double2 e01 = *reinterpret_cast<const double2*>(B1 + rE);
     const double2 e23 = *reinterpret_cast<const double2*>(B1 + rE + 2);
     const double e4 = B1[rE + 4];
     KE = __fma_rn(W[4], e4, __fma_rn(W[2], e23.x, W[0] * e01.x)) + __fma_rn(W[3], e23.y, W[1] * e01.y);
-    const double2 f12 = *reinterpret_cast<const double2*>(B1 + oV + 8);
-    const double2 f34 = *reinterpret_cast<const double2*>(B1 + oV + 10);
-    const double f5 = B1[oV + 12];
+    const double2 f12 = *reinterpret_cast<const double2*>(B0 + oV + 8);
+    const double2 f34 = *reinterpret_cast<const double2*>(B0 + oV + 10);
+    const double f5 = B0[oV + 12];
     const double e0 = sIn[0];
     const double A = __fma_rn(pp5, f5, __fma_rn(pp3, f34.x, pp1 * f12.x));
     const double Bv = __fma_rn(pp4, f34.y, pp2 * f12.y);
-    g0n = (e0 + A) - Bv;
-    x1n = __fma_rn(2.0, A, e0);
-    if (s >= 1) ginf = B1[rVf];  // d12[s](0) = f_s(0)
+    B0[oG] = (e0 + A) - Bv;  // every lane writes the same pair
+    B0[oG + 1] = __fma_rn(2.0, A, e0);
     __syncwarp();
-    sBuf[oG] = g0n;  // every lane holds the same pair
-    sBuf[oG + 1] = x1n;
   }
+  auto dot6 = [](const double (&x)[6], const double (&y)[6]) {
+    return __fma_rn(x[4], y[4], __fma_rn(x[2], y[2], x[0] * y[0])) +
+           __fma_rn(x[5], y[5], __fma_rn(x[3], y[3], x[1] * y[1]));
+  };
+  yz = dot6(c, z);
+  cp = dot6(c, P);
+  cpinc = dot6(cinc, P);
 
-  int po = 0;  // offset of the current exchange buffer (0 or kBufD)
-#pragma unroll 1
-  for (int n = 0; n < N; ++n) {
-    double* B = sBuf + po;
-    const bool has_next = n + 1 < N;
-    // ---------------- region 1
+  int inIdx = 1;                 // ring slot of the next sample's excitation
+  double* outp = sOut + lane;    // this lane's column of the output tile
+
+  auto step = [&](double* __restrict__ B, double* __restrict__ Bn, const double* __restrict__ vp, auto LAST) {
+    constexpr bool last = decltype(LAST)::value;
+    // ---------------- region 1: critical path  u -> K -> partial y
     const double K = __fma_rn(kap, uin, KE);
+    B[wYP] = __fma_rn(K, cp, yz);
     t[0] = __fma_rn(P[0], K, z[0]);
     t[1] = __fma_rn(P[1], K, z[1]);
     t[2] = __fma_rn(P[2], K, z[2]);
@@ -208,9 +224,13 @@ __global__ void __launch_bounds__(32) k_mlsa_v2(BatchLayout b, VocoderParams p, 
     t[4] = __fma_rn(P[4], K, z[4]);
     t[5] = __fma_rn(P[5], K, z[5]);
     tm1 = bb > 0 ? K : 0.0;
-    const double ya = __fma_rn(c[4], t[4], __fma_rn(c[2], t[2], c[0] * t[0]));
-    const double yb = __fma_rn(c[5], t[5], __fma_rn(c[3], t[3], c[1] * t[1]));
-    B[wYP] = ya + yb;
+    __syncwarp();
+    // ---------------- region 2
+    const double2 r01 = *reinterpret_cast<const double2*>(B + rYP);  // 6 partials of stage `instage`
+    const double2 r23 = *reinterpret_cast<const double2*>(B + rYP + 2);
+    const double2 r45 = *reinterpret_cast<const double2*>(B + rYP + 4);
+    gin = B[rGin];                                                     // d12[s] of this sample
+    const double base = *(R ? sIn + inIdx : B + oG + 1);               // R = 1: e(n+1);  R = 0: x after df1 (n)
     {  // zero-carry scan of the next sample
       const double q0 = __fma_rn(a, t[0], tm1), q1 = __fma_rn(a, t[1], t[0]), q2 = __fma_rn(a, t[2], t[1]),
                    q3 = __fma_rn(a, t[3], t[2]), q4 = __fma_rn(a, t[4], t[3]), q5 = __fma_rn(a, t[5], t[4]);
@@ -224,6 +244,7 @@ __global__ void __launch_bounds__(32) k_mlsa_v2(BatchLayout b, VocoderParams p, 
     B[wE] = z[5];
 #pragma unroll
     for (int i = 0; i < 6; ++i) c[i] += cinc[i];  // mod.rs:133-135
+    cp += cpinc;
     c1 += c1inc;
     if (--left == 0) {  // frame end: *coefficients = cc (mod.rs:140), then the next frame's prologue
 #pragma unroll
@@ -235,6 +256,8 @@ __global__ void __launch_bounds__(32) k_mlsa_v2(BatchLayout b, VocoderParams p, 
       c1 = cc1;
       cc1 = ccn1;
       c1inc = (cc1 - c1) / fper;
+      cp = dot6(c, P);
+      cpinc = dot6(cinc, P);
       const double* bn = bsrc + (int64_t)(fnext < f1 ? fnext : f1 - 1) * kNM;
 #pragma unroll
       for (int i = 0; i < 6; ++i) ccn[i] = cvalid[i] ? bn[jtap[i]] : 0.0;
@@ -242,54 +265,49 @@ __global__ void __launch_bounds__(32) k_mlsa_v2(BatchLayout b, VocoderParams p, 
       ++fnext;
       left = fp;
     }
-    if ((n & (kCH - 1)) == kCH - 2) cp_async_wait_all();  // the chunk after this one has landed
+    const double ysum = ((r01.x + r01.y) + (r23.x + r23.y)) + (r45.x + r45.y);
+    B[wVy] = ysum;
+    if (!last) {  // df1 section s+1, one sample ahead (mlsa.rs:57-58)
+      d11 = __fma_rn(a, d11, iaa * gin);
+      Bn[wVf] = d11 * c1;
+    }
     __syncwarp();
-    // ---------------- region 2
-    const double2 r01 = *reinterpret_cast<const double2*>(B + rYP);
-    const double2 r23 = *reinterpret_cast<const double2*>(B + rYP + 2);
-    const double2 r45 = *reinterpret_cast<const double2*>(B + rYP + 4);
+    // ---------------- region 3
+    const double2 v12 = *reinterpret_cast<const double2*>(vp);
+    const double2 v34 = *reinterpret_cast<const double2*>(vp + 2);
+    const double v5 = vp[4];
     const double2 e01 = *reinterpret_cast<const double2*>(B + rE);
     const double2 e23 = *reinterpret_cast<const double2*>(B + rE + 2);
     const double e4 = B[rE + 4];
-    const double2 gx = *reinterpret_cast<const double2*>(B + oG);  // (d12[0], x after df1) of sample n
-    const double e_next = sIn[(n + 1) & (2 * kCH - 1)];
-    const double ysum = ((r01.x + r01.y) + (r23.x + r23.y)) + (r45.x + r45.y);
-    KE = __fma_rn(W[4], e4, __fma_rn(W[2], e23.x, W[0] * e01.x)) + __fma_rn(W[3], e23.y, W[1] * e01.y);
-    g0n = gx.x;
-    x1n = gx.y;
-    // df1 section s+1, one sample ahead (mlsa.rs:57-58)
-    const double d11n = __fma_rn(a, d11, iaa * (s == 0 ? g0n : ginf));
-    const double fk = d11n * c1;
-    d11 = has_next ? d11n : d11;
-    B[wVy] = ysum;
-    B[wVf] = fk;
-    __syncwarp();
-    // ---------------- region 3: one combine for both cascades (mlsa.rs:59-65, 72-78)
-    const double2 v12 = *reinterpret_cast<const double2*>(B + rV);
-    const double2 v34 = *reinterpret_cast<const double2*>(B + rV + 2);
-    const double v5 = B[rV + 4];
-    const double gf = B[rVf];
-    const double base = R ? e_next : x1n;
+    yz = dot6(c, z);
     const double A = __fma_rn(pp5, v5, __fma_rn(pp3, v34.x, pp1 * v12.x));
     const double Bv = __fma_rn(pp4, v34.y, pp2 * v12.y);
-    const double r1 = (base + A) - Bv;      // R = 0: d22[0](n)    R = 1: d12[0](n+1)
+    const double r1 = (base + A) - Bv;         // R = 0: d22[0](n)    R = 1: d12[0](n+1)
     const double r2 = __fma_rn(2.0, A, base);  // R = 0: output(n)    R = 1: x after df1 (n+1)
+    KE = __fma_rn(W[4], e4, __fma_rn(W[2], e23.x, W[0] * e01.x)) + __fma_rn(W[3], e23.y, W[1] * e01.y);
     uin = s == 0 ? r1 : ysum;
-    ginf = (has_next && s >= 1) ? gf : ginf;
-    sOut[(n & (kCH - 1)) * 32 + lane] = r2;
-    po ^= kBufD;
-    {
-      double* Bn = sBuf + po;
-      Bn[wG] = r1;
-      Bn[wG + 1] = r2;
+    *outp = r2;
+    outp += 32;
+    if (!last) *reinterpret_cast<double2*>(Bn + wG) = make_double2(r1, r2);
+    inIdx = (inIdx + 1) & (2 * kCH - 1);
+  };
+
+  const std::false_type F{};
+  const std::true_type L{};
+  for (int i0 = 0; i0 < N; i0 += kCH) {
+    outp = sOut + lane;
+#pragma unroll 1
+    for (int j = 0; j < kCH - 2; j += 2) {
+      step(B0, B1, vpE, F);
+      step(B1, B0, vpO, F);
     }
-    if ((n & (kCH - 1)) == kCH - 1) {  // chunk done: flush 16 outputs, refill this half of the ring
-      __syncwarp();
-      const int i0 = n - (kCH - 1);
-      if (lane < kCH) {
-        wv[i0 + lane] = sOut[lane * 32] * p.volume;
-        if (i0 + 2 * kCH + lane < N) cp_async8(&sIn[(i0 & kCH) + lane], wv + i0 + 2 * kCH + lane);
-      }
+    cp_async_wait_all();  // the next chunk has landed; the sync inside the next step publishes it
+    step(B0, B1, vpE, F);
+    if (i0 + kCH >= N) step(B1, B0, vpO, L); else step(B1, B0, vpO, F);
+    __syncwarp();
+    if (lane < kCH) {  // flush 16 outputs, refill this half of the ring
+      wv[i0 + lane] = sOut[lane * 32] * p.volume;
+      if (i0 + 2 * kCH + lane < N) cp_async8(&sIn[(i0 & kCH) + lane], wv + i0 + 2 * kCH + lane);
     }
   }
 
@@ -306,15 +324,15 @@ __global__ void __launch_bounds__(32) k_mlsa_v2(BatchLayout b, VocoderParams p, 
       if (bb > 0) stp[226 + 5 * s + bb - 1] = tm1;
       if (bb == 0) {
         stp[170 + s + 1] = d11;
-        stp[176 + s] = s == 0 ? g0n : ginf;  // d12[s]
-        stp[182 + s] = uin;                  // d22[s]
+        stp[176 + s] = gin;  // d12[s]
+        stp[182 + s] = uin;  // d22[s]
       }
     }
     if (lane == 0) {
       stp[188 + 1] = c1;
       stp[188] = bsrc[(int64_t)(f1 - 1) * kNM];  // coefficients[0] = cc[0] at a frame end
-      stp[176 + 5] = sBuf[po + oV + 8 + 4];      // d12[5], d22[5]: inputs of no stage, kept for layout parity
-      stp[182 + 5] = sBuf[(po ^ kBufD) + oV + 4];
+      stp[176 + 5] = B1[oV + 8 + 4];             // d12[5], d22[5]: inputs of no stage, kept for layout parity
+      stp[182 + 5] = B1[oV + 4];
     }
   }
 }

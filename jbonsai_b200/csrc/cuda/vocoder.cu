@@ -55,9 +55,14 @@ __global__ void k_frame_prep(VocoderParams p, VocoderDev d, int64_t total_frames
 }
 
 // ---------------------------------------------------------------- pulse train
-__global__ void k_pulse(BatchLayout b, VocoderParams p, VocoderDev d) {
+// One thread per utterance walks the pitch counter sample by sample (the additions must round
+// exactly like excitation.rs:72-86, so the walk is sequential) but only WRITES the pulses: the
+// pulse array is zeroed beforehand (launch_pulse memsets it; dense=1 zeroes frame by frame for the
+// chunked streaming path). Pitch values of the next frame are fetched one frame ahead.
+__global__ void __launch_bounds__(32) k_pulse(BatchLayout b, VocoderParams p, VocoderDev d, int dense) {
   int u = blockIdx.x * blockDim.x + threadIdx.x;
   if (u >= b.n_utt) return;
+  if (b.order) u = b.order[u];  // neighbouring lanes get utterances of similar length
   const int64_t foff = b.frame_off[u];
   const int T = (int)(b.frame_off[u + 1] - foff);
   int f0 = d.frame_begin, f1 = f0 + d.frame_count;
@@ -67,33 +72,34 @@ __global__ void k_pulse(BatchLayout b, VocoderParams p, VocoderDev d) {
     p_cur = d.state[(int64_t)u * kVocStateDoubles + 223];
     cnt = d.state[(int64_t)u * kVocStateDoubles + 224];
   }
-  const double fper = (double)p.fperiod;
+  const int fp = p.fperiod;
+  const double fper = (double)fp;
+  double pitch_next = f0 < f1 ? d.pitch[foff + f0] : 0.0;
   for (int f = f0; f < f1; ++f) {
-    const double pitch = d.pitch[foff + f];
+    const double pitch = pitch_next;
+    if (f + 1 < f1) pitch_next = d.pitch[foff + f + 1];
     double inc;
-    if (p_cur != 0.0 && pitch != 0.0) {  // Excitation::start
+    if (p_cur != 0.0 && pitch != 0.0) {  // Excitation::start (excitation.rs:25-33)
       inc = (pitch - p_cur) / fper;
     } else {
       inc = 0.0;
       p_cur = pitch;
       cnt = pitch;
     }
-    double* out = d.pulse + (foff + f) * p.fperiod;
-    if (p_cur == 0.0) {
-      for (int i = 0; i < p.fperiod; ++i) out[i] = 0.0;
-    } else {
-      for (int i = 0; i < p.fperiod; ++i) {
+    double* out = d.pulse + (foff + f) * fp;
+    if (dense)
+      for (int i = 0; i < fp; ++i) out[i] = 0.0;
+    if (p_cur != 0.0) {
+      for (int i = 0; i < fp; ++i) {  // voiced_frame (excitation.rs:72-86)
         cnt += 1.0;
-        double pulse = 0.0;
         if (cnt >= p_cur) {
           cnt -= p_cur;
-          pulse = sqrt(p_cur);
+          out[i] = sqrt(p_cur);
         }
-        out[i] = pulse;
         p_cur += inc;
       }
     }
-    p_cur = pitch;  // Excitation::end
+    p_cur = pitch;  // Excitation::end (excitation.rs:102-104)
   }
   if (d.state) {
     d.state[(int64_t)u * kVocStateDoubles + 223] = p_cur;
@@ -102,17 +108,19 @@ __global__ void k_pulse(BatchLayout b, VocoderParams p, VocoderDev d) {
 }
 
 // ---------------------------------------------------------------- excitation + gain
-// One block per frame. Gather form of the ring-buffer overlap-add: output sample n sums, oldest
-// source first, over source samples m = n-(nlpf-1) .. n:
+// One block per frame. Gather form of the ring-buffer overlap-add (excitation.rs:43-64,67-100):
+// output sample n sums, oldest source first, over source samples m = n-(nlpf-1) .. n:
 //    [m == n-h]   + noise[m]                       (get_antipode_mut, h = (nlpf-1)/2)
 //    [voiced(m)]  + (pulse[m]-noise[m]) * lpf_{frame(m)}[n-m]
-// which is exactly the order in which the reference's scatter adds reach ring slot n.
+// which is exactly the order in which the reference's scatter adds reach ring slot n. Unvoiced
+// sources contribute (pulse-noise) := 0, i.e. an exact "+ 0.0". The gain exp(c[0]) (mod.rs:129-131)
+// uses coefficients[0] advanced by repeated addition like the per-sample loop (mod.rs:133-135);
+// that 240-step chain runs in the last thread of the block while the others do the taps.
 constexpr int kMaxLpf = 64;
 constexpr int kMaxFperiod = 1024;
 
 __global__ void __launch_bounds__(256) k_excitation(BatchLayout b, VocoderParams p, VocoderDev d,
                                                     int64_t total_frames) {
-  // block -> (utterance, frame) restricted to [frame_begin, frame_begin+frame_count)
   const int64_t gf = blockIdx.x;
   if (gf >= total_frames) return;
   const int u = find_utt(b.frame_off, b.n_utt, gf);
@@ -120,26 +128,29 @@ __global__ void __launch_bounds__(256) k_excitation(BatchLayout b, VocoderParams
   const int f = (int)(gf - foff);
   if (f < d.frame_begin || (d.frame_count >= 0 && f - d.frame_begin >= d.frame_count)) return;
 
-  __shared__ double s_pulse[kMaxFperiod + kMaxLpf];
+  __shared__ double s_diff[kMaxFperiod + kMaxLpf];   // voiced(m) ? pulse[m] - noise[m] : 0
   __shared__ double s_noise[kMaxFperiod + kMaxLpf];
-  __shared__ double s_lpf[2][kMaxLpf];
+  __shared__ double s_lpf[2 * kMaxLpf];               // [0..64) previous frame, [64..128) this frame
   __shared__ double s_c0[kMaxFperiod];
   const int nl = p.nlpf, fp = p.fperiod, hist = nl > 0 ? nl - 1 : 0;
   const int64_t n0 = (int64_t)f * fp;  // first sample of this frame within the utterance
   const bool voiced_cur = d.pitch[gf] != 0.0;
   const bool voiced_prev = f > 0 && d.pitch[gf - 1] != 0.0;
+  const double* pulse = d.pulse + foff * fp + n0 - hist;
+  const double* noise = d.noise + n0 - hist;
 
   for (int i = threadIdx.x; i < fp + hist; i += blockDim.x) {
-    const int64_t m = n0 - hist + i;
-    s_pulse[i] = m >= 0 ? d.pulse[foff * fp + m] : 0.0;
-    s_noise[i] = m >= 0 ? d.noise[m] : 0.0;
+    const bool in = n0 - hist + i >= 0;
+    const double nz = in ? noise[i] : 0.0;
+    const bool v = i >= hist ? voiced_cur : voiced_prev;
+    s_noise[i] = nz;
+    s_diff[i] = (in && v) ? (nl > 0 ? pulse[i] - nz : pulse[i]) : 0.0;
   }
   for (int i = threadIdx.x; i < nl; i += blockDim.x) {
-    s_lpf[1][i] = d.lpf[gf * nl + i];
-    s_lpf[0][i] = f > 0 ? d.lpf[(gf - 1) * nl + i] : 0.0;
+    s_lpf[kMaxLpf + i] = d.lpf[gf * nl + i];
+    s_lpf[i] = f > 0 ? d.lpf[(gf - 1) * nl + i] : 0.0;
   }
-  if (threadIdx.x == 0) {
-    // coefficients[0] by repeated addition, as the per-sample loop does (mod.rs:133-135)
+  if (threadIdx.x == blockDim.x - 1) {
     const double cc = d.b[gf * p.nmcp];
     double c = f > 0 ? d.b[(gf - 1) * p.nmcp] : cc;
     const double cinc = (cc - c) / (double)fp;
@@ -150,24 +161,27 @@ __global__ void __launch_bounds__(256) k_excitation(BatchLayout b, VocoderParams
   }
   __syncthreads();
 
+  double* wave = d.wave + foff * fp + n0;
   for (int i = threadIdx.x; i < fp; i += blockDim.x) {
     double x;
     if (nl > 0) {
       const int h = (nl - 1) / 2;
-      x = 0.0;
-      for (int k = nl - 1; k >= 0; --k) {  // source m = n - k, oldest first
-        const int j = i + hist - k;        // index into the staged window
-        const int64_t m = n0 + i - k;
-        if (m < 0) continue;
-        const bool cur = (i - k) >= 0;     // source sample lies in this frame
-        if (k == h) x += s_noise[j];
-        if (cur ? voiced_cur : voiced_prev) x += (s_pulse[j] - s_noise[j]) * s_lpf[cur ? 1 : 0][k];
+      if (!voiced_cur && !(voiced_prev && i < hist)) {
+        x = 0.0 + s_noise[i + hist - h];  // only the centre-tap noise reaches this slot
+      } else {
+        x = 0.0;
+        // sources of the previous frame (k > i) use its filter, the rest this frame's
+        for (int k = nl - 1; k >= 0; --k) {
+          const int j = i + hist - k;
+          if (k == h) x += s_noise[j];
+          x += s_diff[j] * s_lpf[(k <= i ? kMaxLpf : 0) + k];
+        }
       }
     } else {
-      x = voiced_cur ? s_pulse[i] : s_noise[i];
+      x = voiced_cur ? s_diff[i] : s_noise[i];
     }
     if (x != 0.0) x *= exp(s_c0[i]);
-    d.wave[foff * fp + n0 + i] = x;
+    wave[i] = x;
   }
 }
 
@@ -595,10 +609,17 @@ int launch_frame_prep(const BatchLayout& b, const VocoderParams& p, const Vocode
   return (int)cudaGetLastError();
 }
 
-int launch_pulse(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, cudaStream_t stream) {
+int launch_pulse(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, int64_t total_samples,
+                 cudaStream_t stream) {
   if (b.n_utt == 0) return 0;
   const int threads = 32;
-  k_pulse<<<(b.n_utt + threads - 1) / threads, threads, 0, stream>>>(b, p, d);
+  // whole-batch synthesis: zero the array with one memset and write only the pulses
+  const bool whole = d.frame_begin == 0 && d.frame_count < 0;
+  if (whole) {
+    cudaError_t e = cudaMemsetAsync(d.pulse, 0, (size_t)total_samples * sizeof(double), stream);
+    if (e != cudaSuccess) return (int)e;
+  }
+  k_pulse<<<(b.n_utt + threads - 1) / threads, threads, 0, stream>>>(b, p, d, whole ? 0 : 1);
   return (int)cudaGetLastError();
 }
 

@@ -496,7 +496,7 @@ static void launch_mlpg_all(Engine::Resident* r) {
 static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_excitation,
                            cudaEvent_t after_exc) {
   cudaStream_t st = r->ctx->stream;
-  JB_LAUNCH(jbk::launch_pulse(r->layout, r->vp, r->vd, st));
+  JB_LAUNCH(jbk::launch_pulse(r->layout, r->vp, r->vd, r->total_samples, st));
   JB_LAUNCH(jbk::launch_excitation(r->layout, r->vp, r->vd, r->total_frames, st));
   if (after_exc) JB_CUDA(cudaEventRecord(after_exc, st));
   if (!stop_after_excitation) JB_LAUNCH(jbk::launch_mlsa(r->layout, r->vp, r->vd, variant, st));
