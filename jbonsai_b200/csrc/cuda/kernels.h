@@ -35,6 +35,7 @@ struct BatchLayout {
   const int64_t* frame_off;  // [n_utt+1]
   const int32_t* durations;  // [total_states]
   int32_t* frame_state;      // [total_frames]  (out of expand) state index within the utterance
+  int max_frames;            // longest utterance of the batch (frames)
   const int32_t* order;      // [n_utt] utterances by decreasing length (block scheduling order) or null
 };
 

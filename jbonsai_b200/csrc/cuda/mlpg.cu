@@ -287,6 +287,366 @@ __global__ void __launch_bounds__(128) k_mlpg(BatchLayout b, StreamDev s, int64_
   }
 }
 
+
+// ================================================================ fast path
+// Same arithmetic as k_mlpg above (reference operation order for the band build, the LDL^T
+// factorisation and both substitutions), restructured for the memory system:
+//   * the (mean, ivar) pair of a frame only changes when the frame's state changes, so each
+//     thread keeps the current state's values in registers (one reciprocal per state and window,
+//     not seven per frame) and slides a 3-frame window over them;
+//   * the GV adjustment runs in its own kernel (k_mlpg_gv), one CTA per system with the system
+//     in shared memory, data-parallel over frames.
+// Window shapes: kShape1 = one static window of width 1 (band width 1); kShape133 = static + two
+// 3-tap dynamic windows (band width 3) — every shipped voice. Other shapes use k_mlpg.
+constexpr int kShape1 = 0, kShape133 = 1;
+
+template <int SHAPE>
+__global__ void __launch_bounds__(128) k_mlpg_solve(BatchLayout b, StreamDev s, int64_t plane) {
+  constexpr int BW = SHAPE == kShape133 ? 3 : 1;
+  constexpr int NW = SHAPE == kShape133 ? 3 : 1;
+  const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int u = gid / s.dim, d = gid - u * s.dim;
+  if (u >= b.n_utt) return;
+  const int64_t soff = b.state_off[u], foff = b.frame_off[u];
+  const int T = (int)(b.frame_off[u + 1] - foff);
+  const int dim = s.dim, L = s.dim * s.nwin;
+  const bool msd = s.is_msd != 0;
+  const int Tp = msd ? s.nvoiced[u] : T;
+
+  double* const base = s.scratch + foff * dim + d;
+  double* const pwum = base + (int64_t)BW * plane;
+  double* const pg = base + (int64_t)(BW + 1) * plane;
+  const bool gv = s.has_gv != 0;
+  const int32_t* const fstate = b.frame_state + foff;
+  const int32_t* const vidx = msd ? s.vidx + foff : nullptr;
+  const int32_t* const left = msd ? s.left + foff : nullptr;
+  const int32_t* const right = msd ? s.right + foff : nullptr;
+
+  // window coefficients (uniform)
+  double wc[NW][3];
+#pragma unroll
+  for (int w = 0; w < NW; ++w)
+#pragma unroll
+    for (int i = 0; i < 3; ++i) wc[w][i] = (w == 0) ? (i == 0 ? s.windows.coef[0][0] : 0.0) : s.windows.coef[w][i];
+
+  // (mean, ivar) of the current state, per window; refreshed when the state index changes
+  int st_cached = -1;
+  double cm[NW], civ[NW];
+  // sliding window over compacted frames k-1, k, k+1: effective (mean, ivar) per window
+  double m_[NW][3], iv_[NW][3];
+#pragma unroll
+  for (int w = 0; w < NW; ++w)
+#pragma unroll
+    for (int i = 0; i < 3; ++i) { m_[w][i] = 0.0; iv_[w][i] = 0.0; }
+
+  auto fetch = [&](int k, double (&mo)[NW], double (&ivo)[NW]) {  // params of compacted frame k (mod.rs:57-84)
+    const int t = msd ? vidx[k] : k;
+    const int st = fstate[t];
+    if (st != st_cached) {
+      st_cached = st;
+      const int64_t o = (soff + st) * L + d;
+#pragma unroll
+      for (int w = 0; w < NW; ++w) {
+        cm[w] = s.mean[o + dim * w];
+        civ[w] = with_ivar(s.vari[o + dim * w]);
+      }
+    }
+    const int l = msd ? left[t] : t;
+    const int r = msd ? right[t] : T - 1 - t;
+#pragma unroll
+    for (int w = 0; w < NW; ++w) {
+      mo[w] = cm[w];
+      ivo[w] = (w != 0 && (l < 1 || r < 1)) ? 0.0 : civ[w];  // 3-tap window: left/right width 1
+    }
+  };
+
+  // ---- pass 1: band build (mlpg.rs:31-61), LDL (mlpg.rs:79-92), forward substitution (:98-104)
+  double prev[BW][BW], gprev[BW];
+#pragma unroll
+  for (int i = 0; i < BW; ++i) {
+    gprev[i] = 0.0;
+#pragma unroll
+    for (int j = 0; j < BW; ++j) prev[i][j] = 0.0;
+  }
+  if (Tp > 0) {
+    double mo[NW], ivo[NW];
+    fetch(0, mo, ivo);
+#pragma unroll
+    for (int w = 0; w < NW; ++w) { m_[w][1] = mo[w]; iv_[w][1] = ivo[w]; }  // slot 1 = frame k, slot 2 = k+1
+    if (Tp > 1) {
+      fetch(1, mo, ivo);
+#pragma unroll
+      for (int w = 0; w < NW; ++w) { m_[w][2] = mo[w]; iv_[w][2] = ivo[w]; }
+    }
+  }
+  for (int k = 0; k < Tp; ++k) {
+    double row[BW];
+#pragma unroll
+    for (int j = 0; j < BW; ++j) row[j] = 0.0;
+    double wum = 0.0;
+    {  // window 0: static, width 1
+      const double coef = wc[0][0];
+      if (coef != 0.0) {
+        const double wu = coef * iv_[0][1];
+        wum += wu * m_[0][1];
+        row[0] += wu * coef;
+      }
+    }
+    if (SHAPE == kShape133) {
+#pragma unroll
+      for (int w = 1; w < NW; ++w) {
+#pragma unroll
+        for (int index = 2; index >= 0; --index) {
+          const double coef = wc[w][index];
+          if (coef == 0.0) continue;
+          const int idx = k - (index - 1);  // slot = 1 - (index - 1) = 2 - index
+          if (idx < 0 || idx >= Tp) continue;
+          const double wu = coef * iv_[w][2 - index];
+          wum += wu * m_[w][2 - index];
+#pragma unroll
+          for (int inner = 2; inner >= index; --inner) {
+            const double c2 = wc[w][inner];
+            if (c2 == 0.0) continue;
+            const int j = inner - index;
+            if (k + j >= Tp) break;
+            row[j] += wu * c2;
+          }
+        }
+      }
+    }
+    if (gv) {
+#pragma unroll
+      for (int j = 0; j < BW; ++j) base[(int64_t)(BW + 2 + j) * plane + (int64_t)k * dim] = row[j];
+    }
+    pwum[(int64_t)k * dim] = wum;
+#pragma unroll
+    for (int i = 1; i < BW; ++i)
+      if (i < k + 1) row[0] -= prev[i][i] * prev[i][i] * prev[i][0];
+#pragma unroll
+    for (int i = 1; i < BW; ++i) {
+#pragma unroll
+      for (int j = 1; j < BW; ++j)
+        if (j < BW - i && j < k + 1) row[i] -= prev[j][j] * prev[j][i + j] * prev[j][0];
+      row[i] /= row[0];
+    }
+    double g = wum;
+#pragma unroll
+    for (int i = 1; i < BW; ++i)
+      if (i < k + 1) g -= prev[i][i] * gprev[i];
+#pragma unroll
+    for (int j = 0; j < BW; ++j) base[(int64_t)j * plane + (int64_t)k * dim] = row[j];
+    pg[(int64_t)k * dim] = g;
+#pragma unroll
+    for (int i = BW - 1; i >= 2; --i) {
+      gprev[i] = gprev[i - 1];
+#pragma unroll
+      for (int j = 0; j < BW; ++j) prev[i][j] = prev[i - 1][j];
+    }
+    if (BW > 1) {
+      gprev[1] = g;
+#pragma unroll
+      for (int j = 0; j < BW; ++j) prev[1][j] = row[j];
+    }
+    // slide the parameter window
+#pragma unroll
+    for (int w = 0; w < NW; ++w) {
+      m_[w][0] = m_[w][1]; iv_[w][0] = iv_[w][1];
+      m_[w][1] = m_[w][2]; iv_[w][1] = iv_[w][2];
+    }
+    if (k + 2 < Tp) {
+      double mo[NW], ivo[NW];
+      fetch(k + 2, mo, ivo);
+#pragma unroll
+      for (int w = 0; w < NW; ++w) { m_[w][2] = mo[w]; iv_[w][2] = ivo[w]; }
+    }
+  }
+
+  // ---- pass 2: backward substitution (mlpg.rs:106-113); loads of the next steps are issued ahead
+  double* out = s.par + foff * dim + d;
+  const bool direct = !gv;  // without GV this kernel also writes the output
+  if (direct && msd)
+    for (int t = 0; t < T; ++t)
+      if (left[t] < 0) out[(int64_t)t * dim] = kNoData;
+  {
+    double pn[BW];
+#pragma unroll
+    for (int i = 0; i < BW; ++i) pn[i] = 0.0;
+    constexpr int U = 4;
+    for (int k0 = Tp - 1; k0 >= 0; k0 -= U) {
+      double fg[U], f[U][BW];
+#pragma unroll
+      for (int q = 0; q < U; ++q) {
+        const int k = k0 - q;
+        if (k >= 0) {
+          fg[q] = pg[(int64_t)k * dim];
+#pragma unroll
+          for (int j = 0; j < BW; ++j) f[q][j] = base[(int64_t)j * plane + (int64_t)k * dim];
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < U; ++q) {
+        const int k = k0 - q;
+        if (k < 0) break;
+        double par = fg[q] / f[q][0];
+#pragma unroll
+        for (int i = 1; i < BW; ++i)
+          if (i < Tp - k) par -= f[q][i] * pn[i];
+        pg[(int64_t)k * dim] = par;
+        if (direct) out[(int64_t)(msd ? vidx[k] : k) * dim] = par;
+#pragma unroll
+        for (int i = BW - 1; i >= 2; --i) pn[i] = pn[i - 1];
+        if (BW > 1) pn[1] = par;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------- GV adjustment, one CTA per system
+// MlpgGlobalVariance::{calc_gv, conv_gv, calc_hmmobj_derivative, next_step, parmgen}
+// (mlpg.rs:168-292) on the solution left in the `g` plane by k_mlpg_solve, using the un-factorised
+// band and W'U^-1 mu it stored. All passes are data-parallel over frames; the three sums per
+// iteration are fixed-shape block reductions (deterministic; they differ from the reference's
+// left-to-right sums only in rounding, far inside the 1e-9 parameter tolerance). The system lives
+// in shared memory when it fits (smem_frames), else the same code runs on the global planes.
+__device__ __forceinline__ double block_sum(double v, double* red) {
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  const int w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  __syncthreads();  // red[] may still be read from the previous reduction
+  if ((threadIdx.x & 31) == 0) red[w] = v;
+  __syncthreads();
+  double t = 0.0;
+  for (int i = 0; i < nw; ++i) t += red[i];
+  return t;
+}
+
+template <int BW>
+__global__ void __launch_bounds__(256) k_mlpg_gv(BatchLayout b, StreamDev s, int64_t plane, int smem_frames) {
+  extern __shared__ double sm[];
+  __shared__ double red[8];
+  const int sys = blockIdx.x;
+  const int u = sys / s.dim, d = sys - u * s.dim;
+  const int64_t soff = b.state_off[u], foff = b.frame_off[u];
+  const int T = (int)(b.frame_off[u + 1] - foff);
+  const int dim = s.dim, tid = threadIdx.x, nt = blockDim.x;
+  const bool msd = s.is_msd != 0;
+  const int Tp = msd ? s.nvoiced[u] : T;
+  const int32_t* const fstate = b.frame_state + foff;
+  const int32_t* const vidx = msd ? s.vidx + foff : nullptr;
+  double* out = s.par + foff * dim + d;
+  if (msd)
+    for (int t = tid; t < T; t += nt)
+      if (s.left[foff + t] < 0) out[(int64_t)t * dim] = kNoData;  // Mask::fill (mask.rs:34-49)
+  if (Tp == 0) return;
+
+  double* const gbase = s.scratch + foff * dim + d;
+  double* const g_par = gbase + (int64_t)(BW + 1) * plane;
+  double* const g_wum = gbase + (int64_t)BW * plane;
+  const bool in_smem = Tp <= smem_frames;
+  double *PAR, *WUM, *GRAD, *O[BW];
+  int64_t st;  // element stride
+  uint8_t* SW = nullptr;
+  if (in_smem) {
+    PAR = sm;
+#pragma unroll
+    for (int j = 0; j < BW; ++j) O[j] = sm + (int64_t)(1 + j) * Tp;
+    WUM = sm + (int64_t)(1 + BW) * Tp;
+    GRAD = sm + (int64_t)(2 + BW) * Tp;
+    SW = reinterpret_cast<uint8_t*>(sm + (int64_t)(3 + BW) * Tp);
+    st = 1;
+    for (int k = tid; k < Tp; k += nt) {
+      PAR[k] = g_par[(int64_t)k * dim];
+      WUM[k] = g_wum[(int64_t)k * dim];
+#pragma unroll
+      for (int j = 0; j < BW; ++j) O[j][k] = gbase[(int64_t)(BW + 2 + j) * plane + (int64_t)k * dim];
+      SW[k] = s.gv_switch[soff + fstate[msd ? vidx[k] : k]];
+    }
+    __syncthreads();
+  } else {
+    PAR = g_par;
+    WUM = g_wum;
+#pragma unroll
+    for (int j = 0; j < BW; ++j) O[j] = gbase + (int64_t)(BW + 2 + j) * plane;
+    GRAD = gbase + (int64_t)(2 * BW + 2) * plane;
+    st = dim;
+  }
+  auto sw = [&](int k) -> bool { return in_smem ? SW[k] != 0 : s.gv_switch[soff + fstate[msd ? vidx[k] : k]] != 0; };
+
+  double cnt = 0.0;
+  for (int k = tid; k < Tp; k += nt) cnt += sw(k) ? 1.0 : 0.0;
+  const int gv_length = (int)block_sum(cnt, red);
+  if (gv_length > 0) {
+    const double gv_mean = s.gv_mean[(int64_t)u * dim + d] * s.gv_weight;  // mlpg.rs:137-138
+    const double gv_vari = s.gv_vari[(int64_t)u * dim + d];
+    const double n = (double)gv_length;
+    auto calc_gv = [&](double& mean, double& vari) {  // mlpg.rs:168-188
+      double a = 0.0;
+      for (int k = tid; k < Tp; k += nt)
+        if (sw(k)) a += PAR[k * st];
+      mean = block_sum(a, red) / n;
+      a = 0.0;
+      for (int k = tid; k < Tp; k += nt)
+        if (sw(k)) {
+          const double p = PAR[k * st];
+          a += (p - mean) * (p - mean);
+        }
+      vari = block_sum(a, red) / n;
+    };
+    {  // conv_gv (mlpg.rs:191-199)
+      double mean, vari;
+      calc_gv(mean, vari);
+      const double ratio = sqrt(gv_mean / vari);
+      for (int k = tid; k < Tp; k += nt)
+        if (sw(k)) PAR[k * st] = ratio * (PAR[k * st] - mean) + mean;
+      __syncthreads();
+    }
+    const double wnorm = 1.0 / (double)((int64_t)s.nwin * (int64_t)Tp);
+    const double len = (double)Tp;
+    const double len2 = (double)((int64_t)Tp * (int64_t)Tp);
+    const double lenm1 = (double)(Tp - 1);
+    double step = 0.1, prevobj = 0.0;
+    for (int it = 1; it <= 5; ++it) {
+      double mean, vari;
+      calc_gv(mean, vari);
+      const double gvobj = -0.5 * 1.0 * vari * gv_vari * (vari - 2.0 * gv_mean);
+      double h = 0.0;  // calc_hmmobj_derivative (mlpg.rs:200-226)
+      for (int k = tid; k < Tp; k += nt) {
+        double g = O[0][k * st] * PAR[k * st];
+#pragma unroll
+        for (int i = 1; i < BW; ++i) {
+          if (k + i < Tp) g += O[i][k * st] * PAR[(k + i) * st];
+          if (k + 1 > i) g += O[i][(k - i) * st] * PAR[(k - i) * st];
+        }
+        GRAD[k * st] = g;
+        h += 1.0 * wnorm * PAR[k * st] * (WUM[k * st] - 0.5 * g);
+      }
+      const double hmmobj = block_sum(h, red);
+      const double obj = -(hmmobj + gvobj);
+      if (it > 1) {
+        if (obj > prevobj)
+          step *= 0.5;
+        else if (obj < prevobj)
+          step *= 1.2;
+      }
+      const double dv = -2.0 * gv_vari * (vari - gv_mean) / len;  // next_step (mlpg.rs:227-256)
+      for (int k = tid; k < Tp; k += nt) {
+        const double p = PAR[k * st];
+        const double hh = -1.0 * wnorm * O[0][k * st] -
+                          1.0 * 2.0 / len2 * (lenm1 * gv_vari * (vari - gv_mean) + 2.0 * gv_vari * (p - mean) * (p - mean));
+        const double gk = GRAD[k * st], wk = WUM[k * st];
+        double next_g;
+        if (sw(k))
+          next_g = 1.0 / hh * (1.0 * wnorm * (-gk + wk) + 1.0 * dv * (p - mean));
+        else
+          next_g = 1.0 / hh * (1.0 * wnorm * (-gk + wk));
+        PAR[k * st] = p + step * next_g;
+      }
+      __syncthreads();
+      prevobj = obj;
+    }
+  }
+  for (int k = tid; k < Tp; k += nt) out[(int64_t)(msd ? vidx[k] : k) * dim] = PAR[k * st];
+}
 }  // namespace
 
 int launch_expand(const BatchLayout& b, const StreamSet& set, cudaStream_t stream) {
@@ -302,7 +662,29 @@ int launch_mlpg(const BatchLayout& b, const StreamDev& s, int64_t total_frames, 
   const int64_t nthreads = (int64_t)b.n_utt * s.dim;
   const int threads = 128;
   const int blocks = (int)((nthreads + threads - 1) / threads);
-  switch (s.windows.band_width()) {
+  const WindowSet& w = s.windows;
+  const bool shape1 = w.nwin == 1 && w.width[0] == 1;
+  const bool shape133 = w.nwin == 3 && w.width[0] == 1 && w.width[1] == 3 && w.width[2] == 3;
+  if (shape1 || shape133) {
+    if (shape1) k_mlpg_solve<kShape1><<<blocks, threads, 0, stream>>>(b, s, plane);
+    else k_mlpg_solve<kShape133><<<blocks, threads, 0, stream>>>(b, s, plane);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess || !s.has_gv) return (int)e;
+    // GV: one CTA per system, the system in shared memory when it fits
+    const int bw = shape1 ? 1 : 3;
+    const size_t per_frame = (size_t)(3 + bw) * sizeof(double) + 1;
+    const size_t cap = 200 * 1024;
+    int smem_frames = (int)((cap - 16) / per_frame);
+    if (smem_frames > b.max_frames) smem_frames = b.max_frames;
+    const size_t smem = (size_t)smem_frames * per_frame + 16;
+    // per device and cheap, so set on every launch
+    cudaFuncSetAttribute(k_mlpg_gv<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap);
+    cudaFuncSetAttribute(k_mlpg_gv<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap);
+    if (bw == 1) k_mlpg_gv<1><<<(unsigned)nthreads, 256, smem, stream>>>(b, s, plane, smem_frames);
+    else k_mlpg_gv<3><<<(unsigned)nthreads, 256, smem, stream>>>(b, s, plane, smem_frames);
+    return (int)cudaGetLastError();
+  }
+  switch (s.windows.band_width()) {  // other window shapes: the general kernel
     case 1: k_mlpg<1><<<blocks, threads, 0, stream>>>(b, s, plane); break;
     case 3: k_mlpg<3><<<blocks, threads, 0, stream>>>(b, s, plane); break;
     case 5: k_mlpg<5><<<blocks, threads, 0, stream>>>(b, s, plane); break;

@@ -429,6 +429,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   r->layout.durations = (const int32_t*)(di + o_dur);
   r->layout.frame_state = (int32_t*)(dw + w_fstate);
   r->layout.order = (const int32_t*)(di + o_order);
+  r->layout.max_frames = (int)r->max_frames;
   r->streams.n = (int)nstream;
   for (size_t s = 0; s < nstream; ++s) {
     jbk::StreamDev& sd = r->streams.s[s];

