@@ -110,8 +110,9 @@ struct VocoderDev {
   int frame_count;      // frames processed per utterance by this launch (clipped to its length)
 };
 
+// what: bit 0 = pitch period from lf0, bit 1 = b = mc2b(mcp)
 int launch_frame_prep(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,
-                      int64_t total_frames, cudaStream_t stream);
+                      int64_t total_frames, int what, cudaStream_t stream);
 int launch_pulse(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, int64_t total_samples,
                  cudaStream_t stream);
 int launch_excitation(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,

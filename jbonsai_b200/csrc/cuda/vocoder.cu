@@ -33,16 +33,20 @@ __device__ __forceinline__ int find_utt(const int64_t* frame_off, int n_utt, int
 }
 
 // ---------------------------------------------------------------- frame prep
-__global__ void k_frame_prep(VocoderParams p, VocoderDev d, int64_t total_frames) {
+// what: bit 0 = pitch period from lf0, bit 1 = b = mc2b(mcp) (the two halves depend on different streams)
+__global__ void k_frame_prep(VocoderParams p, VocoderDev d, int64_t total_frames, int what) {
   int64_t gf = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gf >= total_frames) return;
-  const double lf0 = d.lf0[gf];
-  double pitch = 0.0;
-  if (lf0 != kNoData) {
-    double l = lf0 < kMinLf0 ? kMinLf0 : (lf0 > kMaxLf0 ? kMaxLf0 : lf0);
-    pitch = p.rate / exp(l);
+  if (what & 1) {
+    const double lf0 = d.lf0[gf];
+    double pitch = 0.0;
+    if (lf0 != kNoData) {
+      double l = lf0 < kMinLf0 ? kMinLf0 : (lf0 > kMaxLf0 ? kMaxLf0 : lf0);
+      pitch = p.rate / exp(l);
+    }
+    d.pitch[gf] = pitch;
   }
-  d.pitch[gf] = pitch;
+  if (!(what & 2)) return;
   const double* c = d.mcp + gf * p.nmcp;
   double* b = d.b + gf * p.nmcp;
   const int last = p.nmcp - 1;
@@ -104,6 +108,43 @@ __global__ void __launch_bounds__(32) k_pulse(BatchLayout b, VocoderParams p, Vo
   if (d.state) {
     d.state[(int64_t)u * kVocStateDoubles + 223] = p_cur;
     d.state[(int64_t)u * kVocStateDoubles + 224] = cnt;
+  }
+}
+
+// Whole-utterance synthesis: the pitch counter restarts at every unvoiced -> voiced transition
+// (Excitation::start resets pitch_of_curr_point and pitch_counter when the previous frame was
+// unvoiced, excitation.rs:25-33), so each maximal run of voiced frames is an independent walk:
+// one thread per frame, the threads that sit on the first frame of a run walk it.
+__global__ void __launch_bounds__(128) k_pulse_runs(BatchLayout b, VocoderParams p, VocoderDev d,
+                                                    int64_t total_frames) {
+  const int64_t gf = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gf >= total_frames) return;
+  const double first = d.pitch[gf];
+  if (first == 0.0) return;
+  const int u = find_utt(b.frame_off, b.n_utt, gf);
+  const int64_t foff = b.frame_off[u];
+  const int T = (int)(b.frame_off[u + 1] - foff);
+  const int f = (int)(gf - foff);
+  if (f > 0 && d.pitch[gf - 1] != 0.0) return;  // not the start of a run
+  const int fp = p.fperiod;
+  const double fper = (double)fp;
+  double p_cur = first, cnt = first, inc = 0.0, pitch = first;
+  for (int ff = f;;) {
+    double* out = d.pulse + (foff + ff) * fp;
+    const double pitch_next = ff + 1 < T ? d.pitch[foff + ff + 1] : 0.0;
+    for (int i = 0; i < fp; ++i) {  // voiced_frame (excitation.rs:72-86)
+      cnt += 1.0;
+      if (cnt >= p_cur) {
+        cnt -= p_cur;
+        out[i] = sqrt(p_cur);
+      }
+      p_cur += inc;
+    }
+    p_cur = pitch;  // Excitation::end
+    if (pitch_next == 0.0) break;
+    ++ff;
+    pitch = pitch_next;
+    inc = (pitch - p_cur) / fper;  // Excitation::start with both pitches non-zero
   }
 }
 
@@ -601,11 +642,11 @@ int launch_gather_chunk(const BatchLayout& b, const VocoderParams& p, const Voco
 }
 
 int launch_frame_prep(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,
-                      int64_t total_frames, cudaStream_t stream) {
+                      int64_t total_frames, int what, cudaStream_t stream) {
   if (total_frames == 0) return 0;
   const int threads = 128;
   const int blocks = (int)((total_frames + threads - 1) / threads);
-  k_frame_prep<<<blocks, threads, 0, stream>>>(p, d, total_frames);
+  k_frame_prep<<<blocks, threads, 0, stream>>>(p, d, total_frames, what);
   return (int)cudaGetLastError();
 }
 
@@ -618,6 +659,12 @@ int launch_pulse(const BatchLayout& b, const VocoderParams& p, const VocoderDev&
   if (whole) {
     cudaError_t e = cudaMemsetAsync(d.pulse, 0, (size_t)total_samples * sizeof(double), stream);
     if (e != cudaSuccess) return (int)e;
+  }
+  if (whole && !d.state) {
+    const int64_t total_frames = total_samples / p.fperiod;
+    if (total_frames == 0) return 0;
+    k_pulse_runs<<<(unsigned)((total_frames + 127) / 128), 128, 0, stream>>>(b, p, d, total_frames);
+    return (int)cudaGetLastError();
   }
   k_pulse<<<(b.n_utt + threads - 1) / threads, threads, 0, stream>>>(b, p, d, whole ? 0 : 1);
   return (int)cudaGetLastError();

@@ -89,6 +89,38 @@ PinnedPool& pinned() {
 
 size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
+// Runs fn(0..n-1) on all host cores; rethrows the first jb::Error.
+template <class F>
+void parallel_for(size_t n, F fn) {
+  size_t nthreads = std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), n / 8 + 1);
+  if (nthreads <= 1) {
+    for (size_t i = 0; i < n; ++i) fn(i);
+    return;
+  }
+  std::atomic<size_t> next{0};
+  std::mutex emu;
+  std::unique_ptr<Error> err;
+  std::vector<std::thread> th;
+  for (size_t t = 0; t < nthreads; ++t)
+    th.emplace_back([&]() {
+      for (;;) {
+        const size_t i = next.fetch_add(1);
+        if (i >= n) return;
+        try {
+          fn(i);
+        } catch (const Error& e) {
+          std::lock_guard<std::mutex> g(emu);
+          if (!err) err.reset(new Error(e));
+        } catch (const std::exception& e) {
+          std::lock_guard<std::mutex> g(emu);
+          if (!err) err.reset(new Error(kErrArgument, e.what()));
+        }
+      }
+    });
+  for (auto& t : th) t.join();
+  if (err) throw *err;
+}
+
 struct Carver {  // carve aligned sections out of one allocation
   size_t off = 0;
   size_t take(size_t bytes) {
@@ -105,6 +137,8 @@ class DeviceCtx {
  public:
   int device;
   cudaStream_t stream = nullptr;
+  cudaStream_t stream2 = nullptr;  // side stream: LF0 solve -> pitch -> pulse train run beside MCP/LPF
+  cudaEvent_t evx[2];
   std::mutex mu;  // one in-flight batch per (engine, device)
   double* d_noise = nullptr;
   size_t noise_len = 0;
@@ -121,6 +155,8 @@ class DeviceCtx {
     if (dev < 0 || dev >= n) throw Error(kErrCuda, "CUDA device index out of range");
     JB_CUDA(cudaSetDevice(dev));
     JB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    JB_CUDA(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking));
+    for (auto& x : evx) JB_CUDA(cudaEventCreateWithFlags(&x, cudaEventDisableTiming));
     for (auto& x : ev) JB_CUDA(cudaEventCreate(&x));
   }
   ~DeviceCtx() {
@@ -128,6 +164,8 @@ class DeviceCtx {
     for (auto& kv : cached) cudaFree(kv.second);
     if (d_noise) cudaFree(d_noise);
     for (auto& x : ev) cudaEventDestroy(x);
+    for (auto& x : evx) cudaEventDestroy(x);
+    if (stream2) cudaStreamDestroy(stream2);
     if (stream) cudaStreamDestroy(stream);
   }
   void* dalloc(size_t bytes, size_t* cap) {
@@ -280,6 +318,12 @@ struct Engine::Resident {
   double* d_chunk = nullptr;  // streaming gather buffer
   size_t chunk_cap = 0;
   int64_t h2d_bytes = 0;
+  // kernels per pass: expand, 3 solves (+ GV kernels), 2 frame preps, pulse, excitation, MLSA
+  int launches() const {
+    int n = 1 + 3 + 2 + 3;
+    for (int i = 0; i < streams.n; ++i) n += streams.s[i].has_gv ? 1 : 0;
+    return n;
+  }
 };
 
 static jbk::WindowSet make_windows(const Windows& w) {
@@ -356,11 +400,12 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
                      [&](int32_t x, int32_t y) { return packs[x].nframes > packs[y].nframes; });
     if (n_utt) memcpy(h + o_order, order.data(), n_utt * 4);
   }
-  int64_t voiced_frames = 0;
-  for (size_t u = 0; u < n_utt; ++u) {
+  std::atomic<int64_t> voiced_frames{0};
+  auto pack_one = [&](size_t u) {
     const UtterancePack& p = packs[u];
     const size_t so = (size_t)state_off[u];
     if (p.nstates) memcpy(h + o_dur + so * 4, p.durations.data(), p.nstates * 4);
+    int64_t vf = 0;
     for (size_t s = 0; s < nstream && s < p.streams.size(); ++s) {
       const StreamPack& sp = p.streams[s];
       const size_t L = (size_t)dim[s] * nwin[s];
@@ -384,10 +429,12 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
       }
       if (s == 1)
         for (size_t i = 0; i < p.nstates; ++i)
-          if (sp.msd[i] > cond.msd_threshold[1]) voiced_frames += p.durations[i];
+          if (sp.msd[i] > cond.msd_threshold[1]) vf += p.durations[i];
     }
-  }
-  r->voiced_samples = voiced_frames * fperiod;
+    voiced_frames += vf;
+  };
+  parallel_for(n_utt, pack_one);  // the batching layer copies ~0.5 MB per utterance: use every core
+  r->voiced_samples = voiced_frames.load() * fperiod;
 
   JB_CUDA(cudaSetDevice(ctx->device));
   r->d_in = ctx->dalloc(r->in_bytes, &r->in_cap);
@@ -400,7 +447,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   Carver wk;
   const size_t w_fstate = wk.take((size_t)TF * 4);
   size_t w_left[3] = {0}, w_right[3] = {0}, w_vidx[3] = {0}, w_nv[3] = {0}, w_par[3];
-  size_t scratch_bytes = 0;
+  size_t scratch_bytes = 0, scratch1_bytes = 0;  // streams 0/2 run one after the other; stream 1 beside them
   for (size_t s = 0; s < nstream; ++s) {
     if (is_msd[s]) {
       w_left[s] = wk.take((size_t)TF * 4);
@@ -410,10 +457,12 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
     }
     w_par[s] = wk.take((size_t)TF * dim[s] * 8);
     jbk::WindowSet ws = make_windows(vs.stream_windows(s));
-    scratch_bytes = std::max(scratch_bytes, (size_t)jbk::mlpg_scratch_planes(ws.band_width(), has_gv[s]) *
+    size_t& sb = (s == 1) ? scratch1_bytes : scratch_bytes;
+    sb = std::max(sb, (size_t)jbk::mlpg_scratch_planes(ws.band_width(), has_gv[s]) *
                                                 (size_t)TF * dim[s] * 8);
   }
   const size_t w_scratch = wk.take(scratch_bytes);
+  const size_t w_scratch1 = wk.take(scratch1_bytes);
   const size_t w_b = wk.take((size_t)TF * dim[0] * 8);
   const size_t w_pitch = wk.take((size_t)TF * 8);
   const size_t w_pulse = wk.take((size_t)r->total_samples * 8);
@@ -450,7 +499,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
     sd.right = is_msd[s] ? (int32_t*)(dw + w_right[s]) : nullptr;
     sd.vidx = is_msd[s] ? (int32_t*)(dw + w_vidx[s]) : nullptr;
     sd.nvoiced = is_msd[s] ? (int32_t*)(dw + w_nv[s]) : nullptr;
-    sd.scratch = (double*)(dw + w_scratch);
+    sd.scratch = (double*)(dw + (s == 1 ? w_scratch1 : w_scratch));
     sd.par = (double*)(dw + w_par[s]);
   }
   r->vp.nmcp = dim[0];
@@ -486,18 +535,29 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   return r.release();
 }
 
-static void launch_mlpg_all(Engine::Resident* r) {
-  cudaStream_t st = r->ctx->stream;
+// MLPG for the three streams + the per-frame vocoder inputs. The LF0 chain (solve, GV, pitch
+// period and, for whole-utterance synthesis, the pulse train) only has n_utt systems, so it runs
+// on the side stream beside the MCP/LPF solves instead of in front of them.
+static void launch_mlpg_all(Engine::Resident* r, bool with_pulse) {
+  DeviceCtx* c = r->ctx;
+  cudaStream_t st = c->stream, sb = c->stream2;
   JB_LAUNCH(jbk::launch_expand(r->layout, r->streams, st));
-  for (int s = 0; s < r->streams.n; ++s)
-    JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[s], r->total_frames, st));
-  JB_LAUNCH(jbk::launch_frame_prep(r->layout, r->vp, r->vd, r->total_frames, st));
+  JB_CUDA(cudaEventRecord(c->evx[0], st));
+  JB_CUDA(cudaStreamWaitEvent(sb, c->evx[0], 0));
+  JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[1], r->total_frames, sb));
+  JB_LAUNCH(jbk::launch_frame_prep(r->layout, r->vp, r->vd, r->total_frames, 1, sb));
+  if (with_pulse) JB_LAUNCH(jbk::launch_pulse(r->layout, r->vp, r->vd, r->total_samples, sb));
+  JB_CUDA(cudaEventRecord(c->evx[1], sb));
+  JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[0], r->total_frames, st));
+  JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[2], r->total_frames, st));
+  JB_LAUNCH(jbk::launch_frame_prep(r->layout, r->vp, r->vd, r->total_frames, 2, st));
+  JB_CUDA(cudaStreamWaitEvent(st, c->evx[1], 0));
 }
 
 static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_excitation,
-                           cudaEvent_t after_exc) {
+                           cudaEvent_t after_exc, bool pulse_done) {
   cudaStream_t st = r->ctx->stream;
-  JB_LAUNCH(jbk::launch_pulse(r->layout, r->vp, r->vd, r->total_samples, st));
+  if (!pulse_done) JB_LAUNCH(jbk::launch_pulse(r->layout, r->vp, r->vd, r->total_samples, st));
   JB_LAUNCH(jbk::launch_excitation(r->layout, r->vp, r->vd, r->total_frames, st));
   if (after_exc) JB_CUDA(cudaEventRecord(after_exc, st));
   if (!stop_after_excitation) JB_LAUNCH(jbk::launch_mlsa(r->layout, r->vp, r->vd, variant, st));
@@ -518,9 +578,9 @@ double Engine::run_resident(Resident* r, BatchTimings* tm) const {
   std::lock_guard<std::mutex> g(c->mu);
   JB_CUDA(cudaSetDevice(c->device));
   JB_CUDA(cudaEventRecord(c->ev[2], c->stream));
-  launch_mlpg_all(r);
+  launch_mlpg_all(r, true);
   JB_CUDA(cudaEventRecord(c->ev[3], c->stream));
-  launch_vocoder(r, mlsa_variant, false, c->ev[4]);
+  launch_vocoder(r, mlsa_variant, false, c->ev[4], true);
   JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
   JB_CUDA(cudaEventSynchronize(c->ev[5]));
   float total = 0, a = 0, b = 0, m = 0;
@@ -537,7 +597,7 @@ double Engine::run_resident(Resident* r, BatchTimings* tm) const {
     tm->total_samples = r->total_samples;
     tm->voiced_samples = r->voiced_samples;
     tm->h2d_bytes = r->h2d_bytes;
-    tm->launches = 1 + r->streams.n + 1 + 3;
+    tm->launches = r->launches();
   }
   return total;
 }
@@ -622,9 +682,9 @@ void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts,
       BatchTimings& t = tms[k];
       t.pack_ms = now_ms() - p0;
       JB_CUDA(cudaEventRecord(c->ev[2], c->stream));
-      launch_mlpg_all(r);
+      launch_mlpg_all(r, true);
       JB_CUDA(cudaEventRecord(c->ev[3], c->stream));
-      launch_vocoder(r, mlsa_variant, dbg && dbg->stop_after_excitation, c->ev[4]);
+      launch_vocoder(r, mlsa_variant, dbg && dbg->stop_after_excitation, c->ev[4], true);
       JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
       if (r->total_samples)
         JB_CUDA(cudaMemcpyAsync(host + (*out_off)[u0], r->vd.wave, (size_t)r->total_samples * 8,
@@ -660,7 +720,7 @@ void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts,
       t.total_frames = r->total_frames;
       t.total_samples = r->total_samples;
       t.voiced_samples = r->voiced_samples;
-      t.launches = 1 + r->streams.n + 1 + 3;
+      t.launches = r->launches();
     } catch (const Error& e) {
       errs[k].reset(new Error(e));
     } catch (const std::exception& e) {
@@ -709,7 +769,7 @@ Stream::Stream(const Engine* e, const std::vector<std::vector<std::string>>& utt
   std::lock_guard<std::mutex> g(c->mu);
   r_ = Engine::make_resident(*e, c, packs.data(), packs.size(), true, e->condition);
   // MLPG for the whole utterance up front, like Engine::generator (engine.rs:333-357)
-  launch_mlpg_all(r_);
+  launch_mlpg_all(r_, false);
   if (r_->n_utt)
     JB_CUDA(cudaMemsetAsync(r_->vd.state, 0, (size_t)r_->n_utt * jbk::kVocStateDoubles * 8, c->stream));
   JB_CUDA(cudaStreamSynchronize(c->stream));
@@ -734,7 +794,7 @@ double Stream::step(size_t n_frames, double* out, size_t* written) {
   r_->vd.frame_begin = (int)next_;
   r_->vd.frame_count = (int)n_frames;
   JB_CUDA(cudaEventRecord(c->ev[2], c->stream));
-  launch_vocoder(r_, e_->mlsa_variant, false, nullptr);
+  launch_vocoder(r_, e_->mlsa_variant, false, nullptr, false);
   JB_LAUNCH(jbk::launch_gather_chunk(r_->layout, r_->vp, r_->vd, r_->d_chunk, c->stream));
   JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
   JB_CUDA(cudaMemcpyAsync(out, r_->d_chunk, n * chunk * 8, cudaMemcpyDeviceToHost, c->stream));

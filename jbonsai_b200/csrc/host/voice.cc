@@ -90,7 +90,19 @@ void Model::get_index(size_t state_index, const std::string& label, long* tree_i
       ti = (long)i;
       break;
     }
-  const Tree& tree = trees[ti < 0 ? 0 : (size_t)ti];
+  const size_t tsel = ti < 0 ? 0 : (size_t)ti;
+  const Tree& tree = trees[tsel];
+  *tree_index = ti < 0 ? -1 : ti + 2;
+  // cache: 0 = not resolved yet, -1 = no leaf, else the 1-based pdf index
+  LabelCache::Shard& sh = cache->shards[std::hash<std::string>()(label) % LabelCache::kShards];
+  {
+    std::lock_guard<std::mutex> g(sh.mu);
+    auto it = sh.map.find(label);
+    if (it != sh.map.end() && it->second[tsel] != 0) {
+      *pdf_index = it->second[tsel];
+      return;
+    }
+  }
   long pi = -1;
   size_t node = 0;
   while (node < tree.nodes.size()) {
@@ -101,8 +113,16 @@ void Model::get_index(size_t state_index, const std::string& label, long* tree_i
     }
     node = questions[(size_t)nd.question].test(label) ? nd.yes : nd.no;
   }
-  *tree_index = ti < 0 ? -1 : ti + 2;
   *pdf_index = pi;
+  {
+    std::lock_guard<std::mutex> g(sh.mu);
+    auto it = sh.map.find(label);
+    if (it == sh.map.end()) {
+      if (sh.map.size() >= LabelCache::kMaxPerShard) return;
+      it = sh.map.emplace(label, std::vector<int32_t>(trees.size(), 0)).first;
+    }
+    it->second[tsel] = (int32_t)pi;
+  }
 }
 
 const ModelParameter& Model::get_parameter(size_t state_index, const std::string& label) const {

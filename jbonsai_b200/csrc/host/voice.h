@@ -10,7 +10,9 @@
 #include <cstdint>
 #include <memory>
 #include <stdexcept>
+#include <mutex>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 namespace jb {
@@ -84,10 +86,25 @@ struct Tree {
   std::vector<TreeNode> nodes;
 };
 
+// Leaf indices already resolved for a label string, per tree (host front-end cache: a decision
+// tree walk costs a few hundred wildcard matches, and batches repeat labels). Bounded; sharded
+// so that the front-end threads of a batch do not serialise on it. Results are exactly the tree
+// walk's (Model::get_index computes on a miss).
+struct LabelCache {
+  static constexpr size_t kShards = 64;
+  static constexpr size_t kMaxPerShard = 4096;
+  struct Shard {
+    std::mutex mu;
+    std::unordered_map<std::string, std::vector<int32_t>> map;
+  };
+  Shard shards[kShards];
+};
+
 struct Model {
   std::vector<Question> questions;
   std::vector<Tree> trees;
   std::vector<std::vector<ModelParameter>> pdf;  // [tree][pdf_index-1]
+  std::shared_ptr<LabelCache> cache = std::make_shared<LabelCache>();
 
   // (tree_index + 2, pdf_index) like Model::get_index (voice/model.rs:50-67); -1 = None.
   void get_index(size_t state_index, const std::string& label, long* tree_index,
