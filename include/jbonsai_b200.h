@@ -65,8 +65,14 @@ int jb_engine_set_interpolation_weight(jb_engine* e, int kind, size_t stream, co
 /* CUDA devices used by this engine (default: device 0). A batch is sharded over them by
  * contiguous utterance ranges balanced by frame count (no collective). */
 int jb_engine_set_devices(jb_engine* e, const int* devices, size_t n);
-/* MLSA kernel variant (-1 = default). For A/B measurements only. */
+/* MLSA kernel variant (-1 = default = 3: time-segmented; 2: one warp per utterance, sequential;
+ * 0: reference operation order). For A/B measurements only. */
 int jb_engine_set_mlsa_variant(jb_engine* e, int variant);
+/* Variant 3 cuts utterances into time segments that are filtered concurrently; each segment first
+ * filters `warm_frames` frames ahead of its own range from a zero state (default 40). The states on
+ * both sides of every cut are compared on the device; when they differ by more than `cut_tolerance`
+ * (default 1e-8, absolute) the batch is filtered again by the sequential kernel. */
+int jb_engine_set_mlsa_segmenting(jb_engine* e, int warm_frames, double cut_tolerance);
 
 /* Engine::synthesize (src/engine.rs:294-296): labels -> raw f64 samples (not clipped).
  * *out is owned by the library: release with jb_free(). Empty input -> *out_len = 0. */
@@ -75,10 +81,11 @@ int jb_engine_synthesize(const jb_engine* e, const char* const* lines, size_t n_
 
 /* Batch of utterances (no reference equivalent; BASELINE configs 3-5). Utterance u owns
  * lines[line_off[u] .. line_off[u+1]). out_off must hold n_utt+1 entries: utterance u's samples
- * are (*out)[out_off[u] .. out_off[u+1]), in input order. timings (optional, 16 doubles):
+ * are (*out)[out_off[u] .. out_off[u+1]), in input order. timings (optional, 20 doubles):
  * [0] host front-end ms [1] pack ms [2] H2D ms [3] kernels ms [4] D2H ms [5] MLPG ms
  * [6] excitation ms [7] MLSA ms [8] H2D bytes [9] D2H bytes [10] frames [11] samples
- * [12] voiced samples [13] kernel launches. */
+ * [12] voiced samples [13] kernel launches [14] MLSA time segments [15] frames filtered including
+ * warm-up [16] largest state mismatch at a cut [17] 1 if the sequential kernel redid the batch. */
 int jb_engine_synthesize_batch(const jb_engine* e, const char* const* lines, const size_t* line_off,
                                size_t n_utt, double** out, size_t* out_off, double* timings);
 void jb_free(void* p);

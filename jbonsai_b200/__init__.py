@@ -23,7 +23,7 @@ C_ABI_SYMBOLS = [
     "jb_last_error", "jb_version", "jb_device_count", "jb_device_measure_peaks", "jb_engine_load",
     "jb_engine_load_from_bytes", "jb_engine_free", "jb_engine_set_condition",
     "jb_engine_get_condition", "jb_engine_set_interpolation_weight", "jb_engine_set_devices",
-    "jb_engine_set_mlsa_variant", "jb_engine_synthesize", "jb_engine_synthesize_batch", "jb_free",
+    "jb_engine_set_mlsa_variant", "jb_engine_set_mlsa_segmenting", "jb_engine_synthesize", "jb_engine_synthesize_batch", "jb_free",
     "jb_engine_debug_batch", "jb_engine_noise", "jb_engine_durations", "jb_engine_tree_index",
     "jb_engine_stream_parameters", "jb_engine_duration_parameters", "jb_engine_gv_parameters",
     "jb_resident_prepare", "jb_resident_run", "jb_resident_fetch", "jb_resident_free",
@@ -122,7 +122,8 @@ def _take(ptr, n: int) -> np.ndarray:
 
 TIMING_KEYS = ["host_frontend_ms", "pack_ms", "h2d_ms", "kernels_ms", "d2h_ms", "mlpg_ms",
                "excitation_ms", "mlsa_ms", "h2d_bytes", "d2h_bytes", "frames", "samples",
-               "voiced_samples", "launches"]
+               "voiced_samples", "launches", "mlsa_segments", "mlsa_seg_frames", "mlsa_cut_worst",
+               "mlsa_fallback"]
 
 
 class Engine:
@@ -182,6 +183,9 @@ class Engine:
     def set_mlsa_variant(self, v: int) -> None:
         _check(lib.jb_engine_set_mlsa_variant(self._h, int(v)))
 
+    def set_mlsa_segmenting(self, warm_frames: int = 40, cut_tolerance: float = 1e-8) -> None:
+        _check(lib.jb_engine_set_mlsa_segmenting(self._h, int(warm_frames), C.c_double(cut_tolerance)))
+
     # -- Engine::synthesize (src/engine.rs:294-296)
     def synthesize(self, lines: Sequence[str]) -> np.ndarray:
         arr, n = _lines(lines)
@@ -195,7 +199,7 @@ class Engine:
         arr, offs, n = _flatten(utts)
         out = C.POINTER(C.c_double)()
         out_off = (C.c_size_t * (n + 1))()
-        tm = (C.c_double * 16)()
+        tm = (C.c_double * 20)()
         _check(lib.jb_engine_synthesize_batch(self._h, arr, offs, C.c_size_t(n), C.byref(out),
                                               out_off, tm))
         off = np.array(list(out_off), dtype=np.int64)
@@ -209,7 +213,7 @@ class Engine:
         arr, offs, n = flat
         out = C.POINTER(C.c_double)()
         out_off = (C.c_size_t * (n + 1))()
-        tm = (C.c_double * 16)()
+        tm = (C.c_double * 20)()
         _check(lib.jb_engine_synthesize_batch(self._h, arr, offs, C.c_size_t(n), C.byref(out),
                                               out_off, tm))
         return out, out_off, {k: tm[i] for i, k in enumerate(TIMING_KEYS)}
@@ -318,7 +322,7 @@ class Resident:
 
     def run(self) -> dict:
         ms = C.c_double()
-        tm = (C.c_double * 16)()
+        tm = (C.c_double * 20)()
         _check(lib.jb_resident_run(self._e._h, self._h, C.byref(ms), tm))
         d = {k: tm[i] for i, k in enumerate(TIMING_KEYS)}
         d["device_ms"] = ms.value

@@ -51,10 +51,11 @@ std::vector<std::vector<std::string>> to_utts(const char* const* lines, const si
 
 void fill_timings(const jb::BatchTimings& t, double* out) {
   if (!out) return;
-  const double v[16] = {t.host_frontend_ms, t.pack_ms, t.h2d_ms, t.kernels_ms, t.d2h_ms, t.mlpg_ms,
+  const double v[20] = {t.host_frontend_ms, t.pack_ms, t.h2d_ms, t.kernels_ms, t.d2h_ms, t.mlpg_ms,
                         t.excitation_ms, t.mlsa_ms, (double)t.h2d_bytes, (double)t.d2h_bytes,
                         (double)t.total_frames, (double)t.total_samples, (double)t.voiced_samples,
-                        (double)t.launches, 0, 0};
+                        (double)t.launches, (double)t.mlsa_segments, (double)t.mlsa_seg_frames,
+                        t.mlsa_cut_worst, (double)t.mlsa_fallback, 0, 0};
   memcpy(out, v, sizeof v);
 }
 
@@ -137,6 +138,15 @@ int jb_engine_set_devices(jb_engine* e, const int* devices, size_t n) {
 int jb_engine_set_mlsa_variant(jb_engine* e, int variant) {
   e->e->mlsa_variant = variant;
   return JB_OK;
+}
+
+int jb_engine_set_mlsa_segmenting(jb_engine* e, int warm_frames, double cut_tolerance) {
+  JB_TRY
+  if (warm_frames < 0 || !(cut_tolerance >= 0.0))
+    throw jb::Error(jb::kErrArgument, "warm_frames and cut_tolerance must be non-negative");
+  e->e->mlsa_warm_frames = warm_frames;
+  e->e->mlsa_cut_tolerance = cut_tolerance;
+  JB_CATCH
 }
 
 int jb_engine_synthesize_batch(const jb_engine* e, const char* const* lines, const size_t* line_off,

@@ -104,7 +104,8 @@ struct VocoderDev {
   double* b;            // [total_frames][nmcp]  mc2b(mcp)   (out of frame_prep)
   double* pitch;        // [total_frames]        p per frame (out of frame_prep)
   double* pulse;        // [total_samples]       pulse amplitude or 0 (out of pitch kernel)
-  double* wave;         // [total_samples]       excitation*gain, then filtered in place
+  double* wave;         // [total_samples]       excitation*gain; variants 0-2 filter it in place
+  double* out;          // [total_samples]       variant 3 only: filtered waveform (wave stays the input)
   double* state;        // [n_utt][kVocStateDoubles] or nullptr (whole-utterance synthesis)
   int frame_begin;      // first frame (per utterance) processed by this launch
   int frame_count;      // frames processed per utterance by this launch (clipped to its length)
@@ -122,6 +123,24 @@ int launch_excitation(const BatchLayout& b, const VocoderParams& p, const Vocode
 int launch_mlsa_v2(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, cudaStream_t stream);
 int launch_mlsa(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, int variant,
                 cudaStream_t stream);
+
+// Variant 3 (mlsa_seg.cu): utterances cut into time segments that are filtered independently.
+// Segment = frames [begin, end) of utterance `utt`; filtering starts at frame `warm` <= begin from a
+// zero state (warm == begin == 0 for the first segment) and the output of [warm, begin) is discarded.
+// `prev` = id of the segment that ends where this one begins (-1 for the first of an utterance).
+struct MlsaSegment {
+  int32_t utt, begin, end, warm, prev;
+};
+constexpr int kMlsaSegStateDoubles = 192;  // per (segment, side): 5 stages x (34 taps, d11, d12, d22)
+struct MlsaSegments {
+  int n_seg;
+  const MlsaSegment* seg;  // [n_seg], six consecutive segments share a warp (host sorts by length)
+  double* state;           // [n_seg][2][kMlsaSegStateDoubles] cut-check taps, or nullptr
+};
+// Filters d.wave into d.out; then (state != nullptr) writes the largest state mismatch over all
+// cuts into *worst (device), for the host to compare with its tolerance.
+int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, const MlsaSegments& sg,
+                   double* worst, cudaStream_t stream);
 
 // Streaming: copy frames [frame_begin, frame_begin+frame_count) of every utterance into
 // chunk[n_utt][frame_count*fperiod] (zero padded past the end of an utterance).

@@ -29,6 +29,9 @@ namespace jb {
 
 namespace {
 
+constexpr int kSegWarpsPerSmsp = 2;  // resident warps per scheduler of k_mlsa_v3 (206 registers)
+constexpr int kSegMinFrames = 48;    // shortest own range worth a segment of its own
+
 double now_ms() {
   using namespace std::chrono;
   return duration<double, std::milli>(steady_clock::now().time_since_epoch()).count();
@@ -144,6 +147,8 @@ class DeviceCtx {
   size_t noise_len = 0;
   cudaEvent_t ev[8];
   std::multimap<size_t, void*> cached;  // freed device blocks
+  int sm_count = 148;
+  double* h_worst = nullptr;  // pinned: MLSA variant 3 cut-check result
 
   explicit DeviceCtx(int dev) : device(dev) {
     int n = 0;
@@ -158,11 +163,15 @@ class DeviceCtx {
     JB_CUDA(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking));
     for (auto& x : evx) JB_CUDA(cudaEventCreateWithFlags(&x, cudaEventDisableTiming));
     for (auto& x : ev) JB_CUDA(cudaEventCreate(&x));
+    JB_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+    JB_CUDA(cudaMallocHost((void**)&h_worst, sizeof(double)));
+    *h_worst = 0.0;
   }
   ~DeviceCtx() {
     cudaSetDevice(device);
     for (auto& kv : cached) cudaFree(kv.second);
     if (d_noise) cudaFree(d_noise);
+    if (h_worst) cudaFreeHost(h_worst);
     for (auto& x : ev) cudaEventDestroy(x);
     for (auto& x : evx) cudaEventDestroy(x);
     if (stream2) cudaStreamDestroy(stream2);
@@ -318,9 +327,16 @@ struct Engine::Resident {
   double* d_chunk = nullptr;  // streaming gather buffer
   size_t chunk_cap = 0;
   int64_t h2d_bytes = 0;
-  // kernels per pass: expand, 3 solves (+ GV kernels), 2 frame preps, pulse, excitation, MLSA
+  // MLSA variant 3: time segments (empty when the batch is streamed)
+  jbk::MlsaSegments segs{};
+  double* d_worst = nullptr;
+  int64_t seg_frames = 0;          // frames filtered including warm-up
+  bool used_fallback = false;      // the last pass re-ran the sequential kernel
+  const double* result = nullptr;  // device waveform of the last pass
+  // kernels per pass: expand, 3 solves (+ GV kernels), 2 frame preps, pulse (memset excluded),
+  // excitation, MLSA (+ cut check for variant 3)
   int launches() const {
-    int n = 1 + 3 + 2 + 3;
+    int n = 1 + 3 + 2 + 3 + (segs.n_seg > 0 ? 1 : 0);
     for (int i = 0; i < streams.n; ++i) n += streams.s[i].has_gv ? 1 : 0;
     return n;
   }
@@ -369,6 +385,50 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   const size_t o_soff = in.take((n_utt + 1) * 8), o_foff = in.take((n_utt + 1) * 8);
   const size_t o_dur = in.take((size_t)TS * 4);
   const size_t o_order = in.take(n_utt * 4);
+  // MLSA variant 3: cut every utterance into time segments (kernels.h). The target is enough
+  // segments for kSegWarpsPerSmsp warps of six on every warp scheduler; a segment is never shorter
+  // than kSegMinFrames of its own, so small batches simply run fewer warps.
+  std::vector<jbk::MlsaSegment> segs;
+  if (!streaming && TF > 0) {
+    const int64_t W = e.mlsa_warm_frames;
+    const int64_t target = (int64_t)ctx->sm_count * 4 * kSegWarpsPerSmsp * 6;
+    const int64_t S = std::max<int64_t>(kSegMinFrames, (TF + target - 1) / target);
+    for (size_t u = 0; u < n_utt; ++u) {
+      const int64_t T = (int64_t)packs[u].nframes;
+      if (T <= 0) continue;
+      int64_t G = std::max<int64_t>(1, (T + S / 2) / S);
+      // equal filtered length L for every segment: the first owns L frames, the others L - W
+      while (G > 1 && (T + (G - 1) * W) / G - W < kSegMinFrames / 2) --G;
+      const int64_t L = (T + (G - 1) * W + G - 1) / G;
+      int64_t begin = 0;
+      for (int64_t k = 0; k < G && begin < T; ++k) {
+        int64_t end = (k == G - 1) ? T : std::min<int64_t>(T, begin + (k == 0 ? L : L - W));
+        jbk::MlsaSegment sg;
+        sg.utt = (int32_t)u;
+        sg.begin = (int32_t)begin;
+        sg.end = (int32_t)end;
+        sg.warm = (int32_t)std::max<int64_t>(0, begin - W);
+        sg.prev = k == 0 ? -1 : (int32_t)(segs.size() - 1);  // index before sorting, remapped below
+        segs.push_back(sg);
+        begin = end;
+      }
+    }
+    // six consecutive segments share a warp and run as long as the longest of them
+    std::vector<int32_t> perm(segs.size()), where(segs.size());
+    for (size_t i = 0; i < segs.size(); ++i) perm[i] = (int32_t)i;
+    std::stable_sort(perm.begin(), perm.end(), [&](int32_t x, int32_t y) {
+      return segs[x].end - segs[x].warm > segs[y].end - segs[y].warm;
+    });
+    for (size_t i = 0; i < perm.size(); ++i) where[perm[i]] = (int32_t)i;
+    std::vector<jbk::MlsaSegment> sorted(segs.size());
+    for (size_t i = 0; i < perm.size(); ++i) {
+      sorted[i] = segs[perm[i]];
+      if (sorted[i].prev >= 0) sorted[i].prev = where[sorted[i].prev];
+      r->seg_frames += sorted[i].end - sorted[i].warm;
+    }
+    segs.swap(sorted);
+  }
+  const size_t o_segs = in.take(segs.size() * sizeof(jbk::MlsaSegment));
   size_t o_mean[3], o_vari[3], o_msd[3], o_gvm[3], o_gvv[3], o_gsw[3];
   int dim[3], nwin[3], is_msd[3], has_gv[3];
   for (size_t s = 0; s < nstream; ++s) {
@@ -393,6 +453,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   } rel{h};
   memcpy(h + o_soff, state_off.data(), (n_utt + 1) * 8);
   memcpy(h + o_foff, r->frame_off.data(), (n_utt + 1) * 8);
+  if (!segs.empty()) memcpy(h + o_segs, segs.data(), segs.size() * sizeof(jbk::MlsaSegment));
   {  // longest utterance first: the per-utterance kernels are scheduled block by block in this order
     std::vector<int32_t> order(n_utt);
     for (size_t u = 0; u < n_utt; ++u) order[u] = (int32_t)u;
@@ -468,6 +529,9 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   const size_t w_pulse = wk.take((size_t)r->total_samples * 8);
   const size_t w_wave = wk.take((size_t)r->total_samples * 8);
   const size_t w_state = streaming ? wk.take(n_utt * jbk::kVocStateDoubles * 8) : 0;
+  const size_t w_out = segs.empty() ? 0 : wk.take((size_t)r->total_samples * 8);
+  const size_t w_segstate = segs.empty() ? 0 : wk.take(segs.size() * 2 * jbk::kMlsaSegStateDoubles * 8);
+  const size_t w_worst = wk.take(8);
   r->d_work = ctx->dalloc(wk.off, &r->work_cap);
   uint8_t* di = (uint8_t*)r->d_in;
   uint8_t* dw = (uint8_t*)r->d_work;
@@ -516,6 +580,12 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   r->vd.pulse = (double*)(dw + w_pulse);
   r->vd.wave = (double*)(dw + w_wave);
   r->vd.state = streaming ? (double*)(dw + w_state) : nullptr;
+  r->vd.out = segs.empty() ? nullptr : (double*)(dw + w_out);
+  r->segs.n_seg = (int)segs.size();
+  r->segs.seg = (const jbk::MlsaSegment*)(di + o_segs);
+  r->segs.state = segs.empty() ? nullptr : (double*)(dw + w_segstate);
+  r->d_worst = (double*)(dw + w_worst);
+  r->result = r->vd.wave;
   r->vd.frame_begin = 0;
   r->vd.frame_count = -1;
 
@@ -560,7 +630,33 @@ static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_exc
   if (!pulse_done) JB_LAUNCH(jbk::launch_pulse(r->layout, r->vp, r->vd, r->total_samples, st));
   JB_LAUNCH(jbk::launch_excitation(r->layout, r->vp, r->vd, r->total_frames, st));
   if (after_exc) JB_CUDA(cudaEventRecord(after_exc, st));
-  if (!stop_after_excitation) JB_LAUNCH(jbk::launch_mlsa(r->layout, r->vp, r->vd, variant, st));
+  r->result = r->vd.wave;
+  r->used_fallback = false;
+  if (stop_after_excitation) return;
+  const bool v3 = (variant < 0 || variant == 3) && r->segs.n_seg > 0 && r->vp.nmcp == 35 &&
+                  r->vp.fperiod % 16 == 0 && r->vd.frame_begin == 0 && r->vd.frame_count < 0;
+  if (v3) {
+    JB_LAUNCH(jbk::launch_mlsa_v3(r->layout, r->vp, r->vd, r->segs, r->d_worst, st));
+    JB_CUDA(cudaMemcpyAsync(r->ctx->h_worst, r->d_worst, sizeof(double), cudaMemcpyDeviceToHost, st));
+    r->result = r->vd.out;
+  } else {
+    JB_LAUNCH(jbk::launch_mlsa(r->layout, r->vp, r->vd, variant == 3 ? -1 : variant, st));
+  }
+}
+
+// Variant 3 epilogue, after the stream has been synchronised: when the two sides of some cut
+// disagree (the warm-up was too short for this input) the sequential kernel redoes the batch.
+// Returns true when it did; the caller then repeats whatever it had queued behind the filter.
+static bool mlsa_cut_check_failed(Engine::Resident* r, double tol) {
+  if (r->result != r->vd.out || r->vd.out == nullptr) return false;
+  const double w = *r->ctx->h_worst;
+  return !(w <= tol);  // NaN counts as a failed cut
+}
+static void mlsa_sequential_rerun(Engine::Resident* r) {
+  cudaStream_t st = r->ctx->stream;
+  JB_LAUNCH(jbk::launch_mlsa(r->layout, r->vp, r->vd, 2, st));
+  r->result = r->vd.wave;
+  r->used_fallback = true;
 }
 
 Engine::Resident* Engine::prepare(const std::vector<std::vector<std::string>>& utts,
@@ -583,6 +679,11 @@ double Engine::run_resident(Resident* r, BatchTimings* tm) const {
   launch_vocoder(r, mlsa_variant, false, c->ev[4], true);
   JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
   JB_CUDA(cudaEventSynchronize(c->ev[5]));
+  if (mlsa_cut_check_failed(r, mlsa_cut_tolerance)) {  // timed too: ev[5] is recorded again
+    mlsa_sequential_rerun(r);
+    JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
+    JB_CUDA(cudaEventSynchronize(c->ev[5]));
+  }
   float total = 0, a = 0, b = 0, m = 0;
   JB_CUDA(cudaEventElapsedTime(&total, c->ev[2], c->ev[5]));
   JB_CUDA(cudaEventElapsedTime(&a, c->ev[2], c->ev[3]));
@@ -597,7 +698,11 @@ double Engine::run_resident(Resident* r, BatchTimings* tm) const {
     tm->total_samples = r->total_samples;
     tm->voiced_samples = r->voiced_samples;
     tm->h2d_bytes = r->h2d_bytes;
-    tm->launches = r->launches();
+    tm->launches = r->launches() + (r->used_fallback ? 1 : 0);
+    tm->mlsa_segments = r->segs.n_seg;
+    tm->mlsa_seg_frames = r->seg_frames;
+    tm->mlsa_cut_worst = r->segs.n_seg > 0 ? *c->h_worst : 0.0;
+    tm->mlsa_fallback = r->used_fallback ? 1 : 0;
   }
   return total;
 }
@@ -607,7 +712,8 @@ void Engine::fetch_resident(Resident* r, double** out, std::vector<size_t>* out_
   std::lock_guard<std::mutex> g(c->mu);
   JB_CUDA(cudaSetDevice(c->device));
   double* h = (double*)pinned().alloc((size_t)r->total_samples * 8);
-  cudaError_t e = cudaMemcpyAsync(h, r->vd.wave, (size_t)r->total_samples * 8, cudaMemcpyDeviceToHost, c->stream);
+  cudaError_t e = cudaMemcpyAsync(h, r->result ? r->result : r->vd.wave, (size_t)r->total_samples * 8,
+                                  cudaMemcpyDeviceToHost, c->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
   if (e != cudaSuccess) {
     pinned().release(h);
@@ -687,7 +793,7 @@ void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts,
       launch_vocoder(r, mlsa_variant, dbg && dbg->stop_after_excitation, c->ev[4], true);
       JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
       if (r->total_samples)
-        JB_CUDA(cudaMemcpyAsync(host + (*out_off)[u0], r->vd.wave, (size_t)r->total_samples * 8,
+        JB_CUDA(cudaMemcpyAsync(host + (*out_off)[u0], r->result, (size_t)r->total_samples * 8,
                                 cudaMemcpyDeviceToHost, c->stream));
       JB_CUDA(cudaEventRecord(c->ev[6], c->stream));
       if (dbg) {
@@ -708,6 +814,19 @@ void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts,
         dbg->frame_off = r->frame_off;
       }
       JB_CUDA(cudaStreamSynchronize(c->stream));
+      if (mlsa_cut_check_failed(r, mlsa_cut_tolerance)) {
+        // the copy above carried a waveform with a bad cut: redo the filter sequentially, copy again
+        mlsa_sequential_rerun(r);
+        JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
+        JB_CUDA(cudaMemcpyAsync(host + (*out_off)[u0], r->result, (size_t)r->total_samples * 8,
+                                cudaMemcpyDeviceToHost, c->stream));
+        JB_CUDA(cudaEventRecord(c->ev[6], c->stream));
+        JB_CUDA(cudaStreamSynchronize(c->stream));
+      }
+      t.mlsa_segments = r->segs.n_seg;
+      t.mlsa_seg_frames = r->seg_frames;
+      t.mlsa_cut_worst = r->segs.n_seg > 0 && !(dbg && dbg->stop_after_excitation) ? *c->h_worst : 0.0;
+      t.mlsa_fallback = r->used_fallback ? 1 : 0;
       float f = 0;
       JB_CUDA(cudaEventElapsedTime(&f, c->ev[0], c->ev[1])); t.h2d_ms = f;
       JB_CUDA(cudaEventElapsedTime(&f, c->ev[2], c->ev[5])); t.kernels_ms = f;
@@ -720,7 +839,7 @@ void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts,
       t.total_frames = r->total_frames;
       t.total_samples = r->total_samples;
       t.voiced_samples = r->voiced_samples;
-      t.launches = r->launches();
+      t.launches = r->launches() + (r->used_fallback ? 1 : 0);
     } catch (const Error& e) {
       errs[k].reset(new Error(e));
     } catch (const std::exception& e) {
@@ -756,6 +875,10 @@ void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts,
       tm->total_samples += t.total_samples;
       tm->voiced_samples += t.voiced_samples;
       tm->launches += t.launches;
+      tm->mlsa_segments += t.mlsa_segments;
+      tm->mlsa_seg_frames += t.mlsa_seg_frames;
+      tm->mlsa_cut_worst = std::max(tm->mlsa_cut_worst, t.mlsa_cut_worst);
+      tm->mlsa_fallback += t.mlsa_fallback;
     }
   }
   *out = host;

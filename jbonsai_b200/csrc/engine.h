@@ -35,6 +35,11 @@ struct BatchTimings {
   int64_t h2d_bytes = 0, d2h_bytes = 0;
   int64_t total_frames = 0, total_samples = 0, voiced_samples = 0;
   int launches = 0;
+  // MLSA variant 3 (time-segmented filter): segments, frames filtered including warm-up, the
+  // largest state mismatch found at a cut, and whether the sequential kernel had to redo the batch
+  int64_t mlsa_segments = 0, mlsa_seg_frames = 0;
+  double mlsa_cut_worst = 0;
+  int mlsa_fallback = 0;
 };
 
 class Engine {
@@ -49,7 +54,11 @@ class Engine {
   // GPUs used by synthesize*/streams. Default: device 0 only.
   void set_devices(const std::vector<int>& devices);
   const std::vector<int>& devices() const { return devices_; }
-  int mlsa_variant = -1;  // -1 = default kernel
+  int mlsa_variant = -1;  // -1 = default kernel (3: time-segmented; streams use 2)
+  // Variant 3: frames a segment filters ahead of its own range (from a zero state), and the largest
+  // state mismatch tolerated at a cut before the sequential kernel redoes the batch.
+  int mlsa_warm_frames = 40;
+  double mlsa_cut_tolerance = 1e-8;
 
   // Engine::synthesize for a batch: utterance u = lines[line_off[u] .. line_off[u+1]).
   // `out` is a pinned host buffer owned by the engine's pool: release with free_output().
