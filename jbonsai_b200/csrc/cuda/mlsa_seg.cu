@@ -50,11 +50,6 @@ constexpr int kNM = 35;       // mel-cepstral order + 1
 constexpr int kTaps = 34;     // delay-line taps d[1..34] (d[0] is write-only in the reference)
 constexpr int kSlots = 6;     // segments per warp
 constexpr int kCH = 16;       // samples per staged chunk (input ring of 2 chunks, output tile of 1)
-constexpr int kCRow = 38;     // doubles per coefficient row: 16-byte reads of 6 rows hit 6 bank groups
-constexpr int kCBuf = kSlots * kCRow + 32;  // + dump slots for idle updater entries
-constexpr int kXRow = 16;     // exchange row: y_1..y_5 at 0..4, f_1..f_5 at 8..12
-constexpr int kXBuf = (kSlots + 1) * kXRow;  // + one dump row (lanes 30/31)
-constexpr int kUpd = 7;       // coefficient entries advanced per lane: 6 * 34 = 204 <= 7 * 32
 constexpr int kWPB = 4;       // warps per block (independent of each other)
 
 struct SlotInfo {
@@ -68,25 +63,26 @@ struct SlotInfo {
   int prev;            // id of the segment before this one in the utterance, -1 if none
 };
 
+// Shared memory of one warp. Every array is indexed so that the 16 lanes of a half-warp touch 16
+// different 8-byte banks: Y/F by lane (= 5 slot + stage), In/Out as [sample][slot] rows of 8.
+struct WarpShared {
+  double Y[2][32];            // stage outputs y_1..y_5 of every slot, by lane; double-buffered by sample parity
+  double F[2][32];            // df1 section outputs
+  double In[2 * kCH * 8];     // excitation ring: [sample mod 32][slot]
+  double Out[kCH * 8];        // output tile: [sample mod 16][slot]
+  SlotInfo info[kSlots];
+};
+
 template <int WPB>
-__global__ void __launch_bounds__(32 * WPB)
+__global__ void __launch_bounds__(32 * WPB, 2)
 k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg) {
-  __shared__ __align__(16) double sC[WPB][2][kCBuf];
-  __shared__ __align__(16) double sX[WPB][2][kXBuf];
-  __shared__ __align__(16) double sIn[WPB][kSlots * 2 * kCH];
-  __shared__ __align__(16) double sOut[WPB][kSlots * kCH];
-  __shared__ SlotInfo sInfo[WPB][kSlots];
+  __shared__ __align__(16) WarpShared sh[WPB];
 
   const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int warp = blockIdx.x * WPB + wib;
   if (warp * kSlots >= sg.n_seg) return;  // whole warp leaves; warps of a block never sync with each other
-  double* const C0 = sC[wib][0];
-  double* const C1 = sC[wib][1];
-  double* const X0 = sX[wib][0];
-  double* const X1 = sX[wib][1];
-  double* const In = sIn[wib];
-  double* const Out = sOut[wib];
-  SlotInfo* const info = sInfo[wib];
+  WarpShared& S = sh[wib];
+  SlotInfo* const info = S.info;
 
   const int fp = p.fperiod;
   // ---- slot table
@@ -109,44 +105,40 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg) {
     }
     info[lane] = si;
   }
-  for (int i = lane; i < kCBuf; i += 32) { C0[i] = 0.0; C1[i] = 0.0; }
-  for (int i = lane; i < kXBuf; i += 32) { X0[i] = 0.0; X1[i] = 0.0; }
+  S.Y[0][lane] = 0.0; S.Y[1][lane] = 0.0; S.F[0][lane] = 0.0; S.F[1][lane] = 0.0;
   __syncwarp();
 
   const int g = lane < 30 ? lane / 5 : 5, s = lane < 30 ? lane - 5 * g : lane - 30;
-  const int gx = lane < 30 ? g : kSlots;           // exchange row this lane writes (dump row for 30/31)
-  const int sm1 = s > 0 ? s - 1 : 0;
+  const int g5 = 5 * g;
+  const int prev_lane = s > 0 ? g5 + s - 1 : g5;
   const bool head = lane < 30 && s == 0;
   const double a = p.alpha, ma = -a, iaa = 1.0 - a * a;
   const double pp1 = c_pp3[1], pp2 = c_pp3[2], pp3 = c_pp3[3], pp4 = c_pp3[4], pp5 = c_pp3[5];
   const double fper = (double)fp;
-  const int my_nfr = info[g].nfr, my_own0 = info[g].own0, my_seg = info[g].seg;
-  const bool my_cut = info[g].prev >= 0;  // this segment starts at a cut
-  int nfr_max = my_nfr;
+  const SlotInfo me = info[g];
+  const bool my_cut = me.prev >= 0;  // this segment starts at a cut
+  int nfr_max = me.nfr;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) nfr_max = max(nfr_max, __shfl_xor_sync(0xffffffffu, nfr_max, o));
   if (nfr_max <= 0) return;
 
-  // ---- coefficient entries advanced by this lane: entry k = lane + 32 m -> (slot k / 34, c[1 + k % 34])
-  int uaddr[kUpd];          // offset inside a coefficient buffer
-  double creg[kUpd], ctgt[kUpd], cinc[kUpd];
-  auto load_b = [&](int m, int frame_rel) -> double {
-    const int k = lane + 32 * m;
-    if (k >= kSlots * kTaps) return 0.0;
-    const SlotInfo& si = info[k / kTaps];
-    if (si.nfr <= 0) return 0.0;
-    int f = si.warm + frame_rel;
-    f = f < 0 ? 0 : (f > si.last_frame ? si.last_frame : f);
-    return d.b[si.b_base + (long long)f * kNM + 1 + k % kTaps];
+  // ---- interpolated coefficients c[k] = coefficients[k + 1] of this lane's segment, in registers
+  // (mod.rs:116-125: cinc = (cc - coefficients) / fperiod; coefficients = mc2b of the frame before)
+  const double* const brow = d.b + me.b_base + 1;
+  auto frame_row = [&](int frame_rel) -> const double* {
+    int f = me.warm + frame_rel;
+    f = f < 0 ? 0 : (f > me.last_frame ? me.last_frame : f);
+    return brow + (long long)f * kNM;
   };
+  double c[kTaps], cinc[kTaps];
+  {
+    const double* r0 = frame_row(-1);  // frame 0 itself for the first frame (mod.rs:79-109)
+    const double* r1 = frame_row(0);
 #pragma unroll
-  for (int m = 0; m < kUpd; ++m) {
-    const int k = lane + 32 * m;
-    uaddr[m] = k < kSlots * kTaps ? (k / kTaps) * kCRow + 1 + k % kTaps : kSlots * kCRow + lane;
-    creg[m] = load_b(m, -1);   // coefficients at the top of frame `warm`: mc2b of the frame before
-    ctgt[m] = load_b(m, 0);    // (of frame 0 itself for the first frame, mod.rs:79-109)
-    cinc[m] = (ctgt[m] - creg[m]) / fper;
-    C0[uaddr[m]] = creg[m];
+    for (int k = 0; k < kTaps; ++k) {
+      c[k] = r0[k];
+      cinc[k] = (r1[k] - c[k]) / fper;
+    }
   }
 
   // ---- filter state
@@ -164,7 +156,7 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg) {
       const int gg = k >> 4, i = k & (kCH - 1);
       const SlotInfo& si = info[gg];
       const int n = chunk * kCH + i;
-      double* dst = In + gg * 2 * kCH + (chunk & 1) * kCH + i;
+      double* dst = S.In + ((chunk & 1) * kCH + i) * 8 + gg;
       if (n < si.nfr * fp) cp_async8s(dst, d.wave + si.in_base + n);
       else *dst = 0.0;
     }
@@ -175,8 +167,8 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg) {
   __syncwarp();
 
   auto dump_state = [&](int which) {  // which: 0 = top of the own range, 1 = end of the segment
-    if (lane >= 30 || my_seg < 0 || sg.state == nullptr) return;
-    double* o = sg.state + ((long long)my_seg * 2 + which) * kMlsaSegStateDoubles + s * 37;
+    if (lane >= 30 || me.seg < 0 || sg.state == nullptr) return;
+    double* o = sg.state + ((long long)me.seg * 2 + which) * kMlsaSegStateDoubles + s * 37;
 #pragma unroll
     for (int i = 0; i < kTaps; ++i) o[i] = t[i];
     o[34] = d11;
@@ -184,88 +176,77 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg) {
     o[36] = uin;
   };
 
-  const double* const Cc0 = C0 + g * kCRow;
-  const double* const Cc1 = C1 + g * kCRow;
-  const int wy = gx * kXRow + s, wf = gx * kXRow + 8 + s;
-  const int rx = g * kXRow;
-  int left = fp, frames_done = 0, inIdx = 0;
+  int left = fp, frames_done = 0;
+  const double* inp = S.In + g;
 
-  auto step = [&](const double* __restrict__ Cc, double* __restrict__ Cn, double* __restrict__ X, int jout) {
+  auto step = [&](double* __restrict__ Y, double* __restrict__ F, int jin, int jout) {
     // ---------------- phase A: fir of this lane's stage (mlsa.rs:128-163) and its df1 section
-    const double c1 = Cc[1];
     double po = t[0];
     double pn = __fma_rn(a, po, iaa * uin);
     t[0] = pn;
     double y0 = 0.0, y1 = 0.0;
 #pragma unroll
-    for (int i = 1; i < kTaps; i += 2) {  // taps j = i + 1 and i + 2 with coefficients c[j], c[j+1]
-      const double2 cj = *reinterpret_cast<const double2*>(Cc + i + 1);
+    for (int i = 1; i < kTaps; i += 2) {  // taps d[i+1], d[i+2] with coefficients[i+1], [i+2]
       double q = __fma_rn(a, t[i], po);
       po = t[i];
       pn = __fma_rn(ma, pn, q);
       t[i] = pn;
-      y0 = __fma_rn(cj.x, pn, y0);
+      y0 = __fma_rn(c[i], pn, y0);
       if (i + 1 < kTaps) {
         q = __fma_rn(a, t[i + 1], po);
         po = t[i + 1];
         pn = __fma_rn(ma, pn, q);
         t[i + 1] = pn;
-        y1 = __fma_rn(cj.y, pn, y1);
+        y1 = __fma_rn(c[i + 1], pn, y1);
       }
     }
     d11 = __fma_rn(a, d11, iaa * gin);  // mlsa.rs:57-58
-    X[wy] = y0 + y1;
-    X[wf] = d11 * c1;
-    // coefficients of the next sample (mod.rs:133-135, :140)
+    Y[lane] = y0 + y1;
+    F[lane] = d11 * c[0];
+    __syncwarp();
+    // coefficients of the next sample (mod.rs:133-135; :140 at a frame end)
 #pragma unroll
-    for (int m = 0; m < kUpd; ++m) creg[m] += cinc[m];
+    for (int k = 0; k < kTaps; ++k) c[k] += cinc[k];
     if (--left == 0) {
       left = fp;
+      const double* r0 = frame_row(frames_done);
+      const double* r1 = frame_row(frames_done + 1);
       ++frames_done;
 #pragma unroll
-      for (int m = 0; m < kUpd; ++m) {
-        creg[m] = ctgt[m];
-        ctgt[m] = load_b(m, frames_done);
-        cinc[m] = (ctgt[m] - creg[m]) / fper;
+      for (int k = 0; k < kTaps; ++k) {
+        c[k] = r0[k];
+        cinc[k] = (r1[k] - c[k]) / fper;
       }
     }
-#pragma unroll
-    for (int m = 0; m < kUpd; ++m) Cn[uaddr[m]] = creg[m];
-    __syncwarp();
     // ---------------- phase B: Pade combine of df1 then df2 (mlsa.rs:54-79), next stage inputs
-    const double* Xr = X + rx;
-    const double2 y12 = *reinterpret_cast<const double2*>(Xr);
-    const double2 y34 = *reinterpret_cast<const double2*>(Xr + 2);
-    const double y5 = Xr[4];
-    const double2 f12 = *reinterpret_cast<const double2*>(Xr + 8);
-    const double2 f34 = *reinterpret_cast<const double2*>(Xr + 10);
-    const double f5 = Xr[12];
-    const double yprev = Xr[sm1], fprev = Xr[8 + sm1];
-    const double e = In[g * 2 * kCH + inIdx];
-    const double Af = __fma_rn(pp5, f5, __fma_rn(pp3, f34.x, pp1 * f12.x));
-    const double Bf = __fma_rn(pp4, f34.y, pp2 * f12.y);
-    const double Ay = __fma_rn(pp5, y5, __fma_rn(pp3, y34.x, pp1 * y12.x));
-    const double By = __fma_rn(pp4, y34.y, pp2 * y12.y);
+    const double y1v = Y[g5], y2v = Y[g5 + 1], y3v = Y[g5 + 2], y4v = Y[g5 + 3], y5v = Y[g5 + 4];
+    const double f1v = F[g5], f2v = F[g5 + 1], f3v = F[g5 + 2], f4v = F[g5 + 3], f5v = F[g5 + 4];
+    const double yprev = Y[prev_lane], fprev = F[prev_lane];
+    const double e = inp[jin * 8];
+    const double Af = __fma_rn(pp5, f5v, __fma_rn(pp3, f3v, pp1 * f1v));
+    const double Bf = __fma_rn(pp4, f4v, pp2 * f2v);
+    const double Ay = __fma_rn(pp5, y5v, __fma_rn(pp3, y3v, pp1 * y1v));
+    const double By = __fma_rn(pp4, y4v, pp2 * y2v);
     const double d120 = (e + Af) - Bf;        // d12[0]
     const double x1 = __fma_rn(2.0, Af, e);   // x after df1
     const double d220 = (x1 + Ay) - By;       // d22[0]
     const double outv = __fma_rn(2.0, Ay, x1);
     gin = s == 0 ? d120 : fprev;
     uin = s == 0 ? d220 : yprev;
-    if (head) Out[g * kCH + jout] = outv;
-    inIdx = (inIdx + 1) & (2 * kCH - 1);
+    if (head) S.Out[jout * 8 + g] = outv;
   };
 
   for (int i0 = 0; i0 < nsmp_max; i0 += kCH) {
     if (left == fp) {  // top of a frame (fp % kCH == 0): state taps for the cut check
-      if (frames_done == my_own0 && my_cut) dump_state(0);
+      if (frames_done == me.own0 && my_cut) dump_state(0);
     }
+    const int ring = (i0 & kCH);  // which half of the input ring this chunk sits in
 #pragma unroll 1
     for (int j = 0; j < kCH; j += 2) {
-      step(Cc0, C1, X0, j);
-      step(Cc1, C0, X1, j + 1);
+      step(S.Y[0], S.F[0], ring + j, j);
+      step(S.Y[1], S.F[1], ring + j + 1, j + 1);
     }
-    if (left == fp && frames_done == my_nfr) dump_state(1);
+    if (left == fp && frames_done == me.nfr) dump_state(1);
     cp_async_wait_all_s();  // chunk i0/kCH + 1 has landed
     __syncwarp();
     {  // flush 6 x 16 outputs; refill the half of the ring that was just consumed
@@ -276,7 +257,7 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg) {
         const int gg = k >> 4, i = k & (kCH - 1);
         const SlotInfo& si = info[gg];
         const int n = i0 + i;
-        if (n >= si.own0 * fp && n < si.nfr * fp) d.out[si.in_base + n] = Out[gg * kCH + i] * p.volume;
+        if (n >= si.own0 * fp && n < si.nfr * fp) d.out[si.in_base + n] = S.Out[i * 8 + gg] * p.volume;
       }
       if ((chunk + 2) * kCH < nsmp_max) fill_chunk(chunk + 2);
     }

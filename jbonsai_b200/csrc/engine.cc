@@ -392,26 +392,36 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   if (!streaming && TF > 0) {
     const int64_t W = e.mlsa_warm_frames;
     const int64_t target = (int64_t)ctx->sm_count * 4 * kSegWarpsPerSmsp * 6;
-    const int64_t S = std::max<int64_t>(kSegMinFrames, (TF + target - 1) / target);
-    for (size_t u = 0; u < n_utt; ++u) {
-      const int64_t T = (int64_t)packs[u].nframes;
-      if (T <= 0) continue;
-      int64_t G = std::max<int64_t>(1, (T + S / 2) / S);
-      // equal filtered length L for every segment: the first owns L frames, the others L - W
-      while (G > 1 && (T + (G - 1) * W) / G - W < kSegMinFrames / 2) --G;
-      const int64_t L = (T + (G - 1) * W + G - 1) / G;
-      int64_t begin = 0;
-      for (int64_t k = 0; k < G && begin < T; ++k) {
-        int64_t end = (k == G - 1) ? T : std::min<int64_t>(T, begin + (k == 0 ? L : L - W));
-        jbk::MlsaSegment sg;
-        sg.utt = (int32_t)u;
-        sg.begin = (int32_t)begin;
-        sg.end = (int32_t)end;
-        sg.warm = (int32_t)std::max<int64_t>(0, begin - W);
-        sg.prev = k == 0 ? -1 : (int32_t)(segs.size() - 1);  // index before sorting, remapped below
-        segs.push_back(sg);
-        begin = end;
+    int64_t S = std::max<int64_t>(kSegMinFrames, (TF + target - 1) / target);
+    auto cut = [&](int64_t S) {
+      segs.clear();
+      for (size_t u = 0; u < n_utt; ++u) {
+        const int64_t T = (int64_t)packs[u].nframes;
+        if (T <= 0) continue;
+        int64_t G = std::max<int64_t>(1, (T + S / 2) / S);
+        // equal filtered length L for every segment: the first owns L frames, the others L - W
+        while (G > 1 && (T + (G - 1) * W) / G - W < kSegMinFrames / 2) --G;
+        const int64_t L = (T + (G - 1) * W + G - 1) / G;
+        int64_t begin = 0;
+        for (int64_t k = 0; k < G && begin < T; ++k) {
+          int64_t end = (k == G - 1) ? T : std::min<int64_t>(T, begin + (k == 0 ? L : L - W));
+          jbk::MlsaSegment sg;
+          sg.utt = (int32_t)u;
+          sg.begin = (int32_t)begin;
+          sg.end = (int32_t)end;
+          sg.warm = (int32_t)std::max<int64_t>(0, begin - W);
+          sg.prev = k == 0 ? -1 : (int32_t)(segs.size() - 1);  // index before sorting, remapped below
+          segs.push_back(sg);
+          begin = end;
+        }
       }
+    };
+    cut(S);
+    // One wave: all segments run about equally long, so a grid slightly larger than the chip holds
+    // (target segments) would leave a second, nearly empty wave as long as the first.
+    for (int it = 0; it < 64 && (int64_t)segs.size() > target && (int64_t)segs.size() < 2 * target; ++it) {
+      S += std::max<int64_t>(1, S / 50);
+      cut(S);
     }
     // six consecutive segments share a warp and run as long as the longest of them
     std::vector<int32_t> perm(segs.size()), where(segs.size());
