@@ -68,6 +68,11 @@ int jb_engine_set_devices(jb_engine* e, const int* devices, size_t n);
 /* MLSA kernel variant (-1 = default = 3: time-segmented; 2: one warp per utterance, sequential;
  * 0: reference operation order). For A/B measurements only. */
 int jb_engine_set_mlsa_variant(jb_engine* e, int variant);
+/* Where VoiceSet::weighted (src/model/voice_set.rs:80-96) runs. 1 (default): the leaf pdf tables
+ * stay resident in HBM, the host sends one row index per (state, voice) and a kernel interpolates;
+ * 0: the host interpolates and copies the state-level vectors (~0.5 MB per 5 s utterance). Results
+ * are bit-identical. */
+int jb_engine_set_device_gather(jb_engine* e, int enabled);
 /* Variant 3 cuts utterances into time segments that are filtered concurrently; each segment first
  * filters `warm_frames` frames ahead of its own range from a zero state (default 40). The states on
  * both sides of every cut are compared on the device; when they differ by more than `cut_tolerance`

@@ -23,7 +23,7 @@ C_ABI_SYMBOLS = [
     "jb_last_error", "jb_version", "jb_device_count", "jb_device_measure_peaks", "jb_engine_load",
     "jb_engine_load_from_bytes", "jb_engine_free", "jb_engine_set_condition",
     "jb_engine_get_condition", "jb_engine_set_interpolation_weight", "jb_engine_set_devices",
-    "jb_engine_set_mlsa_variant", "jb_engine_set_mlsa_segmenting", "jb_engine_synthesize", "jb_engine_synthesize_batch", "jb_free",
+    "jb_engine_set_mlsa_variant", "jb_engine_set_mlsa_segmenting", "jb_engine_set_device_gather", "jb_engine_synthesize", "jb_engine_synthesize_batch", "jb_free",
     "jb_engine_debug_batch", "jb_engine_noise", "jb_engine_durations", "jb_engine_tree_index",
     "jb_engine_stream_parameters", "jb_engine_duration_parameters", "jb_engine_gv_parameters",
     "jb_resident_prepare", "jb_resident_run", "jb_resident_fetch", "jb_resident_free",
@@ -182,6 +182,9 @@ class Engine:
 
     def set_mlsa_variant(self, v: int) -> None:
         _check(lib.jb_engine_set_mlsa_variant(self._h, int(v)))
+
+    def set_device_gather(self, enabled: bool) -> None:
+        _check(lib.jb_engine_set_device_gather(self._h, int(bool(enabled))))
 
     def set_mlsa_segmenting(self, warm_frames: int = 40, cut_tolerance: float = 1e-8) -> None:
         _check(lib.jb_engine_set_mlsa_segmenting(self._h, int(warm_frames), C.c_double(cut_tolerance)))

@@ -140,6 +140,11 @@ int jb_engine_set_mlsa_variant(jb_engine* e, int variant) {
   return JB_OK;
 }
 
+int jb_engine_set_device_gather(jb_engine* e, int enabled) {
+  e->e->device_gather = enabled != 0;
+  return JB_OK;
+}
+
 int jb_engine_set_mlsa_segmenting(jb_engine* e, int warm_frames, double cut_tolerance) {
   JB_TRY
   if (warm_frames < 0 || !(cut_tolerance >= 0.0))

@@ -74,6 +74,27 @@ struct StreamSet {
   StreamDev s[3];
 };
 
+// Device-side parameter gather: the leaf pdfs of a stream stay resident in HBM
+// (`tab_*`, [rows][width]); the host sends rows[state][nvoices] and the kernel forms the
+// interpolated state-level vectors exactly like VoiceSet::weighted (src/model/voice_set.rs:80-96:
+// first * w0, then += w_v * rhs with separate multiply and add), plus
+// StreamParameter::apply_additional_half_tone (src/model/stream_parameter.rs:29-37) when asked.
+constexpr int kMaxVoices = 8;
+struct GatherStream {
+  int width, is_msd, nvoices;
+  double w[kMaxVoices];
+  const double* tab_mean;
+  const double* tab_vari;
+  const double* tab_msd;
+  const int32_t* rows;  // [total_states][nvoices]
+  double* mean;         // [total_states][width]
+  double* vari;
+  double* msd;          // [total_states] (is_msd only)
+  int half_tone;        // apply mean[0] = clamp(mean[0] + half_tone_add)
+  double half_tone_add, lf0_min, lf0_max;
+};
+int launch_gather_states(const GatherStream& g, int64_t total_states, cudaStream_t stream);
+
 int launch_expand(const BatchLayout& b, const StreamSet& streams, cudaStream_t stream);
 int launch_mlpg(const BatchLayout& b, const StreamDev& s, int64_t total_frames, cudaStream_t stream);
 

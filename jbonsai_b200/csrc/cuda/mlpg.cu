@@ -649,6 +649,41 @@ __global__ void __launch_bounds__(256) k_mlpg_gv(BatchLayout b, StreamDev s, int
 }
 }  // namespace
 
+namespace {
+__global__ void __launch_bounds__(256) k_gather_states(GatherStream g, int64_t total) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= total) return;
+  const int64_t i = e / g.width;
+  const int k = (int)(e - i * g.width);
+  const int32_t* r = g.rows + i * g.nvoices;
+  int64_t row = r[0];
+  double m = g.tab_mean[row * g.width + k] * g.w[0];
+  double v = g.tab_vari[row * g.width + k] * g.w[0];
+  double ms = (g.is_msd && k == 0) ? g.w[0] * g.tab_msd[row] : 0.0;
+  for (int q = 1; q < g.nvoices; ++q) {
+    row = r[q];
+    m += g.w[q] * g.tab_mean[row * g.width + k];  // -fmad=false: multiply, then add
+    v += g.w[q] * g.tab_vari[row * g.width + k];
+    if (g.is_msd && k == 0) ms += g.w[q] * g.tab_msd[row];
+  }
+  if (g.half_tone && k == 0) {
+    m = m + g.half_tone_add;
+    m = m < g.lf0_min ? g.lf0_min : (m > g.lf0_max ? g.lf0_max : m);
+  }
+  g.mean[e] = m;
+  g.vari[e] = v;
+  if (g.is_msd && k == 0) g.msd[i] = ms;
+}
+}  // namespace
+
+int launch_gather_states(const GatherStream& g, int64_t total_states, cudaStream_t stream) {
+  const int64_t total = total_states * g.width;
+  if (total <= 0) return 0;
+  if (g.nvoices < 1 || g.nvoices > kMaxVoices) return (int)cudaErrorInvalidValue;
+  k_gather_states<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(g, total);
+  return (int)cudaGetLastError();
+}
+
 int launch_expand(const BatchLayout& b, const StreamSet& set, cudaStream_t stream) {
   if (b.n_utt == 0) return 0;
   int threads = 64, blocks = (b.n_utt + threads - 1) / threads;

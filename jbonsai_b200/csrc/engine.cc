@@ -149,6 +149,27 @@ class DeviceCtx {
   std::multimap<size_t, void*> cached;  // freed device blocks
   int sm_count = 148;
   double* h_worst = nullptr;  // pinned: MLSA variant 3 cut-check result
+  // leaf pdf tables of the engine's voices, resident for the life of the context (device gather)
+  double* d_tab_mean[3] = {nullptr, nullptr, nullptr};
+  double* d_tab_vari[3] = {nullptr, nullptr, nullptr};
+  double* d_tab_msd[3] = {nullptr, nullptr, nullptr};
+  bool tables_loaded = false;
+  void load_tables(const std::vector<StreamTable>& tabs) {
+    if (tables_loaded) return;
+    for (size_t s = 0; s < tabs.size() && s < 3; ++s) {
+      const StreamTable& t = tabs[s];
+      if (!t.regular || t.rows == 0) continue;
+      JB_CUDA(cudaMalloc((void**)&d_tab_mean[s], t.mean.size() * 8));
+      JB_CUDA(cudaMalloc((void**)&d_tab_vari[s], t.vari.size() * 8));
+      JB_CUDA(cudaMemcpy(d_tab_mean[s], t.mean.data(), t.mean.size() * 8, cudaMemcpyHostToDevice));
+      JB_CUDA(cudaMemcpy(d_tab_vari[s], t.vari.data(), t.vari.size() * 8, cudaMemcpyHostToDevice));
+      if (t.is_msd) {
+        JB_CUDA(cudaMalloc((void**)&d_tab_msd[s], t.msd.size() * 8));
+        JB_CUDA(cudaMemcpy(d_tab_msd[s], t.msd.data(), t.msd.size() * 8, cudaMemcpyHostToDevice));
+      }
+    }
+    tables_loaded = true;
+  }
 
   explicit DeviceCtx(int dev) : device(dev) {
     int n = 0;
@@ -171,6 +192,11 @@ class DeviceCtx {
     cudaSetDevice(device);
     for (auto& kv : cached) cudaFree(kv.second);
     if (d_noise) cudaFree(d_noise);
+    for (int s = 0; s < 3; ++s) {
+      if (d_tab_mean[s]) cudaFree(d_tab_mean[s]);
+      if (d_tab_vari[s]) cudaFree(d_tab_vari[s]);
+      if (d_tab_msd[s]) cudaFree(d_tab_msd[s]);
+    }
     if (h_worst) cudaFreeHost(h_worst);
     for (auto& x : ev) cudaEventDestroy(x);
     for (auto& x : evx) cudaEventDestroy(x);
@@ -202,7 +228,12 @@ class DeviceCtx {
 };
 
 // ---------------------------------------------------------------- engine basics
-Engine::Engine(VoiceSet v) : voices_(std::move(v)) { condition.load_model(voices_); }
+Engine::Engine(VoiceSet v) : voices_(std::move(v)) {
+  condition.load_model(voices_);
+  tables_ = build_stream_tables(voices_);
+  for (auto& t : tables_)
+    if (voices_.size() > (size_t)jbk::kMaxVoices) t.regular = false;
+}
 Engine::~Engine() = default;
 
 std::unique_ptr<Engine> Engine::load(const std::vector<std::string>& paths) {
@@ -278,9 +309,10 @@ std::vector<UtterancePack> Engine::build_packs(const std::vector<std::vector<std
   if (voices_.global_metadata().num_streams < 3 || voices_.stream_metadata(2).vector_length == 0)
     throw Error(kErrUnsupported, "voices without an LPF stream are not built yet");
   std::vector<UtterancePack> packs(utts.size());
+  const std::vector<StreamTable>* tabs = device_gather ? &tables_ : nullptr;
   size_t nthreads = std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), utts.size());
   if (nthreads <= 1) {
-    for (size_t u = 0; u < utts.size(); ++u) packs[u] = build_utterance(voices_, condition, utts[u]);
+    for (size_t u = 0; u < utts.size(); ++u) packs[u] = build_utterance(voices_, condition, utts[u], tabs);
     return packs;
   }
   std::atomic<size_t> next{0};
@@ -293,7 +325,7 @@ std::vector<UtterancePack> Engine::build_packs(const std::vector<std::vector<std
         size_t u = next.fetch_add(1);
         if (u >= utts.size()) return;
         try {
-          packs[u] = build_utterance(voices_, condition, utts[u]);
+          packs[u] = build_utterance(voices_, condition, utts[u], tabs);
         } catch (const Error& e) {
           std::lock_guard<std::mutex> g(emu);
           if (!err) err.reset(new Error(e));
@@ -327,6 +359,9 @@ struct Engine::Resident {
   double* d_chunk = nullptr;  // streaming gather buffer
   size_t chunk_cap = 0;
   int64_t h2d_bytes = 0;
+  // device-side gather of the state-level parameters (streams whose pdf table is resident)
+  jbk::GatherStream gather[3]{};
+  bool gathered[3] = {false, false, false};
   // MLSA variant 3: time segments (empty when the batch is streamed)
   jbk::MlsaSegments segs{};
   double* d_worst = nullptr;
@@ -337,6 +372,7 @@ struct Engine::Resident {
   // excitation, MLSA (+ cut check for variant 3)
   int launches() const {
     int n = 1 + 3 + 2 + 3 + (segs.n_seg > 0 ? 1 : 0);
+    for (int i = 0; i < 3; ++i) n += gathered[i] ? 1 : 0;
     for (int i = 0; i < streams.n; ++i) n += streams.s[i].has_gv ? 1 : 0;
     return n;
   }
@@ -439,18 +475,23 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
     segs.swap(sorted);
   }
   const size_t o_segs = in.take(segs.size() * sizeof(jbk::MlsaSegment));
-  size_t o_mean[3], o_vari[3], o_msd[3], o_gvm[3], o_gvv[3], o_gsw[3];
-  int dim[3], nwin[3], is_msd[3], has_gv[3];
+  size_t o_mean[3], o_vari[3], o_msd[3], o_gvm[3], o_gvv[3], o_gsw[3], o_rows[3];
+  int dim[3], nwin[3], is_msd[3], has_gv[3], nvoice[3];
+  bool gath[3];
   for (size_t s = 0; s < nstream; ++s) {
+    // device gather: row indices travel instead of the interpolated vectors
+    gath[s] = e.device_gather && s < e.tables_.size() && e.tables_[s].regular;
+    nvoice[s] = (int)std::min(vs.size(), cond.interporation_weight.parameter[s].size());
     const StreamModelMetadata& md = vs.stream_metadata(s);
     dim[s] = (int)md.vector_length;
     nwin[s] = (int)vs.stream_windows(s).size();
     is_msd[s] = md.is_msd;
     has_gv[s] = md.use_gv;
     const size_t L = (size_t)dim[s] * nwin[s];
-    o_mean[s] = in.take((size_t)TS * L * 8);
-    o_vari[s] = in.take((size_t)TS * L * 8);
-    o_msd[s] = is_msd[s] ? in.take((size_t)TS * 8) : 0;
+    o_rows[s] = gath[s] ? in.take((size_t)TS * nvoice[s] * 4) : 0;
+    o_mean[s] = gath[s] ? 0 : in.take((size_t)TS * L * 8);
+    o_vari[s] = gath[s] ? 0 : in.take((size_t)TS * L * 8);
+    o_msd[s] = (is_msd[s] && !gath[s]) ? in.take((size_t)TS * 8) : 0;
     o_gvm[s] = has_gv[s] ? in.take(n_utt * dim[s] * 8) : 0;
     o_gvv[s] = has_gv[s] ? in.take(n_utt * dim[s] * 8) : 0;
     o_gsw[s] = has_gv[s] ? in.take((size_t)TS) : 0;
@@ -480,8 +521,13 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
     for (size_t s = 0; s < nstream && s < p.streams.size(); ++s) {
       const StreamPack& sp = p.streams[s];
       const size_t L = (size_t)dim[s] * nwin[s];
-      if (sp.mean.size() != p.nstates * L) throw Error(kErrArgument, "stream pack has the wrong shape");
-      if (p.nstates) {
+      if (gath[s]) {
+        if (sp.rows.size() != p.nstates * (size_t)nvoice[s])
+          throw Error(kErrArgument, "stream pack has the wrong shape (row indices)");
+        if (p.nstates) memcpy(h + o_rows[s] + so * nvoice[s] * 4, sp.rows.data(), sp.rows.size() * 4);
+      } else if (sp.mean.size() != p.nstates * L) {
+        throw Error(kErrArgument, "stream pack has the wrong shape");
+      } else if (p.nstates) {
         memcpy(h + o_mean[s] + so * L * 8, sp.mean.data(), p.nstates * L * 8);
         memcpy(h + o_vari[s] + so * L * 8, sp.vari.data(), p.nstates * L * 8);
         if (is_msd[s]) memcpy(h + o_msd[s] + so * 8, sp.msd.data(), p.nstates * 8);
@@ -498,9 +544,20 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
           else memset(h + o_gsw[s] + so, 0, p.nstates);
         }
       }
-      if (s == 1)
-        for (size_t i = 0; i < p.nstates; ++i)
-          if (sp.msd[i] > cond.msd_threshold[1]) vf += p.durations[i];
+      if (s == 1 && is_msd[s]) {  // voiced frames, for the flop count of the report only
+        const std::vector<double>& w = cond.interporation_weight.parameter[s];
+        for (size_t i = 0; i < p.nstates; ++i) {
+          double m;
+          if (gath[s]) {  // same arithmetic as k_gather_states / VoiceSet::weighted
+            const int32_t* rr = sp.rows.data() + i * nvoice[s];
+            m = w[0] * e.tables_[s].msd[(size_t)rr[0]];
+            for (int q = 1; q < nvoice[s]; ++q) m += w[q] * e.tables_[s].msd[(size_t)rr[q]];
+          } else {
+            m = sp.msd[i];
+          }
+          if (m > cond.msd_threshold[1]) vf += p.durations[i];
+        }
+      }
     }
     voiced_frames += vf;
   };
@@ -508,6 +565,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   r->voiced_samples = voiced_frames.load() * fperiod;
 
   JB_CUDA(cudaSetDevice(ctx->device));
+  if (e.device_gather) ctx->load_tables(e.tables_);
   r->d_in = ctx->dalloc(r->in_bytes, &r->in_cap);
   JB_CUDA(cudaEventRecord(ctx->ev[0], ctx->stream));
   JB_CUDA(cudaMemcpyAsync(r->d_in, h, r->in_bytes, cudaMemcpyHostToDevice, ctx->stream));
@@ -532,6 +590,14 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
     sb = std::max(sb, (size_t)jbk::mlpg_scratch_planes(ws.band_width(), has_gv[s]) *
                                                 (size_t)TF * dim[s] * 8);
   }
+  size_t w_gmean[3] = {0}, w_gvari[3] = {0}, w_gmsd[3] = {0};
+  for (size_t s = 0; s < nstream; ++s)
+    if (gath[s]) {
+      const size_t L = (size_t)dim[s] * nwin[s];
+      w_gmean[s] = wk.take((size_t)TS * L * 8);
+      w_gvari[s] = wk.take((size_t)TS * L * 8);
+      w_gmsd[s] = is_msd[s] ? wk.take((size_t)TS * 8) : 0;
+    }
   const size_t w_scratch = wk.take(scratch_bytes);
   const size_t w_scratch1 = wk.take(scratch1_bytes);
   const size_t w_b = wk.take((size_t)TF * dim[0] * 8);
@@ -563,9 +629,28 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
     sd.windows = make_windows(vs.stream_windows(s));
     sd.msd_threshold = cond.msd_threshold[s];
     sd.gv_weight = cond.gv_weight[s];
-    sd.mean = (const double*)(di + o_mean[s]);
-    sd.vari = (const double*)(di + o_vari[s]);
-    sd.msd = is_msd[s] ? (const double*)(di + o_msd[s]) : nullptr;
+    sd.mean = gath[s] ? (const double*)(dw + w_gmean[s]) : (const double*)(di + o_mean[s]);
+    sd.vari = gath[s] ? (const double*)(dw + w_gvari[s]) : (const double*)(di + o_vari[s]);
+    sd.msd = !is_msd[s] ? nullptr : gath[s] ? (const double*)(dw + w_gmsd[s]) : (const double*)(di + o_msd[s]);
+    r->gathered[s] = gath[s];
+    if (gath[s]) {
+      jbk::GatherStream& gs = r->gather[s];
+      gs.width = dim[s] * nwin[s];
+      gs.is_msd = is_msd[s];
+      gs.nvoices = nvoice[s];
+      for (int q = 0; q < nvoice[s]; ++q) gs.w[q] = cond.interporation_weight.parameter[s][(size_t)q];
+      gs.tab_mean = ctx->d_tab_mean[s];
+      gs.tab_vari = ctx->d_tab_vari[s];
+      gs.tab_msd = ctx->d_tab_msd[s];
+      gs.rows = (const int32_t*)(di + o_rows[s]);
+      gs.mean = (double*)(dw + w_gmean[s]);
+      gs.vari = (double*)(dw + w_gvari[s]);
+      gs.msd = is_msd[s] ? (double*)(dw + w_gmsd[s]) : nullptr;
+      gs.half_tone = (s == 1 && cond.additional_half_tone != 0.0) ? 1 : 0;
+      gs.half_tone_add = cond.additional_half_tone * kHalfTone;
+      gs.lf0_min = kMinLf0;
+      gs.lf0_max = kMaxLf0;
+    }
     sd.gv_mean = has_gv[s] ? (const double*)(di + o_gvm[s]) : nullptr;
     sd.gv_vari = has_gv[s] ? (const double*)(di + o_gvv[s]) : nullptr;
     sd.gv_switch = has_gv[s] ? (const uint8_t*)(di + o_gsw[s]) : nullptr;
@@ -621,6 +706,8 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
 static void launch_mlpg_all(Engine::Resident* r, bool with_pulse) {
   DeviceCtx* c = r->ctx;
   cudaStream_t st = c->stream, sb = c->stream2;
+  for (int s = 0; s < r->streams.n; ++s)
+    if (r->gathered[s]) JB_LAUNCH(jbk::launch_gather_states(r->gather[s], r->total_states, st));
   JB_LAUNCH(jbk::launch_expand(r->layout, r->streams, st));
   JB_CUDA(cudaEventRecord(c->evx[0], st));
   JB_CUDA(cudaStreamWaitEvent(sb, c->evx[0], 0));

@@ -57,6 +57,9 @@ class Engine {
   int mlsa_variant = -1;  // -1 = default kernel (3: time-segmented; streams use 2)
   // Variant 3: frames a segment filters ahead of its own range (from a zero state), and the largest
   // state mismatch tolerated at a cut before the sequential kernel redoes the batch.
+  // Device-side parameter gather (default): leaf pdf tables stay resident in HBM, the host sends
+  // row indices and k_gather_states interpolates. false = the host packs interpolated vectors.
+  bool device_gather = true;
   int mlsa_warm_frames = 40;
   double mlsa_cut_tolerance = 1e-8;
 
@@ -87,6 +90,7 @@ class Engine {
   friend class Stream;
   explicit Engine(VoiceSet v);
   VoiceSet voices_;
+  std::vector<StreamTable> tables_;  // flattened leaf pdfs per stream (device gather)
   std::vector<int> devices_{0};
   mutable std::mutex ctx_mu_;
   mutable std::map<int, std::unique_ptr<DeviceCtx>> ctx_;

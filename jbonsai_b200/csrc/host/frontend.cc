@@ -2,6 +2,8 @@
 // multiply-adds outside `mlsa::fir`, and interpolation / duration arithmetic must round alike.
 #include "frontend.h"
 
+#include <algorithm>
+#include <climits>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -372,8 +374,52 @@ bool Models::gv(size_t s, std::vector<MeanVari>* params, std::vector<uint8_t>* g
 }
 
 // ---------------------------------------------------------------- utterance pack
+std::vector<StreamTable> build_stream_tables(const VoiceSet& voices) {
+  const size_t nstream = voices.global_metadata().num_streams;
+  std::vector<StreamTable> out(nstream);
+  for (size_t s = 0; s < nstream; ++s) {
+    const StreamModelMetadata& md = voices.stream_metadata(s);
+    StreamTable& t = out[s];
+    t.width = md.vector_length * voices.stream_windows(s).size();
+    t.is_msd = md.is_msd;
+    for (const auto& v : voices.voices) {
+      const Model& m = v->stream_models[s].stream_model;
+      t.voice_base.push_back(t.rows);
+      std::vector<size_t> tb;
+      size_t r = 0;
+      for (const auto& tree_pdfs : m.pdf) {
+        tb.push_back(r);
+        r += tree_pdfs.size();
+      }
+      t.tree_base.push_back(std::move(tb));
+      t.rows += r;
+    }
+    t.mean.resize(t.rows * t.width);
+    t.vari.resize(t.rows * t.width);
+    if (t.is_msd) t.msd.resize(t.rows);
+    size_t row = 0;
+    for (const auto& v : voices.voices)
+      for (const auto& tree_pdfs : v->stream_models[s].stream_model.pdf)
+        for (const ModelParameter& p : tree_pdfs) {
+          if (p.parameters.size() != t.width || p.has_msd != t.is_msd) {
+            t.regular = false;
+          } else {
+            for (size_t k = 0; k < t.width; ++k) {
+              t.mean[row * t.width + k] = p.parameters[k].mean;
+              t.vari[row * t.width + k] = p.parameters[k].vari;
+            }
+            if (t.is_msd) t.msd[row] = p.msd;
+          }
+          ++row;
+        }
+    if (t.rows >= (size_t)INT32_MAX) t.regular = false;
+  }
+  return out;
+}
+
 UtterancePack build_utterance(const VoiceSet& voices, const Condition& cond,
-                              const std::vector<std::string>& lines) {
+                              const std::vector<std::string>& lines,
+                              const std::vector<StreamTable>* tables) {
   Labels labels = Labels::load_from_strings(cond.sampling_frequency, cond.fperiod, lines);
   Models models{labels.labels, voices, cond.interporation_weight};
   std::vector<MeanVari> dur = models.duration();
@@ -394,6 +440,42 @@ UtterancePack build_utterance(const VoiceSet& voices, const Condition& cond,
     sp.dim = md.vector_length;
     sp.nwin = voices.stream_windows(s).size();
     sp.is_msd = md.is_msd;
+    if (tables && (*tables)[s].regular) {
+      // index mode: the same tree walks as Models::stream (model/mod.rs:98-118), rows instead of
+      // vectors; the weighted sum of voice_set.rs:80-96 runs on the device (k_gather_states)
+      const StreamTable& tb = (*tables)[s];
+      const size_t nv = std::min(voices.size(), cond.interporation_weight.parameter[s].size());
+      const size_t ns = models.nstate();
+      const size_t S = std::min(pack.nstates, labels.labels.size() * ns);
+      sp.rows.resize(S * nv);
+      for (size_t i = 0; i < S; ++i) {
+        const std::string& label = labels.labels[i / ns];
+        const size_t st = 2 + i % ns;
+        for (size_t v = 0; v < nv; ++v) {
+          const Model& m = voices.voices[v]->stream_models[s].stream_model;
+          long ti, pi;
+          m.get_index(st, label, &ti, &pi);
+          if (ti < 0 || pi < 1 || (size_t)(ti - 2) >= m.pdf.size() || (size_t)(pi - 1) >= m.pdf[ti - 2].size())
+            throw Error(kErrIndex, "tree/pdf index not found for label: " + label);
+          sp.rows[i * nv + v] = (int32_t)(tb.voice_base[v] + tb.tree_base[v][(size_t)ti - 2] + (size_t)pi - 1);
+        }
+      }
+      std::vector<MeanVari> gvp;
+      std::vector<uint8_t> gsw;
+      if (models.gv(s, &gvp, &gsw)) {
+        sp.has_gv = true;
+        sp.gv_mean.resize(sp.dim);
+        sp.gv_vari.resize(sp.dim);
+        for (size_t d = 0; d < sp.dim; ++d) {
+          sp.gv_mean[d] = gvp[d].mean;
+          sp.gv_vari[d] = gvp[d].vari;
+        }
+        gsw.resize(S);
+        sp.gv_switch = gsw;
+      }
+      pack.streams.push_back(std::move(sp));
+      continue;
+    }
     std::vector<std::vector<MeanVari>> params;
     std::vector<double> msd;
     models.stream(s, &params, &msd);

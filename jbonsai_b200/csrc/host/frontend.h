@@ -115,6 +115,23 @@ struct Models {
   bool gv(size_t s, std::vector<MeanVari>* params, std::vector<uint8_t>* gv_switch) const;
 };
 
+// ---- leaf pdfs of one stream, flattened for the device (the tables stay resident
+// in HBM and the host sends one row index per (state, voice) instead of the interpolated vectors).
+// Row r of voice v, tree t (state t + 2), pdf index i (1-based): voice_base[v] + tree_base[v][t] + i - 1.
+struct StreamTable {
+  size_t width = 0;   // nwin * dim
+  bool is_msd = false;
+  // false when some pdf disagrees with the stream metadata (length or MSD flag): the engine then
+  // keeps interpolating on the host (VoiceSet::weighted) so that results stay exactly the reference's
+  bool regular = true;
+  std::vector<double> mean, vari;  // [rows][width]
+  std::vector<double> msd;         // [rows] (is_msd only)
+  std::vector<size_t> voice_base;
+  std::vector<std::vector<size_t>> tree_base;
+  size_t rows = 0;
+};
+std::vector<StreamTable> build_stream_tables(const VoiceSet& voices);
+
 // ---- the hot path's input for one utterance (state level, before duration expansion)
 struct StreamPack {
   size_t dim = 0;   // vector_length
@@ -123,6 +140,9 @@ struct StreamPack {
   std::vector<double> mean;  // [S][nwin*dim]
   std::vector<double> vari;  // [S][nwin*dim]
   std::vector<double> msd;   // [S] (DBL_MAX if !is_msd)
+  // index mode (device-side gather): rows[i * nvoices + v] = StreamTable row of state i in voice v;
+  // mean/vari/msd stay empty
+  std::vector<int32_t> rows;
   bool has_gv = false;
   std::vector<double> gv_mean;     // [dim]  (already multiplied by nothing; gv_weight applied later)
   std::vector<double> gv_vari;     // [dim]
@@ -137,7 +157,9 @@ struct UtterancePack {
 };
 
 // Engine::generator up to (not including) MlpgAdjust::create  (engine.rs:301-357).
+// tables != nullptr selects index mode for the streams whose table is regular.
 UtterancePack build_utterance(const VoiceSet& voices, const Condition& cond,
-                              const std::vector<std::string>& lines);
+                              const std::vector<std::string>& lines,
+                              const std::vector<StreamTable>* tables = nullptr);
 
 }  // namespace jb

@@ -301,3 +301,25 @@ def test_small_alpha_falls_back_to_reference_order():
     w = e.synthesize(SAMPLE_SENTENCE_1)
     ow = o.synthesize(SAMPLE_SENTENCE_1, fma=True)
     assert np.abs(w - ow).max() <= WAVE_ATOL
+
+
+# ---- device-side parameter gather (k_gather_states) == host interpolation, bit for bit
+@pytest.mark.parametrize("multi", [False, True])
+def test_device_gather_equals_host_pack(multi):
+    def make(gather):
+        e = jb.Engine.load([TOHOKU_NEUTRAL, TOHOKU_HAPPY] if multi else [NITECH])
+        if multi:
+            e.set_interpolation_weight("duration", 0, [0.7, 0.3])
+            e.set_interpolation_weight("parameter", 0, [0.7, 0.3])
+            e.set_interpolation_weight("parameter", 1, [0.4, 0.6])
+            e.set_interpolation_weight("parameter", 2, [1.0, 0.0])
+        e.set("additional_half_tone", 1.5)
+        e.set_device_gather(gather)
+        return e
+    utts = [SAMPLE_SENTENCE_2, [], SAMPLE_SENTENCE_1]
+    a, b = make(True).debug_batch(utts), make(False).debug_batch(utts)
+    for k in ("mcp", "lf0", "lpf", "pulse", "exc"):
+        assert np.array_equal(a[k], b[k]), k
+    wa, offa = make(True).synthesize_batch(utts)
+    wb, offb = make(False).synthesize_batch(utts)
+    assert list(offa) == list(offb) and np.array_equal(wa, wb)
