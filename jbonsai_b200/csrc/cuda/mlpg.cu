@@ -9,6 +9,8 @@
 // (consecutive dims of one utterance) touch consecutive doubles. Compile with -fmad=false:
 // the operation order below is the reference's and no multiply-add may be contracted, which
 // makes the generated parameters bit-identical to the CPU restatement.
+#include <climits>
+
 #include "kernels.h"
 
 namespace jbk {
@@ -18,45 +20,83 @@ namespace {
 constexpr double kNoData = -1e10;
 
 // ---------------------------------------------------------------- expand
-// One thread per utterance: duration expansion (IterExt::duration, mod.rs:105-112), MSD mask
-// (Mask::create, mask.rs:20-28), boundary distances (mask.rs:51-82) and voiced compaction.
-__global__ void k_expand(BatchLayout b, StreamSet set) {
-  const StreamDev* streams = set.s;
-  const int nstream = set.n;
-  int u = blockIdx.x * blockDim.x + threadIdx.x;
-  if (u >= b.n_utt) return;
+// One CTA per utterance: duration expansion (IterExt::duration, mod.rs:105-112), MSD mask
+// (Mask::create, mask.rs:20-28), boundary distances (mask.rs:51-82) and voiced compaction, as
+// block-wide scans over tiles of kExpandThreads states / frames (sum, running max, running min).
+constexpr int kExpandThreads = 256;
+
+// Inclusive block scan of (sum of a, max of b) in tile order; returns the scanned pair of this
+// thread and leaves the tile totals in tot[0], tot[1]. sw: 2 * (kExpandThreads / 32) ints.
+__device__ __forceinline__ void block_scan_sum_max(int& a, int& b, int* sw, int* tot) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int ya = __shfl_up_sync(0xffffffffu, a, o), yb = __shfl_up_sync(0xffffffffu, b, o);
+    if (lane >= o) { a += ya; b = max(b, yb); }
+  }
+  if (lane == 31) { sw[2 * w] = a; sw[2 * w + 1] = b; }
+  __syncthreads();
+  int pa = 0, pb = INT_MIN;
+  for (int i = 0; i < w; ++i) { pa += sw[2 * i]; pb = max(pb, sw[2 * i + 1]); }
+  a += pa;
+  b = max(b, pb);
+  if (threadIdx.x == kExpandThreads - 1) { tot[0] = a; tot[1] = b; }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(kExpandThreads) k_expand(BatchLayout b, StreamSet set) {
+  __shared__ int sw[2 * (kExpandThreads / 32)];
+  __shared__ int tot[2];
+  const int u = blockIdx.x, tid = threadIdx.x;
   const int64_t soff = b.state_off[u], foff = b.frame_off[u];
   const int S = (int)(b.state_off[u + 1] - soff);
   const int T = (int)(b.frame_off[u + 1] - foff);
-  int t = 0;
-  for (int s = 0; s < S; ++s) {
-    int dur = b.durations[soff + s];
-    for (int k = 0; k < dur; ++k) b.frame_state[foff + t++] = s;
+  // frame -> state: exclusive prefix sum of the durations, every state writes its own run
+  int carry = 0;
+  for (int s0 = 0; s0 < S; s0 += kExpandThreads) {
+    const int s = s0 + tid;
+    const int dur = s < S ? b.durations[soff + s] : 0;
+    int a = dur, dummy = 0;
+    block_scan_sum_max(a, dummy, sw, tot);
+    const int start = carry + a - dur;
+    for (int k = 0; k < dur; ++k) b.frame_state[foff + start + k] = s;
+    carry += tot[0];
+    __syncthreads();
   }
-  for (int si = 0; si < nstream; ++si) {
-    const StreamDev& sd = streams[si];
+  __syncthreads();
+  for (int si = 0; si < set.n; ++si) {
+    const StreamDev& sd = set.s[si];
     if (!sd.is_msd) continue;
-    int left = 0, nv = 0;
-    for (int f = 0; f < T; ++f) {
-      bool m = sd.msd[soff + b.frame_state[foff + f]] > sd.msd_threshold;
-      if (m) {
-        sd.left[foff + f] = f - left;
-        sd.vidx[foff + nv++] = f;
-      } else {
-        sd.left[foff + f] = -1;  // masked
-        left = f + 1;
+    // forward: voiced count (compaction index) and last masked frame so far
+    int cnt = 0, last = -1;
+    for (int f0 = 0; f0 < T; f0 += kExpandThreads) {
+      const int f = f0 + tid;
+      const bool m = f < T && sd.msd[soff + b.frame_state[foff + f]] > sd.msd_threshold;
+      int a = m ? 1 : 0, bb = (f < T && !m) ? f : -1;
+      block_scan_sum_max(a, bb, sw, tot);
+      if (f < T) {
+        if (m) {
+          sd.left[foff + f] = f - (max(last, bb) + 1);
+          sd.vidx[foff + cnt + a - 1] = f;
+        } else {
+          sd.left[foff + f] = -1;  // masked
+        }
       }
+      cnt += tot[0];
+      last = max(last, tot[1]);
+      __syncthreads();
     }
-    sd.nvoiced[u] = nv;
-    int right = T - 1;
-    for (int f = T - 1; f >= 0; --f) {
-      if (sd.left[foff + f] >= 0) {
-        sd.right[foff + f] = right - f;
-      } else {
-        sd.right[foff + f] = -1;
-        if (f == 0) break;
-        right = f - 1;
-      }
+    if (tid == 0) sd.nvoiced[u] = cnt;
+    // backward: first masked frame at or after f, as a running max of the negated index
+    int next = T;
+    for (int f0 = 0; f0 < T; f0 += kExpandThreads) {
+      const int f = T - 1 - (f0 + tid);
+      const bool m = f >= 0 && sd.left[foff + f] >= 0;
+      int a = 0, bb = (f >= 0 && !m) ? -f : INT_MIN;
+      block_scan_sum_max(a, bb, sw, tot);
+      if (f >= 0) sd.right[foff + f] = m ? (min(next, bb == INT_MIN ? INT_MAX : -bb) - 1 - f) : -1;
+      if (tot[1] != INT_MIN) next = min(next, -tot[1]);
+      __syncthreads();
     }
   }
 }
@@ -686,8 +726,7 @@ int launch_gather_states(const GatherStream& g, int64_t total_states, cudaStream
 
 int launch_expand(const BatchLayout& b, const StreamSet& set, cudaStream_t stream) {
   if (b.n_utt == 0) return 0;
-  int threads = 64, blocks = (b.n_utt + threads - 1) / threads;
-  k_expand<<<blocks, threads, 0, stream>>>(b, set);
+  k_expand<<<b.n_utt, kExpandThreads, 0, stream>>>(b, set);
   return (int)cudaGetLastError();
 }
 

@@ -132,7 +132,36 @@ __global__ void __launch_bounds__(128) k_pulse_runs(BatchLayout b, VocoderParams
   for (int ff = f;;) {
     double* out = d.pulse + (foff + ff) * fp;
     const double pitch_next = ff + 1 < T ? d.pitch[foff + ff + 1] : 0.0;
-    for (int i = 0; i < fp; ++i) {  // voiced_frame (excitation.rs:72-86)
+    int i = 0;
+    // Eight samples at a time. The pitch chain p += inc is independent of the counter; the counter
+    // itself moves by exact integer steps while it stays inside one binade (cnt >= 1, same exponent
+    // for cnt and cnt + 8): then cnt + k is bit for bit the k-fold "+= 1.0" of the reference, and a
+    // block in which no sample reaches its period is just cnt += 8. Any other block (a pulse, or a
+    // binade crossing where "+= 1.0" rounds) is replayed sample by sample below.
+    for (; i + 8 <= fp; i += 8) {
+      double pk[8];
+      pk[0] = p_cur;
+#pragma unroll
+      for (int k = 1; k < 8; ++k) pk[k] = pk[k - 1] + inc;
+      const double c8 = cnt + 8.0;
+      bool slow = !(cnt >= 1.0) || (__double2hiint(c8) >> 20) != (__double2hiint(cnt) >> 20);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) slow |= (cnt + (double)(k + 1)) >= pk[k];
+      if (!slow) {
+        cnt = c8;
+      } else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {  // voiced_frame (excitation.rs:72-86)
+          cnt += 1.0;
+          if (cnt >= pk[k]) {
+            cnt -= pk[k];
+            out[i + k] = sqrt(pk[k]);
+          }
+        }
+      }
+      p_cur = pk[7] + inc;
+    }
+    for (; i < fp; ++i) {  // voiced_frame (excitation.rs:72-86)
       cnt += 1.0;
       if (cnt >= p_cur) {
         cnt -= p_cur;
@@ -223,6 +252,94 @@ __global__ void __launch_bounds__(256) k_excitation(BatchLayout b, VocoderParams
     }
     if (x != 0.0) x *= exp(s_c0[i]);
     wave[i] = x;
+  }
+}
+
+// Fast path of the same computation for nlpf = NL <= 32 and 8 | fperiod <= 256 (every shipped
+// voice: 31 taps, 240 samples): one warp per frame, each lane owns eight consecutive samples and
+// slides a 38-value register window over them, so a multiply-add costs no shared-memory read of its
+// own (the block-per-frame kernel above reads two operands per tap and is shared-memory bound).
+// Same operands, same order of additions per sample. The staging arrays skip one slot in nine so
+// that lanes reading with a stride of eight doubles fall into different banks.
+constexpr int kExWarps = 4;
+template <int NL>
+__global__ void __launch_bounds__(32 * kExWarps) k_excitation_w(BatchLayout b, VocoderParams p, VocoderDev d,
+                                                                int64_t total_frames) {
+  constexpr int HIST = NL - 1, H = (NL - 1) / 2, R = 8, WIN = R + HIST;
+  constexpr int MAXN = 256 + HIST, PADN = MAXN + MAXN / 8 + 2;
+  __shared__ double s_diff[kExWarps][PADN];
+  __shared__ double s_noise[kExWarps][PADN];
+  __shared__ double s_lpf[kExWarps][2][32];  // [0] previous frame's filter, [1] this frame's
+  __shared__ double s_c0[kExWarps][256];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t gf = (int64_t)blockIdx.x * kExWarps + w;
+  if (gf >= total_frames) return;  // whole warp; warps never sync with each other
+  const int u = find_utt(b.frame_off, b.n_utt, gf);
+  const int64_t foff = b.frame_off[u];
+  const int f = (int)(gf - foff);
+  if (f < d.frame_begin || (d.frame_count >= 0 && f - d.frame_begin >= d.frame_count)) return;
+  const int fp = p.fperiod;
+  const int64_t n0 = (int64_t)f * fp;
+  const bool voiced_cur = d.pitch[gf] != 0.0;
+  const bool voiced_prev = f > 0 && d.pitch[gf - 1] != 0.0;
+  const double* pulse = d.pulse + foff * fp + n0 - HIST;
+  const double* noise = d.noise + n0 - HIST;
+  auto pad = [](int j) { return j + (j >> 3); };
+
+  for (int i = lane; i < fp + HIST; i += 32) {
+    const bool in = n0 - HIST + i >= 0;
+    const double nz = in ? noise[i] : 0.0;
+    const bool v = i >= HIST ? voiced_cur : voiced_prev;
+    s_noise[w][pad(i)] = nz;
+    s_diff[w][pad(i)] = (in && v) ? pulse[i] - nz : 0.0;
+  }
+  if (lane < NL) {
+    s_lpf[w][1][lane] = d.lpf[gf * NL + lane];
+    s_lpf[w][0][lane] = f > 0 ? d.lpf[(gf - 1) * NL + lane] : 0.0;
+  }
+  if (lane == 31) {  // coefficients[0] of every sample, by repeated addition (mod.rs:133-135)
+    const double cc = d.b[gf * p.nmcp];
+    double c = f > 0 ? d.b[(gf - 1) * p.nmcp] : cc;
+    const double cinc = (cc - c) / (double)fp;
+    for (int i = 0; i < fp; ++i) {
+      s_c0[w][i] = c;
+      c += cinc;
+    }
+  }
+  __syncwarp();
+
+  const int i0 = lane * R;
+  if (i0 >= fp) return;
+  double* wave = d.wave + foff * fp + n0 + i0;
+  double x[R];
+  if (!voiced_cur && !(voiced_prev && i0 < HIST)) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) x[r] = 0.0 + s_noise[w][pad(i0 + r + HIST - H)];  // centre-tap noise only
+  } else {
+    double win[WIN], nz[R];
+#pragma unroll
+    for (int t = 0; t < WIN; ++t) win[t] = s_diff[w][pad(i0 + t)];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      nz[r] = s_noise[w][pad(i0 + r + HIST - H)];
+      x[r] = 0.0;
+    }
+#pragma unroll
+    for (int k = NL - 1; k >= 0; --k) {
+      const double lc = s_lpf[w][1][k], lp = s_lpf[w][0][k];
+#pragma unroll
+      for (int r = 0; r < R; ++r) {
+        if (k == H) x[r] += nz[r];
+        // sources of the previous frame (k > i) use its filter, the rest this frame's
+        x[r] += win[r + HIST - k] * ((k - r > i0) ? lp : lc);
+      }
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r) {
+    double v = x[r];
+    if (v != 0.0) v *= exp(s_c0[w][i0 + r]);  // mod.rs:129-131
+    wave[r] = v;
   }
 }
 
@@ -674,7 +791,11 @@ int launch_excitation(const BatchLayout& b, const VocoderParams& p, const Vocode
                       int64_t total_frames, cudaStream_t stream) {
   if (total_frames == 0) return 0;
   if (p.nlpf > kMaxLpf || p.fperiod > kMaxFperiod) return (int)cudaErrorInvalidValue;
-  k_excitation<<<(unsigned)total_frames, 256, 0, stream>>>(b, p, d, total_frames);
+  if (p.nlpf == 31 && p.fperiod % 8 == 0 && p.fperiod <= 256)
+    k_excitation_w<31><<<(unsigned)((total_frames + kExWarps - 1) / kExWarps), 32 * kExWarps, 0, stream>>>(
+        b, p, d, total_frames);
+  else
+    k_excitation<<<(unsigned)total_frames, 256, 0, stream>>>(b, p, d, total_frames);
   return (int)cudaGetLastError();
 }
 
