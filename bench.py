@@ -53,14 +53,13 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--mlsa-variant", type=int, default=-1)
+    ap.add_argument("--device-gather", type=int, default=1, help="0: host interpolates and copies vectors (A/B)")
     return ap.parse_args()
 
 
 def dist_env():
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    return rank, world, local
+    from jbonsai_b200.dist import dist_env as _env
+    return _env()
 
 
 class ClockSampler:
@@ -116,7 +115,8 @@ def build_workload(args, rank):
     import jbonsai_b200 as jb
     seed = wl.SEED_NITECH if args.voice == "nitech" else wl.SEED_TOHOKU
     eng = jb.Engine.load([wl.VOICES[args.voice]])  # host front-end only: label durations
-    utts = wl.timed_batch(eng, args.utts, seed, first=rank * args.utts)
+    from jbonsai_b200.dist import rank_utterance_range
+    utts = wl.timed_batch(eng, args.utts, seed, first=rank_utterance_range(args.utts, rank)[0])
     return wl.VOICES[args.voice], utts
 
 
@@ -143,6 +143,20 @@ def cpu_oracle_rate(voice, utts, nthreads, repeats=1):
         samples = int(off[-1])
         best = dt if best is None else min(best, dt)
     return samples / RATE / best, samples, best
+
+
+def ncu_traffic_bytes():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one MLSA launch, from the committed ncu capture."""
+    try:
+        tot = 0.0
+        for line in open(os.path.join(ROOT, "profiles", "r1_mlsa_v3_full_summary.txt")):
+            if line.startswith("dram__bytes_read.sum") or line.startswith("dram__bytes_write.sum"):
+                unit = line.split("[")[1].split("]")[0]
+                val = float(line.split("=")[1])
+                tot += val * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}[unit]
+        return tot or None
+    except Exception:
+        return None
 
 
 def run_reference(args, rank, world):
@@ -184,39 +198,16 @@ def run_b200(args, rank, world, local):
 
     if jb.device_count() < 1:
         raise SystemExit("bench.py: no CUDA device; jbonsai_b200 has no CPU fallback")
-    dist = None
-    if world > 1:
-        import torch
-        import torch.distributed as dist_
-        torch.cuda.set_device(local)
-        dist_.init_process_group("nccl", device_id=torch.device("cuda", local))
-        dist = dist_
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
-
-    def max_over_ranks(x: float) -> float:
-        if dist is None:
-            return x
-        import torch
-        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(x: float) -> float:
-        if dist is None:
-            return x
-        import torch
-        t = torch.tensor([x], dtype=torch.float64, device=f"cuda:{local}")
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
+    from jbonsai_b200.dist import Reducer
+    red = Reducer(world, "nccl" if world > 1 else None, local)
+    barrier, max_over_ranks, sum_over_ranks = red.barrier, red.max, red.sum
 
     voice, utts = build_workload(args, rank)
     eng = jb.Engine.load([voice])
     eng.set_devices([local])
     if args.mlsa_variant >= 0:
         eng.set_mlsa_variant(args.mlsa_variant)
+    eng.set_device_gather(bool(args.device_gather))
 
     fp64_peak, hbm_live = jb.measure_peaks(local)
 
@@ -283,8 +274,14 @@ def run_b200(args, rank, world, local):
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     mlpg_bytes = frames * (35 * 56 + 56 * (voiced / max(samples, 1)) + 31 * 24)
     roofline = {
-        "kernel": "k_mlsa", "bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
-        "frac": achieved / fp64_peak, "traffic": None,
+        "kernel": "k_mlsa_v3" if t.get("mlsa_segments", 0) > 0 else "k_mlsa_v2", "bound": "fp64",
+        "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
+        "frac": achieved / fp64_peak, "traffic": ncu_traffic_bytes(),
+        "traffic_source": "profiles/r1_mlsa_v3_full_summary.txt (dram read + write of one launch, ncu --set full)",
+        "algorithmic_hbm_bytes": samples * 16.0 + frames * 35 * 8.0,
+        "segments": int(t.get("mlsa_segments", 0)),
+        "warmup_overhead": (t.get("mlsa_seg_frames", 0) / frames - 1.0) if frames else None,
+        "cut_check_worst": t.get("mlsa_cut_worst"), "sequential_fallback": int(t.get("mlsa_fallback", 0)),
         "peak_source": "measured live: DFMA micro-kernel (jb_device_measure_peaks); "
                        "MEASURED_PEAKS.json has no FP64 figure",
         "flops_per_sample": MLSA_FLOP_PER_SAMPLE, "msamples_per_s": samples / mlsa_s / 1e6,
@@ -312,8 +309,7 @@ def run_b200(args, rank, world, local):
                                "mlsa": mlsa_ms / args.steps},
         "samples_per_step": int(total_samples),
     }))
-    if dist is not None:
-        dist.destroy_process_group()
+    red.close()
 
 
 def main():
