@@ -53,6 +53,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--mlsa-variant", type=int, default=-1)
+    ap.add_argument("--output-mode", type=int, default=-1,
+                    help="A/B: 0 one D2H copy, 1 two filter waves, 2 zero-copy stores (library default)")
     ap.add_argument("--device-gather", type=int, default=1, help="0: host interpolates and copies vectors (A/B)")
     return ap.parse_args()
 
@@ -207,6 +209,8 @@ def run_b200(args, rank, world, local):
     eng.set_devices([local])
     if args.mlsa_variant >= 0:
         eng.set_mlsa_variant(args.mlsa_variant)
+    if args.output_mode >= 0:
+        eng.set_output_mode(args.output_mode)
     eng.set_device_gather(bool(args.device_gather))
 
     fp64_peak, hbm_live = jb.measure_peaks(local)

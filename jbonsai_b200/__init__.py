@@ -23,7 +23,8 @@ C_ABI_SYMBOLS = [
     "jb_last_error", "jb_version", "jb_device_count", "jb_device_measure_peaks", "jb_engine_load",
     "jb_engine_load_from_bytes", "jb_engine_free", "jb_engine_set_condition",
     "jb_engine_get_condition", "jb_engine_set_interpolation_weight", "jb_engine_set_devices",
-    "jb_engine_set_mlsa_variant", "jb_engine_set_mlsa_segmenting", "jb_engine_set_device_gather", "jb_engine_synthesize", "jb_engine_synthesize_batch", "jb_free",
+    "jb_engine_set_mlsa_variant", "jb_engine_set_mlsa_segmenting", "jb_engine_set_device_gather",
+    "jb_engine_set_output_mode", "jb_engine_synthesize", "jb_engine_synthesize_batch", "jb_free",
     "jb_engine_debug_batch", "jb_engine_noise", "jb_engine_durations", "jb_engine_tree_index",
     "jb_engine_stream_parameters", "jb_engine_duration_parameters", "jb_engine_gv_parameters",
     "jb_resident_prepare", "jb_resident_run", "jb_resident_fetch", "jb_resident_free",
@@ -188,6 +189,10 @@ class Engine:
 
     def set_mlsa_segmenting(self, warm_frames: int = 40, cut_tolerance: float = 1e-8) -> None:
         _check(lib.jb_engine_set_mlsa_segmenting(self._h, int(warm_frames), C.c_double(cut_tolerance)))
+
+    def set_output_mode(self, mode: int) -> None:
+        """1 (default): two filter waves, first half copied under the second; 2: zero-copy stores; 0: one copy."""
+        _check(lib.jb_engine_set_output_mode(self._h, int(mode)))
 
     # -- Engine::synthesize (src/engine.rs:294-296)
     def synthesize(self, lines: Sequence[str]) -> np.ndarray:

@@ -145,6 +145,13 @@ int jb_engine_set_device_gather(jb_engine* e, int enabled) {
   return JB_OK;
 }
 
+int jb_engine_set_output_mode(jb_engine* e, int mode) {
+  JB_TRY
+  if (mode < 0 || mode > 2) throw jb::Error(jb::kErrArgument, "output mode must be 0, 1 or 2");
+  e->e->output_mode = mode;
+  JB_CATCH
+}
+
 int jb_engine_set_mlsa_segmenting(jb_engine* e, int warm_frames, double cut_tolerance) {
   JB_TRY
   if (warm_frames < 0 || !(cut_tolerance >= 0.0))

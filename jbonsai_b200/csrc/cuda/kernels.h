@@ -158,10 +158,12 @@ struct MlsaSegments {
   const MlsaSegment* seg;  // [n_seg], six consecutive segments share a warp (host sorts by length)
   double* state;           // [n_seg][2][kMlsaSegStateDoubles] cut-check taps, or nullptr
 };
-// Filters d.wave into d.out; then (state != nullptr) writes the largest state mismatch over all
-// cuts into *worst (device), for the host to compare with its tolerance.
+// Filters segments [seg_first, seg_first + seg_count) of d.wave into d.out (one launch = one wave).
 int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, const MlsaSegments& sg,
-                   double* worst, cudaStream_t stream);
+                   int seg_first, int seg_count, cudaStream_t stream);
+// After every wave has run: the largest state mismatch over all cuts -> *worst (device), for the
+// host to compare with its tolerance.
+int launch_mlsa_seg_check(const MlsaSegments& sg, double* worst, cudaStream_t stream);
 
 // Streaming: copy frames [frame_begin, frame_begin+frame_count) of every utterance into
 // chunk[n_utt][frame_count*fperiod] (zero padded past the end of an utterance).

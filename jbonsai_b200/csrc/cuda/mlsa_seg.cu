@@ -75,12 +75,12 @@ struct WarpShared {
 
 template <int WPB>
 __global__ void __launch_bounds__(32 * WPB, 2)
-k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg) {
+k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg_first, int seg_end) {
   __shared__ __align__(16) WarpShared sh[WPB];
 
   const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int warp = blockIdx.x * WPB + wib;
-  if (warp * kSlots >= sg.n_seg) return;  // whole warp leaves; warps of a block never sync with each other
+  if (seg_first + warp * kSlots >= seg_end) return;  // whole warp leaves; warps of a block never sync with each other
   WarpShared& S = sh[wib];
   SlotInfo* const info = S.info;
 
@@ -88,8 +88,8 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg) {
   // ---- slot table
   if (lane < kSlots) {
     SlotInfo si;
-    const int sid = warp * kSlots + lane;
-    if (sid < sg.n_seg) {
+    const int sid = seg_first + warp * kSlots + lane;
+    if (sid < seg_end) {
       const MlsaSegment s = sg.seg[sid];
       const long long foff = b.frame_off[s.utt];
       si.in_base = (foff + s.warm) * (long long)fp;
@@ -287,21 +287,23 @@ __global__ void k_mlsa_seg_check(MlsaSegments sg, double* worst) {
 }  // namespace
 
 int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, const MlsaSegments& sg,
-                   double* worst, cudaStream_t stream) {
-  if (sg.n_seg == 0) return 0;
-  if (p.nmcp != kNM || p.fperiod % kCH != 0 || d.out == nullptr || d.out == d.wave)
+                   int seg_first, int seg_count, cudaStream_t stream) {
+  if (seg_count <= 0) return 0;
+  if (p.nmcp != kNM || p.fperiod % kCH != 0 || d.out == nullptr || d.out == d.wave || seg_first < 0 ||
+      seg_first + seg_count > sg.n_seg)
     return (int)cudaErrorInvalidValue;
-  const int warps = (sg.n_seg + kSlots - 1) / kSlots;
-  k_mlsa_v3<kWPB><<<(warps + kWPB - 1) / kWPB, 32 * kWPB, 0, stream>>>(b, p, d, sg);
-  cudaError_t e = cudaGetLastError();
+  const int warps = (seg_count + kSlots - 1) / kSlots;
+  k_mlsa_v3<kWPB><<<(warps + kWPB - 1) / kWPB, 32 * kWPB, 0, stream>>>(b, p, d, sg, seg_first,
+                                                                        seg_first + seg_count);
+  return (int)cudaGetLastError();
+}
+
+int launch_mlsa_seg_check(const MlsaSegments& sg, double* worst, cudaStream_t stream) {
+  if (sg.n_seg == 0 || worst == nullptr || sg.state == nullptr) return 0;
+  cudaError_t e = cudaMemsetAsync(worst, 0, sizeof(double), stream);
   if (e != cudaSuccess) return (int)e;
-  if (worst && sg.state) {
-    e = cudaMemsetAsync(worst, 0, sizeof(double), stream);
-    if (e != cudaSuccess) return (int)e;
-    k_mlsa_seg_check<<<sg.n_seg, 64, 0, stream>>>(sg, worst);
-    e = cudaGetLastError();
-  }
-  return (int)e;
+  k_mlsa_seg_check<<<sg.n_seg, 64, 0, stream>>>(sg, worst);
+  return (int)cudaGetLastError();
 }
 
 }  // namespace jbk

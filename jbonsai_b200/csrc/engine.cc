@@ -142,6 +142,8 @@ class DeviceCtx {
   cudaStream_t stream = nullptr;
   cudaStream_t stream2 = nullptr;  // side stream: LF0 solve -> pitch -> pulse train run beside MCP/LPF
   cudaEvent_t evx[2];
+  cudaStream_t stream_copy = nullptr;  // device-to-host copies of finished filter waves
+  cudaEvent_t evw[2];
   std::mutex mu;  // one in-flight batch per (engine, device)
   double* d_noise = nullptr;
   size_t noise_len = 0;
@@ -182,7 +184,9 @@ class DeviceCtx {
     JB_CUDA(cudaSetDevice(dev));
     JB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     JB_CUDA(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking));
+    JB_CUDA(cudaStreamCreateWithFlags(&stream_copy, cudaStreamNonBlocking));
     for (auto& x : evx) JB_CUDA(cudaEventCreateWithFlags(&x, cudaEventDisableTiming));
+    for (auto& x : evw) JB_CUDA(cudaEventCreateWithFlags(&x, cudaEventDisableTiming));
     for (auto& x : ev) JB_CUDA(cudaEventCreate(&x));
     JB_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
     JB_CUDA(cudaMallocHost((void**)&h_worst, sizeof(double)));
@@ -200,6 +204,8 @@ class DeviceCtx {
     if (h_worst) cudaFreeHost(h_worst);
     for (auto& x : ev) cudaEventDestroy(x);
     for (auto& x : evx) cudaEventDestroy(x);
+    for (auto& x : evw) cudaEventDestroy(x);
+    if (stream_copy) cudaStreamDestroy(stream_copy);
     if (stream2) cudaStreamDestroy(stream2);
     if (stream) cudaStreamDestroy(stream);
   }
@@ -366,12 +372,16 @@ struct Engine::Resident {
   jbk::MlsaSegments segs{};
   double* d_worst = nullptr;
   int64_t seg_frames = 0;          // frames filtered including warm-up
+  std::vector<int32_t> wave_seg_first;  // [waves+1] segment range of every filter launch
+  std::vector<int32_t> wave_utt_first;  // [waves+1] utterance range whose output that launch completes
   bool used_fallback = false;      // the last pass re-ran the sequential kernel
+  bool copied_by_waves = false;    // the last pass already queued its device-to-host copies
+  cudaEvent_t kernels_end = nullptr;  // recorded after the last kernel of the last pass (variant 3)
   const double* result = nullptr;  // device waveform of the last pass
   // kernels per pass: expand, 3 solves (+ GV kernels), 2 frame preps, pulse (memset excluded),
   // excitation, MLSA (+ cut check for variant 3)
   int launches() const {
-    int n = 1 + 3 + 2 + 3 + (segs.n_seg > 0 ? 1 : 0);
+    int n = 1 + 3 + 2 + 3 + (segs.n_seg > 0 ? (int)wave_seg_first.size() - 1 : 0);
     for (int i = 0; i < 3; ++i) n += gathered[i] ? 1 : 0;
     for (int i = 0; i < streams.n; ++i) n += streams.s[i].has_gv ? 1 : 0;
     return n;
@@ -394,7 +404,7 @@ static jbk::WindowSet make_windows(const Windows& w) {
 // Batching layer: pack the state-level parameters of `packs` into one pinned blob, copy it to
 // the device, and lay out every work array of the pipeline in one arena.
 Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const UtterancePack* packs,
-                                        size_t n_utt, bool streaming, const Condition& cond) {
+                                        size_t n_utt, bool streaming, const Condition& cond, int mlsa_waves) {
   std::unique_ptr<Engine::Resident> r(new Engine::Resident());
   r->ctx = ctx;
   r->n_utt = (int)n_utt;
@@ -424,56 +434,82 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   // MLSA variant 3: cut every utterance into time segments (kernels.h). The target is enough
   // segments for kSegWarpsPerSmsp warps of six on every warp scheduler; a segment is never shorter
   // than kSegMinFrames of its own, so small batches simply run fewer warps.
+  // With `mlsa_waves` = 2 (Engine::synthesize_batch) the utterances form two groups of about equal
+  // frame count, each cut into its own full wave of segments and filtered by its own launch, so that
+  // the device-to-host copy of the first group overlaps the filter of the second.
   std::vector<jbk::MlsaSegment> segs;
+  r->wave_seg_first.assign(1, 0);
+  r->wave_utt_first.assign(1, 0);
   if (!streaming && TF > 0) {
     const int64_t W = e.mlsa_warm_frames;
     const int64_t target = (int64_t)ctx->sm_count * 4 * kSegWarpsPerSmsp * 6;
-    int64_t S = std::max<int64_t>(kSegMinFrames, (TF + target - 1) / target);
-    auto cut = [&](int64_t S) {
-      segs.clear();
-      for (size_t u = 0; u < n_utt; ++u) {
-        const int64_t T = (int64_t)packs[u].nframes;
-        if (T <= 0) continue;
-        int64_t G = std::max<int64_t>(1, (T + S / 2) / S);
-        // equal filtered length L for every segment: the first owns L frames, the others L - W
-        while (G > 1 && (T + (G - 1) * W) / G - W < kSegMinFrames / 2) --G;
-        const int64_t L = (T + (G - 1) * W + G - 1) / G;
-        int64_t begin = 0;
-        for (int64_t k = 0; k < G && begin < T; ++k) {
-          int64_t end = (k == G - 1) ? T : std::min<int64_t>(T, begin + (k == 0 ? L : L - W));
-          jbk::MlsaSegment sg;
-          sg.utt = (int32_t)u;
-          sg.begin = (int32_t)begin;
-          sg.end = (int32_t)end;
-          sg.warm = (int32_t)std::max<int64_t>(0, begin - W);
-          sg.prev = k == 0 ? -1 : (int32_t)(segs.size() - 1);  // index before sorting, remapped below
-          segs.push_back(sg);
-          begin = end;
+    int waves = std::max(1, mlsa_waves);
+    if (TF < (int64_t)waves * target * kSegMinFrames) waves = 1;  // too small to fill two waves
+    std::vector<size_t> ucut(waves + 1, n_utt);
+    ucut[0] = 0;
+    for (int wv = 1; wv < waves; ++wv) {
+      size_t u = ucut[wv - 1];
+      while (u < n_utt && r->frame_off[u] < TF * wv / waves) ++u;
+      ucut[wv] = u;
+    }
+    for (int wv = 0; wv < waves; ++wv) {
+      const size_t ua = ucut[wv], ub = ucut[wv + 1];
+      const int64_t TFw = r->frame_off[ub] - r->frame_off[ua];
+      if (TFw <= 0) continue;
+      std::vector<jbk::MlsaSegment> ws;
+      auto cut = [&](int64_t S) {
+        ws.clear();
+        for (size_t u = ua; u < ub; ++u) {
+          const int64_t T = (int64_t)packs[u].nframes;
+          if (T <= 0) continue;
+          int64_t G = std::max<int64_t>(1, (T + S / 2) / S);
+          // equal filtered length L for every segment: the first owns L frames, the others L - W
+          while (G > 1 && (T + (G - 1) * W) / G - W < kSegMinFrames / 2) --G;
+          const int64_t L = (T + (G - 1) * W + G - 1) / G;
+          int64_t begin = 0;
+          for (int64_t k = 0; k < G && begin < T; ++k) {
+            int64_t end = (k == G - 1) ? T : std::min<int64_t>(T, begin + (k == 0 ? L : L - W));
+            jbk::MlsaSegment sg;
+            sg.utt = (int32_t)u;
+            sg.begin = (int32_t)begin;
+            sg.end = (int32_t)end;
+            sg.warm = (int32_t)std::max<int64_t>(0, begin - W);
+            sg.prev = k == 0 ? -1 : (int32_t)(ws.size() - 1);  // index before sorting, remapped below
+            ws.push_back(sg);
+            begin = end;
+          }
         }
-      }
-    };
-    cut(S);
-    // One wave: all segments run about equally long, so a grid slightly larger than the chip holds
-    // (target segments) would leave a second, nearly empty wave as long as the first.
-    for (int it = 0; it < 64 && (int64_t)segs.size() > target && (int64_t)segs.size() < 2 * target; ++it) {
-      S += std::max<int64_t>(1, S / 50);
+      };
+      int64_t S = std::max<int64_t>(kSegMinFrames, (TFw + target - 1) / target);
       cut(S);
+      // One wave: all segments run about equally long, so a grid slightly larger than the chip holds
+      // (target segments) would leave a second, nearly empty wave as long as the first.
+      for (int it = 0; it < 64 && (int64_t)ws.size() > target && (int64_t)ws.size() < 2 * target; ++it) {
+        S += std::max<int64_t>(1, S / 50);
+        cut(S);
+      }
+      // six consecutive segments share a warp and run as long as the longest of them
+      std::vector<int32_t> perm(ws.size()), where(ws.size());
+      for (size_t i = 0; i < ws.size(); ++i) perm[i] = (int32_t)i;
+      std::stable_sort(perm.begin(), perm.end(), [&](int32_t x, int32_t y) {
+        return ws[x].end - ws[x].warm > ws[y].end - ws[y].warm;
+      });
+      for (size_t i = 0; i < perm.size(); ++i) where[perm[i]] = (int32_t)i;
+      const int32_t base = (int32_t)segs.size();
+      if (wv > 0) {
+        r->wave_seg_first.push_back(base);
+        r->wave_utt_first.push_back((int32_t)ua);
+      }
+      for (size_t i = 0; i < perm.size(); ++i) {
+        jbk::MlsaSegment sg = ws[perm[i]];
+        if (sg.prev >= 0) sg.prev = base + where[sg.prev];
+        r->seg_frames += sg.end - sg.warm;
+        segs.push_back(sg);
+      }
     }
-    // six consecutive segments share a warp and run as long as the longest of them
-    std::vector<int32_t> perm(segs.size()), where(segs.size());
-    for (size_t i = 0; i < segs.size(); ++i) perm[i] = (int32_t)i;
-    std::stable_sort(perm.begin(), perm.end(), [&](int32_t x, int32_t y) {
-      return segs[x].end - segs[x].warm > segs[y].end - segs[y].warm;
-    });
-    for (size_t i = 0; i < perm.size(); ++i) where[perm[i]] = (int32_t)i;
-    std::vector<jbk::MlsaSegment> sorted(segs.size());
-    for (size_t i = 0; i < perm.size(); ++i) {
-      sorted[i] = segs[perm[i]];
-      if (sorted[i].prev >= 0) sorted[i].prev = where[sorted[i].prev];
-      r->seg_frames += sorted[i].end - sorted[i].warm;
-    }
-    segs.swap(sorted);
   }
+  r->wave_seg_first.push_back((int32_t)segs.size());
+  r->wave_utt_first.push_back((int32_t)n_utt);
   const size_t o_segs = in.take(segs.size() * sizeof(jbk::MlsaSegment));
   size_t o_mean[3], o_vari[3], o_msd[3], o_gvm[3], o_gvv[3], o_gsw[3], o_rows[3];
   int dim[3], nwin[3], is_msd[3], has_gv[3], nvoice[3];
@@ -721,21 +757,57 @@ static void launch_mlpg_all(Engine::Resident* r, bool with_pulse) {
   JB_CUDA(cudaStreamWaitEvent(st, c->evx[1], 0));
 }
 
+// Where the waveform goes while the filter is still running: wave w's utterance range is copied to
+// host + its sample offset on `copy_stream` as soon as launch w has finished.
+struct WaveCopy {
+  double* host = nullptr;  // destination of utterance 0 of this resident batch
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t done = nullptr;  // recorded after the last copy (or after the filter when `direct`)
+  bool direct = false;         // the filter stores straight into `host` (pinned, device-visible)
+};
+
 static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_excitation,
-                           cudaEvent_t after_exc, bool pulse_done) {
+                           cudaEvent_t after_exc, bool pulse_done, const WaveCopy* wc = nullptr) {
   cudaStream_t st = r->ctx->stream;
   if (!pulse_done) JB_LAUNCH(jbk::launch_pulse(r->layout, r->vp, r->vd, r->total_samples, st));
   JB_LAUNCH(jbk::launch_excitation(r->layout, r->vp, r->vd, r->total_frames, st));
   if (after_exc) JB_CUDA(cudaEventRecord(after_exc, st));
   r->result = r->vd.wave;
   r->used_fallback = false;
+  r->copied_by_waves = false;
+  r->kernels_end = nullptr;
   if (stop_after_excitation) return;
   const bool v3 = (variant < 0 || variant == 3) && r->segs.n_seg > 0 && r->vp.nmcp == 35 &&
                   r->vp.fperiod % 16 == 0 && r->vd.frame_begin == 0 && r->vd.frame_count < 0;
   if (v3) {
-    JB_LAUNCH(jbk::launch_mlsa_v3(r->layout, r->vp, r->vd, r->segs, r->d_worst, st));
+    const int waves = (int)r->wave_seg_first.size() - 1;
+    const bool direct = wc && wc->direct;
+    jbk::VocoderDev vd = r->vd;
+    if (direct) vd.out = wc->host;  // zero-copy: output stores cross PCIe while the filter runs
+    for (int w = 0; w < waves; ++w) {
+      const int s0 = r->wave_seg_first[w], s1 = r->wave_seg_first[w + 1];
+      JB_LAUNCH(jbk::launch_mlsa_v3(r->layout, r->vp, vd, r->segs, s0, s1 - s0, st));
+      if (wc && !direct) {
+        const int64_t f0 = r->frame_off[(size_t)r->wave_utt_first[w]];
+        const int64_t f1 = r->frame_off[(size_t)r->wave_utt_first[w + 1]];
+        const int64_t n0 = f0 * r->vp.fperiod, n1 = f1 * r->vp.fperiod;
+        JB_CUDA(cudaEventRecord(r->ctx->evw[w & 1], st));
+        JB_CUDA(cudaStreamWaitEvent(wc->copy_stream, r->ctx->evw[w & 1], 0));
+        if (n1 > n0)
+          JB_CUDA(cudaMemcpyAsync(wc->host + n0, r->vd.out + n0, (size_t)(n1 - n0) * 8,
+                                  cudaMemcpyDeviceToHost, wc->copy_stream));
+      }
+    }
+    JB_LAUNCH(jbk::launch_mlsa_seg_check(r->segs, r->d_worst, st));
+    // end of the kernels for the timers: the 8-byte copy below can queue behind a wave copy
+    JB_CUDA(cudaEventRecord(r->ctx->ev[7], st));
+    r->kernels_end = r->ctx->ev[7];
     JB_CUDA(cudaMemcpyAsync(r->ctx->h_worst, r->d_worst, sizeof(double), cudaMemcpyDeviceToHost, st));
     r->result = r->vd.out;
+    if (wc) {
+      JB_CUDA(cudaEventRecord(wc->done, direct ? st : wc->copy_stream));
+      r->copied_by_waves = true;
+    }
   } else {
     JB_LAUNCH(jbk::launch_mlsa(r->layout, r->vp, r->vd, variant == 3 ? -1 : variant, st));
   }
@@ -871,12 +943,15 @@ void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts,
       DeviceCtx* c = ctxs[k];
       std::lock_guard<std::mutex> g(c->mu);
       const double p0 = now_ms();
-      Resident* r = make_resident(*this, c, packs.data() + u0, u1 - u0, false, condition);
+      // two filter waves: the copy of the first half of the waveform overlaps the second launch
+      Resident* r = make_resident(*this, c, packs.data() + u0, u1 - u0, false, condition,
+                                  (!dbg && output_mode == 1) ? 2 : 1);
       struct Guard {
         DeviceCtx* c;
         Resident* r;
         ~Guard() {
           cudaStreamSynchronize(c->stream);
+          cudaStreamSynchronize(c->stream_copy);
           c->dfree(r->d_in, r->in_cap);
           c->dfree(r->d_work, r->work_cap);
           delete r;
@@ -887,12 +962,20 @@ void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts,
       JB_CUDA(cudaEventRecord(c->ev[2], c->stream));
       launch_mlpg_all(r, true);
       JB_CUDA(cudaEventRecord(c->ev[3], c->stream));
-      launch_vocoder(r, mlsa_variant, dbg && dbg->stop_after_excitation, c->ev[4], true);
+      WaveCopy wc;
+      wc.host = host + (*out_off)[u0];
+      wc.copy_stream = c->stream_copy;
+      wc.done = c->ev[6];
+      wc.direct = output_mode == 2;
+      launch_vocoder(r, mlsa_variant, dbg && dbg->stop_after_excitation, c->ev[4], true,
+                     (dbg || output_mode == 0) ? nullptr : &wc);
       JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
-      if (r->total_samples)
-        JB_CUDA(cudaMemcpyAsync(host + (*out_off)[u0], r->result, (size_t)r->total_samples * 8,
-                                cudaMemcpyDeviceToHost, c->stream));
-      JB_CUDA(cudaEventRecord(c->ev[6], c->stream));
+      if (!r->copied_by_waves) {
+        if (r->total_samples)
+          JB_CUDA(cudaMemcpyAsync(host + (*out_off)[u0], r->result, (size_t)r->total_samples * 8,
+                                  cudaMemcpyDeviceToHost, c->stream));
+        JB_CUDA(cudaEventRecord(c->ev[6], c->stream));
+      }
       if (dbg) {
         const jbk::StreamSet& ss = r->streams;
         const size_t TF = (size_t)r->total_frames;
@@ -911,6 +994,7 @@ void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts,
         dbg->frame_off = r->frame_off;
       }
       JB_CUDA(cudaStreamSynchronize(c->stream));
+      if (r->copied_by_waves) JB_CUDA(cudaStreamSynchronize(c->stream_copy));
       if (mlsa_cut_check_failed(r, mlsa_cut_tolerance)) {
         // the copy above carried a waveform with a bad cut: redo the filter sequentially, copy again
         mlsa_sequential_rerun(r);
@@ -926,11 +1010,13 @@ void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts,
       t.mlsa_fallback = r->used_fallback ? 1 : 0;
       float f = 0;
       JB_CUDA(cudaEventElapsedTime(&f, c->ev[0], c->ev[1])); t.h2d_ms = f;
-      JB_CUDA(cudaEventElapsedTime(&f, c->ev[2], c->ev[5])); t.kernels_ms = f;
+      cudaEvent_t kend = (r->kernels_end && !r->used_fallback) ? r->kernels_end : c->ev[5];
+      JB_CUDA(cudaEventElapsedTime(&f, c->ev[2], kend)); t.kernels_ms = f;
       JB_CUDA(cudaEventElapsedTime(&f, c->ev[2], c->ev[3])); t.mlpg_ms = f;
       JB_CUDA(cudaEventElapsedTime(&f, c->ev[3], c->ev[4])); t.excitation_ms = f;
-      JB_CUDA(cudaEventElapsedTime(&f, c->ev[4], c->ev[5])); t.mlsa_ms = f;
-      JB_CUDA(cudaEventElapsedTime(&f, c->ev[5], c->ev[6])); t.d2h_ms = f;
+      JB_CUDA(cudaEventElapsedTime(&f, c->ev[4], kend)); t.mlsa_ms = f;
+      // with two filter waves the first copy runs under the second launch: this is the tail only
+      JB_CUDA(cudaEventElapsedTime(&f, kend, c->ev[6])); t.d2h_ms = f > 0 ? f : 0;
       t.h2d_bytes = r->h2d_bytes;
       t.d2h_bytes = r->total_samples * 8;
       t.total_frames = r->total_frames;

@@ -62,6 +62,11 @@ class Engine {
   bool device_gather = true;
   int mlsa_warm_frames = 40;
   double mlsa_cut_tolerance = 1e-8;
+  // How synthesize_batch brings the waveform to the host: 0 = one copy after the filter, 1 = two
+  // filter waves with the first half copied under the second (default), 2 = the filter stores
+  // straight into the pinned output buffer (zero-copy; measured slower: SM stores reach ~34 GB/s
+  // over PCIe against ~52 GB/s for the copy engine).
+  int output_mode = 1;
 
   // Engine::synthesize for a batch: utterance u = lines[line_off[u] .. line_off[u+1]).
   // `out` is a pinned host buffer owned by the engine's pool: release with free_output().
@@ -102,7 +107,7 @@ class Engine {
   const std::vector<double>& noise_table(size_t n) const;
   std::vector<UtterancePack> build_packs(const std::vector<std::vector<std::string>>& utts) const;
   static Resident* make_resident(const Engine& e, DeviceCtx* ctx, const UtterancePack* packs,
-                                 size_t n_utt, bool streaming, const Condition& cond);
+                                 size_t n_utt, bool streaming, const Condition& cond, int mlsa_waves = 1);
 };
 
 // SpeechGenerator (src/speech.rs) for many utterances at once: MLPG up front, then the
