@@ -53,6 +53,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--mlsa-variant", type=int, default=-1)
+    ap.add_argument("--beta", type=float, default=0.0, help="post-filter coefficient (default off, as the reference)")
     ap.add_argument("--output-mode", type=int, default=-1,
                     help="A/B: 0 one D2H copy, 1 two filter waves, 2 zero-copy stores (library default)")
     ap.add_argument("--device-gather", type=int, default=1, help="0: host interpolates and copies vectors (A/B)")
@@ -126,7 +127,7 @@ def config_dict(args, world):
     return {
         "workload": f"BASELINE config 3: batch of {args.utts} synthetic label sequences (~5 s each: 4-6 s "
                     f"genji.lab slices between sil labels) per GPU, voice {args.voice}, 48 kHz, fperiod 240",
-        "utterances_per_gpu": args.utts, "voice": args.voice, "n_gpus": world,
+        "utterances_per_gpu": args.utts, "voice": args.voice, "n_gpus": world, "beta": args.beta,
         "parallelism": f"utterance-sharded x{world}, no collective",
         "l2": "inputs and work arrays (> 4 GB per step) are far larger than the 126 MB L2",
     }
@@ -211,6 +212,8 @@ def run_b200(args, rank, world, local):
         eng.set_mlsa_variant(args.mlsa_variant)
     if args.output_mode >= 0:
         eng.set_output_mode(args.output_mode)
+    if args.beta > 0:
+        eng.set("beta", args.beta)
     eng.set_device_gather(bool(args.device_gather))
 
     fp64_peak, hbm_live = jb.measure_peaks(local)

@@ -122,7 +122,10 @@ struct VocoderDev {
   const double* lf0;    // [total_frames]
   const double* lpf;    // [total_frames][nlpf]
   const double* noise;  // [>= max samples per utterance] global Gaussian sequence
-  double* b;            // [total_frames][nmcp]  mc2b(mcp)   (out of frame_prep)
+  double* b;            // [total_frames][nmcp]  mc2b(mcp), post-filtered when beta > 0 (out of frame_prep / postfilter)
+  const double* b_first;  // [n_utt][nmcp] or nullptr. beta > 0 only: mc2b of the un-filtered first frame, the
+                          // coefficients the reference starts from (is_first, vocoder/mod.rs:79-88); nullptr =
+                          // row 0 of `b` (identical when beta == 0)
   double* pitch;        // [total_frames]        p per frame (out of frame_prep)
   double* pulse;        // [total_samples]       pulse amplitude or 0 (out of pitch kernel)
   double* wave;         // [total_samples]       excitation*gain; variants 0-2 filter it in place
@@ -135,6 +138,11 @@ struct VocoderDev {
 // what: bit 0 = pitch period from lf0, bit 1 = b = mc2b(mcp)
 int launch_frame_prep(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,
                       int64_t total_frames, int what, cudaStream_t stream);
+// beta > 0 (MelCepstrum::postfilter_mcp, cepstrum.rs:23-37): first copies row 0 of every utterance
+// of d.b (= mc2b of the raw first frame) to b_first[n_utt][nmcp], then rewrites every row of d.b as
+// mc2b(postfilter_mcp(c)). Runs after launch_frame_prep(what & 2). No-op when beta <= 0 or nmcp <= 2.
+int launch_postfilter(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, double beta,
+                      double* b_first, int64_t total_frames, cudaStream_t stream);
 int launch_pulse(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, int64_t total_samples,
                  cudaStream_t stream);
 int launch_excitation(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,

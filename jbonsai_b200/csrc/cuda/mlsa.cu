@@ -149,10 +149,11 @@ __global__ void __launch_bounds__(32) k_mlsa_v2(BatchLayout b, VocoderParams p, 
     }
     cc1 = bf[1];
     ccn1 = bn[1];
-    if (f0 == 0) {  // is_first: coefficients = mc2b(first frame)
+    if (f0 == 0) {  // is_first: coefficients = mc2b(first frame), before the post-filter
+      const double* b1 = d.b_first ? d.b_first + (int64_t)u * kNM : bf;
 #pragma unroll
-      for (int i = 0; i < 6; ++i) c[i] = cc[i];
-      c1 = cc1;
+      for (int i = 0; i < 6; ++i) c[i] = cvalid[i] ? b1[jtap[i]] : 0.0;
+      c1 = b1[1];
     }
 #pragma unroll
     for (int i = 0; i < 6; ++i) cinc[i] = (cc[i] - c[i]) / fper;

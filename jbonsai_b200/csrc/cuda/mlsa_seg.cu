@@ -61,6 +61,7 @@ struct SlotInfo {
   int own0;            // begin - warm: frames whose output is discarded
   int seg;             // segment id (state slot), -1 for an empty slot
   int prev;            // id of the segment before this one in the utterance, -1 if none
+  int utt;             // utterance (row of VocoderDev::b_first)
 };
 
 // Shared memory of one warp. Every array is indexed so that the 16 lanes of a half-warp touch 16
@@ -100,8 +101,10 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
       si.own0 = s.begin - s.warm;
       si.seg = sid;
       si.prev = s.prev;
+      si.utt = s.utt;
     } else {
       si.in_base = 0; si.b_base = 0; si.warm = 0; si.last_frame = 0; si.nfr = 0; si.own0 = 0; si.seg = -1; si.prev = -1;
+      si.utt = 0;
     }
     info[lane] = si;
   }
@@ -132,7 +135,10 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
   };
   double c[kTaps], cinc[kTaps];
   {
-    const double* r0 = frame_row(-1);  // frame 0 itself for the first frame (mod.rs:79-109)
+    // the frame before the first is frame 0 itself (mod.rs:79-109); with beta > 0 it is mc2b of the
+    // un-filtered first frame
+    const double* r0 = (me.warm == 0 && d.b_first != nullptr) ? d.b_first + (long long)info[g].utt * kNM + 1
+                                                              : frame_row(-1);
     const double* r1 = frame_row(0);
 #pragma unroll
     for (int k = 0; k < kTaps; ++k) {

@@ -222,7 +222,7 @@ __global__ void __launch_bounds__(256) k_excitation(BatchLayout b, VocoderParams
   }
   if (threadIdx.x == blockDim.x - 1) {
     const double cc = d.b[gf * p.nmcp];
-    double c = f > 0 ? d.b[(gf - 1) * p.nmcp] : cc;
+    double c = f > 0 ? d.b[(gf - 1) * p.nmcp] : (d.b_first ? d.b_first[(int64_t)u * p.nmcp] : cc);
     const double cinc = (cc - c) / (double)fp;
     for (int i = 0; i < fp; ++i) {
       s_c0[i] = c;
@@ -299,7 +299,7 @@ __global__ void __launch_bounds__(32 * kExWarps) k_excitation_w(BatchLayout b, V
   }
   if (lane == 31) {  // coefficients[0] of every sample, by repeated addition (mod.rs:133-135)
     const double cc = d.b[gf * p.nmcp];
-    double c = f > 0 ? d.b[(gf - 1) * p.nmcp] : cc;
+    double c = f > 0 ? d.b[(gf - 1) * p.nmcp] : (d.b_first ? d.b_first[(int64_t)u * p.nmcp] : cc);
     const double cinc = (cc - c) / (double)fp;
     for (int i = 0; i < fp; ++i) {
       s_c0[w][i] = c;
@@ -445,7 +445,8 @@ __global__ void __launch_bounds__(32 * WPB) k_mlsa_v0(BatchLayout b, VocoderPara
     // frame prologue (mod.rs:116-125): cc = mc2b(spectrum); cinc = (cc - c)/fperiod
     for (int k = gl; k < NM; k += G) {
       const double cc = factive ? d.b[gf * NM + k] : 0.0;
-      const double c = (f == 0 || !factive) ? cc : s_c[k][sg];  // is_first: c = mc2b(first frame)
+      // is_first: c = mc2b(first frame), before the post-filter (mod.rs:79-88)
+      const double c = !factive ? cc : (f == 0 ? (d.b_first ? d.b_first[(int64_t)uu * NM + k] : cc) : s_c[k][sg]);
       s_c[k][sg] = c;
       s_cc[k][sg] = cc;
       s_cinc[k][sg] = (cc - c) / (double)p.fperiod;
@@ -621,10 +622,11 @@ __global__ void __launch_bounds__(32) k_mlsa_v1(BatchLayout b, VocoderParams p, 
 #pragma unroll
       for (int i = 0; i < 6; ++i) cc[i] = cvalid[i] ? bf[jtap[i]] : 0.0;
       cc1 = bf[1];
-      if (f == 0) {  // is_first: coefficients = mc2b(first frame)
+      if (f == 0) {  // is_first: coefficients = mc2b(first frame), before the post-filter
+        const double* b1 = d.b_first ? d.b_first + (int64_t)u * NM : bf;
 #pragma unroll
-        for (int i = 0; i < 6; ++i) c[i] = cc[i];
-        c1 = cc1;
+        for (int i = 0; i < 6; ++i) c[i] = cvalid[i] ? b1[jtap[i]] : 0.0;
+        c1 = b1[1];
       }
 #pragma unroll
       for (int i = 0; i < 6; ++i) cinc[i] = (cc[i] - c[i]) / fper;

@@ -310,8 +310,6 @@ std::vector<double> Engine::noise_prefix(size_t n) const {
 std::vector<UtterancePack> Engine::build_packs(const std::vector<std::vector<std::string>>& utts) const {
   if (condition.stage != 0)
     throw Error(kErrUnsupported, "stage != 0 (GAMMA option: LSP/MGLSA vocoder) is not built yet");
-  if (condition.beta > 0.0)
-    throw Error(kErrUnsupported, "beta > 0 (mel-cepstral post-filter) is not built yet");
   if (voices_.global_metadata().num_streams < 3 || voices_.stream_metadata(2).vector_length == 0)
     throw Error(kErrUnsupported, "voices without an LPF stream are not built yet");
   std::vector<UtterancePack> packs(utts.size());
@@ -374,6 +372,7 @@ struct Engine::Resident {
   int64_t seg_frames = 0;          // frames filtered including warm-up
   std::vector<int32_t> wave_seg_first;  // [waves+1] segment range of every filter launch
   std::vector<int32_t> wave_utt_first;  // [waves+1] utterance range whose output that launch completes
+  double beta = 0.0;               // > 0: post-filter kernels run after frame_prep
   bool used_fallback = false;      // the last pass re-ran the sequential kernel
   bool copied_by_waves = false;    // the last pass already queued its device-to-host copies
   cudaEvent_t kernels_end = nullptr;  // recorded after the last kernel of the last pass (variant 3)
@@ -381,7 +380,7 @@ struct Engine::Resident {
   // kernels per pass: expand, 3 solves (+ GV kernels), 2 frame preps, pulse (memset excluded),
   // excitation, MLSA (+ cut check for variant 3)
   int launches() const {
-    int n = 1 + 3 + 2 + 3 + (segs.n_seg > 0 ? (int)wave_seg_first.size() - 1 : 0);
+    int n = 1 + 3 + 2 + 3 + (segs.n_seg > 0 ? (int)wave_seg_first.size() - 1 : 0) + (beta > 0.0 ? 2 : 0);
     for (int i = 0; i < 3; ++i) n += gathered[i] ? 1 : 0;
     for (int i = 0; i < streams.n; ++i) n += streams.s[i].has_gv ? 1 : 0;
     return n;
@@ -644,6 +643,8 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   const size_t w_out = segs.empty() ? 0 : wk.take((size_t)r->total_samples * 8);
   const size_t w_segstate = segs.empty() ? 0 : wk.take(segs.size() * 2 * jbk::kMlsaSegStateDoubles * 8);
   const size_t w_worst = wk.take(8);
+  const bool postfilter = cond.beta > 0.0 && dim[0] > 2;  // cepstrum.rs:24
+  const size_t w_bfirst = postfilter ? wk.take(n_utt * (size_t)dim[0] * 8) : 0;
   r->d_work = ctx->dalloc(wk.off, &r->work_cap);
   uint8_t* di = (uint8_t*)r->d_in;
   uint8_t* dw = (uint8_t*)r->d_work;
@@ -707,6 +708,8 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   r->vd.lf0 = r->streams.s[1].par;
   r->vd.lpf = r->streams.s[2].par;
   r->vd.b = (double*)(dw + w_b);
+  r->vd.b_first = postfilter ? (const double*)(dw + w_bfirst) : nullptr;
+  r->beta = postfilter ? cond.beta : 0.0;
   r->vd.pitch = (double*)(dw + w_pitch);
   r->vd.pulse = (double*)(dw + w_pulse);
   r->vd.wave = (double*)(dw + w_wave);
@@ -754,6 +757,9 @@ static void launch_mlpg_all(Engine::Resident* r, bool with_pulse) {
   JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[0], r->total_frames, st));
   JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[2], r->total_frames, st));
   JB_LAUNCH(jbk::launch_frame_prep(r->layout, r->vp, r->vd, r->total_frames, 2, st));
+  if (r->beta > 0.0)  // MelCepstrum::postfilter_mcp (cepstrum.rs:23-37): rewrites vd.b in place
+    JB_LAUNCH(jbk::launch_postfilter(r->layout, r->vp, r->vd, r->beta, const_cast<double*>(r->vd.b_first),
+                                     r->total_frames, st));
   JB_CUDA(cudaStreamWaitEvent(st, c->evx[1], 0));
 }
 

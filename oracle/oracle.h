@@ -88,6 +88,7 @@ struct Vocoder {
 // helpers exposed for kernel-granularity known-answer tests
 std::vector<double> mc2b(const double* c, size_t n, double alpha);       // cepstrum.rs:139-149
 void postfilter_mcp(std::vector<double>* c, double alpha, double beta);  // cepstrum.rs:23-37
+double b2en(const std::vector<double>& b, double alpha);                // coefficients.rs:75-78
 double fir(double* d, size_t dlen, double x, double alpha, const double* coefficients,
            bool fma);                                                    // mlsa.rs:128-163
 

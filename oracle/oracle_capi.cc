@@ -283,6 +283,16 @@ int orc_mlpg(size_t nstates, const int32_t* durations, size_t dim, size_t nwin,
   }
 }
 
+// MelCepstrum::postfilter_mcp in place on c[n]; also the impulse-response energies b2en(mc2b(c))
+// before and after (the filter's defining property: they are equal).
+void orc_postfilter(double* c, size_t n, double alpha, double beta, double* e_before, double* e_after) {
+  std::vector<double> v(c, c + n);
+  *e_before = oracle::b2en(oracle::mc2b(v.data(), n, alpha), alpha);
+  oracle::postfilter_mcp(&v, alpha, beta);
+  *e_after = oracle::b2en(oracle::mc2b(v.data(), n, alpha), alpha);
+  for (size_t i = 0; i < n; ++i) c[i] = v[i];
+}
+
 void orc_boundary_distances(const uint8_t* mask, size_t n, size_t* left, size_t* right) {
   std::vector<uint8_t> m(mask, mask + n);
   std::vector<size_t> l, r;

@@ -97,7 +97,7 @@ static std::vector<double> c2ir(const std::vector<double>& c, size_t len) {
 }
 
 // CoefficientsT::b2en (coefficients.rs:75-78)
-static double b2en(const std::vector<double>& b, double alpha) {
+double b2en(const std::vector<double>& b, double alpha) {
   std::vector<double> ir = c2ir(freqt(b2mc(b, alpha), 576 - 1, -alpha), 576);
   double s = 0.0;
   for (double x : ir) s += x * x;

@@ -108,6 +108,16 @@ def vocoder(mcp, lf0, lpf, rate=48000, fperiod=240, alpha=0.55, beta=0.0, volume
     return (out, exc) if tap else out
 
 
+def postfilter(c, alpha=0.55, beta=0.3):
+    """MelCepstrum::postfilter_mcp (cepstrum.rs:23-37) -> (c', energy before, energy after)."""
+    v = np.array(c, dtype=np.float64)
+    e0, e1 = C.c_double(), C.c_double()
+    _L.orc_postfilter.restype = None
+    _L.orc_postfilter(v.ctypes.data_as(D), C.c_size_t(len(v)), C.c_double(alpha), C.c_double(beta),
+                      C.byref(e0), C.byref(e1))
+    return v, e0.value, e1.value
+
+
 def mlpg(durations, dim, windows, mean, vari, msd, msd_threshold=0.5, gv=None, gv_weight=1.0):
     """windows: list of coefficient lists. gv: (mean[dim], vari[dim], switch[S]) or None."""
     durations = np.ascontiguousarray(durations, dtype=np.int32)

@@ -170,6 +170,38 @@ def test_condition_knobs_vs_oracle():
     assert np.abs(w - ow).max() <= WAVE_ATOL
 
 
+# ---- beta > 0: MelCepstrum::postfilter_mcp (cepstrum.rs:23-37) runs as its own kernel
+@pytest.mark.parametrize("variant", [0, 1, 2, 3])
+def test_postfilter_vs_oracle(variant):
+    e, o = jb.Engine.load([NITECH]), Oracle([NITECH])
+    e.set("beta", 0.4)
+    o.set("beta", 0.4)
+    e.set_mlsa_variant(variant)
+    utts = [SAMPLE_SENTENCE_1, SAMPLE_SENTENCE_2[:6]]
+    w, off = e.synthesize_batch(utts)
+    for u, lab in enumerate(utts):
+        ow = o.synthesize(lab, fma=True)
+        assert off[u + 1] - off[u] == len(ow)
+        assert np.abs(w[off[u]:off[u + 1]] - ow).max() <= WAVE_ATOL
+    # the filter does something: the un-filtered waveform is far away
+    e.set("beta", 0.0)
+    w0, _ = e.synthesize_batch(utts)
+    assert np.abs(w - w0).max() > 1.0
+
+
+def test_postfilter_streaming_and_tohoku():
+    e, o = jb.Engine.load([TOHOKU_NEUTRAL]), Oracle([TOHOKU_NEUTRAL])
+    e.set("beta", 0.2)
+    o.set("beta", 0.2)
+    ow = o.synthesize(SAMPLE_SENTENCE_1, fma=True)
+    w = e.synthesize(SAMPLE_SENTENCE_1)
+    assert len(w) == len(ow) and np.abs(w - ow).max() <= WAVE_ATOL
+    g = e.generator([SAMPLE_SENTENCE_1])
+    parts = g.generate_all(7)
+    g.close()
+    assert len(parts[0]) == len(ow) and np.abs(parts[0] - ow).max() <= WAVE_ATOL
+
+
 def test_unsupported_is_loud():
     e = jb.Engine.load([NITECH])
     e.set("stage", 2)

@@ -88,3 +88,29 @@ def test_batch_equals_single(nitech):
     assert list(off) == [0, 66480, 66480, 66480 + 100800]
     assert np.array_equal(w[:66480], nitech.synthesize(SAMPLE_SENTENCE_1))
     assert np.array_equal(w[66480:], nitech.synthesize(SAMPLE_SENTENCE_2))
+
+
+def test_postfilter_properties():
+    """No golden in the reference exercises beta > 0 (parity of that branch is unpinned; note that
+    the reference's freqt walks its input in ascending order, cepstrum.rs:158, unlike hts_engine, and
+    the oracle follows the reference). What can be checked is the algebra of cepstrum.rs:23-37 in the
+    mc2b domain: b[k>=2] scaled by 1+beta, b[1] -= beta*alpha*b[2], b[0] += ln(e1/e2)/2."""
+    import oracle_lib as ol
+    o = Oracle([NITECH])
+    mcp = o.parameters(SAMPLE_SENTENCE_1)[0]
+    a, beta = 0.55, 0.3
+
+    def mc2b(c):
+        b = c.copy()
+        for i in range(len(c) - 2, -1, -1):
+            b[i] = c[i] - a * b[i + 1]
+        return b
+
+    for row in mcp[::40]:
+        c2, e_before, e_after = ol.postfilter(row, a, beta)
+        b, b2 = mc2b(row), mc2b(c2)
+        assert np.allclose(b2[2:], (1 + beta) * b[2:], rtol=1e-12, atol=1e-14)
+        assert abs(b2[1] - (b[1] - beta * a * b[2])) < 1e-12
+        assert np.isfinite(b2[0]) and abs(b2[0] - b[0]) > 1e-6 and e_before > 0 and e_after > 0
+        same, _, _ = ol.postfilter(row, a, 0.0)
+        assert np.array_equal(same, row)
