@@ -16,7 +16,7 @@ from typing import Iterable, List, Optional, Sequence
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libjbonsai_b200.so")
+LIB_PATH = os.environ.get("JBONSAI_B200_LIB") or os.path.join(_HERE, "libjbonsai_b200.so")
 
 # every symbol include/jbonsai_b200.h declares (checked by tests/test_capi_symbols.py)
 C_ABI_SYMBOLS = [

@@ -50,6 +50,7 @@ struct StreamDev {
   double gv_weight;
   const double* mean;        // [total_states][nwin*dim]
   const double* vari;        // [total_states][nwin*dim]
+  double* ivar;              // [total_states][nwin*dim] work: MeanVari::with_ivar(vari) (split path)
   const double* msd;         // [total_states] (only read when is_msd)
   const double* gv_mean;     // [n_utt][dim]
   const double* gv_vari;     // [n_utt][dim]
@@ -65,8 +66,9 @@ struct StreamDev {
 };
 
 inline int mlpg_scratch_planes(int band_width, int has_gv) {
-  // factorised band (bw) + wum/g (2) [+ unfactorised band (bw) + wum copy is shared + grad (1)]
-  return band_width + 2 + (has_gv ? band_width + 1 : 0);
+  // factorised band (bw) + g + W'U^-1 mu + un-factorised band (bw) [+ solution + gradient for GV];
+  // see the plane map in mlpg.cu (the general kernel uses a subset of this)
+  return 2 * band_width + 2 + (has_gv ? 2 : 0);
 }
 
 struct StreamSet {
@@ -96,7 +98,8 @@ struct GatherStream {
 int launch_gather_states(const GatherStream& g, int64_t total_states, cudaStream_t stream);
 
 int launch_expand(const BatchLayout& b, const StreamSet& streams, cudaStream_t stream);
-int launch_mlpg(const BatchLayout& b, const StreamDev& s, int64_t total_frames, cudaStream_t stream);
+int launch_mlpg(const BatchLayout& b, const StreamDev& s, int64_t total_frames, int64_t total_states,
+                cudaStream_t stream);
 
 struct VocoderParams {
   int nmcp;     // 35

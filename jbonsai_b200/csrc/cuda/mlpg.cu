@@ -541,6 +541,243 @@ __global__ void __launch_bounds__(128) k_mlpg_solve(BatchLayout b, StreamDev s, 
   }
 }
 
+
+// ================================================================ split path (shape 1-3-3, the shipped voices)
+// The band build of mlpg.rs:31-61 has no dependence along time: frame k only needs the (mean, ivar)
+// pairs of frames k-1, k, k+1. Only the LDL^T factorisation and the two substitutions are serial. So:
+//   k_state_ivar   ivar = MeanVari::with_ivar(vari), one division per (state, window, dim)
+//   k_band_build   thread per compacted frame (loops over dim): un-factorised band + W'U^-1 mu,
+//                  written "system-major" ([utt][dim][frame]: the T frames of one system contiguous)
+//   k_ldl          thread per system: factorisation + forward substitution reading its own
+//                  contiguous stream four frames ahead (no data-dependent addresses, so the loads
+//                  run ahead of the recurrence), factorised rows written [frame][dim] (coalesced
+//                  over the dims of an utterance), then the backward substitution
+//   k_mlpg_gv      CTA per system, reads the system-major planes with unit stride
+// Every floating-point operation and its order is the one of k_mlpg_solve / the reference; only
+// where it runs changed, so the parameters stay bit-identical.
+// Plane map (each plane = total_frames * dim doubles): [0, BW) factorised band, BW: g, then
+// system-major: BW+1: W'U^-1 mu, BW+2+j: un-factorised band j, 2BW+2: solution (GV input),
+// 2BW+3: GV gradient (only when a system does not fit in shared memory).
+__global__ void __launch_bounds__(256) k_state_ivar(const double* __restrict__ vari, double* __restrict__ ivar,
+                                                    int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) ivar[i] = with_ivar(vari[i]);
+}
+
+__global__ void __launch_bounds__(128) k_band_build(BatchLayout b, StreamDev s, int64_t plane) {
+  constexpr int BW = 3, NW = 3;
+  const int u = blockIdx.y;
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t soff = b.state_off[u], foff = b.frame_off[u];
+  const int T = (int)(b.frame_off[u + 1] - foff);
+  const bool msd = s.is_msd != 0;
+  const int Tp = msd ? s.nvoiced[u] : T;
+  if (k >= Tp) return;
+  const int dim = s.dim, L = s.dim * s.nwin;
+  const int32_t* const fstate = b.frame_state + foff;
+
+  double wc[NW][3];
+#pragma unroll
+  for (int w = 0; w < NW; ++w)
+#pragma unroll
+    for (int i = 0; i < 3; ++i) wc[w][i] = (w == 0) ? (i == 0 ? s.windows.coef[0][0] : 0.0) : s.windows.coef[w][i];
+
+  // compacted frames k-1, k, k+1: state row and "inside the mask" flag (mod.rs:57-84)
+  int64_t srow[3];
+  bool edge[3], valid[3];
+#pragma unroll
+  for (int i = 0; i < 3; ++i) {
+    const int kk = k - 1 + i;
+    valid[i] = kk >= 0 && kk < Tp;
+    const int t = valid[i] ? (msd ? s.vidx[foff + kk] : kk) : 0;
+    srow[i] = (soff + fstate[t]) * L;
+    const int l = msd ? s.left[foff + t] : t;
+    const int r = msd ? s.right[foff + t] : T - 1 - t;
+    edge[i] = l < 1 || r < 1;  // 3-tap window: left/right width 1
+  }
+  double* const sys = s.scratch + foff * dim + k;  // + d * T: system d of this utterance
+  for (int d = 0; d < dim; ++d) {
+    double m_[NW][3], iv_[NW][3];
+#pragma unroll
+    for (int w = 0; w < NW; ++w)
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        const bool need = valid[i] && (w != 0 || i == 1);
+        m_[w][i] = need ? s.mean[srow[i] + dim * w + d] : 0.0;
+        iv_[w][i] = need ? ((w != 0 && edge[i]) ? 0.0 : s.ivar[srow[i] + dim * w + d]) : 0.0;
+      }
+    double row[BW] = {0.0, 0.0, 0.0};
+    double wum = 0.0;
+    {  // window 0: static, width 1
+      const double coef = wc[0][0];
+      if (coef != 0.0) {
+        const double wu = coef * iv_[0][1];
+        wum += wu * m_[0][1];
+        row[0] += wu * coef;
+      }
+    }
+#pragma unroll
+    for (int w = 1; w < NW; ++w) {
+#pragma unroll
+      for (int index = 2; index >= 0; --index) {
+        const double coef = wc[w][index];
+        if (coef == 0.0) continue;
+        const int idx = k - (index - 1);  // slot = 2 - index
+        if (idx < 0 || idx >= Tp) continue;
+        const double wu = coef * iv_[w][2 - index];
+        wum += wu * m_[w][2 - index];
+#pragma unroll
+        for (int inner = 2; inner >= index; --inner) {
+          const double c2 = wc[w][inner];
+          if (c2 == 0.0) continue;
+          const int j = inner - index;
+          if (k + j >= Tp) break;
+          row[j] += wu * c2;
+        }
+      }
+    }
+    double* o = sys + (int64_t)d * T;
+    o[(int64_t)(BW + 1) * plane] = wum;
+#pragma unroll
+    for (int j = 0; j < BW; ++j) o[(int64_t)(BW + 2 + j) * plane] = row[j];
+  }
+}
+
+__global__ void __launch_bounds__(128) k_ldl(BatchLayout b, StreamDev s, int64_t plane) {
+  constexpr int BW = 3, U = 4;
+  const int gid = blockIdx.x * blockDim.x + threadIdx.x;
+  const int u = gid / s.dim, d = gid - u * s.dim;
+  if (u >= b.n_utt) return;
+  const int64_t foff = b.frame_off[u];
+  const int T = (int)(b.frame_off[u + 1] - foff);
+  const int dim = s.dim;
+  const bool msd = s.is_msd != 0;
+  const int Tp = msd ? s.nvoiced[u] : T;
+  const bool gv = s.has_gv != 0;
+
+  double* const base = s.scratch + foff * dim + d;             // [frame][dim] planes
+  double* const pg = base + (int64_t)BW * plane;
+  double* const sys = s.scratch + foff * dim + (int64_t)d * T;  // system-major planes
+  const double* const swum = sys + (int64_t)(BW + 1) * plane;
+  const double* const sband = sys + (int64_t)(BW + 2) * plane;
+  double* const spar = sys + (int64_t)(2 * BW + 2) * plane;
+
+  // ---- LDL (mlpg.rs:79-92) + forward substitution (:98-104)
+  double prev[BW][BW], gprev[BW];
+#pragma unroll
+  for (int i = 0; i < BW; ++i) {
+    gprev[i] = 0.0;
+#pragma unroll
+    for (int j = 0; j < BW; ++j) prev[i][j] = 0.0;
+  }
+  for (int k0 = 0; k0 < Tp; k0 += U) {
+    double in[U][BW], inw[U];
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      const int k = k0 + q;
+      if (k < Tp) {
+        inw[q] = __ldg(swum + k);
+#pragma unroll
+        for (int j = 0; j < BW; ++j) in[q][j] = __ldg(sband + (int64_t)j * plane + k);
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      const int k = k0 + q;
+      if (k >= Tp) break;
+      double row[BW];
+#pragma unroll
+      for (int j = 0; j < BW; ++j) row[j] = in[q][j];
+#pragma unroll
+      for (int i = 1; i < BW; ++i)
+        if (i < k + 1) row[0] -= prev[i][i] * prev[i][i] * prev[i][0];
+#pragma unroll
+      for (int i = 1; i < BW; ++i) {
+#pragma unroll
+        for (int j = 1; j < BW; ++j)
+          if (j < BW - i && j < k + 1) row[i] -= prev[j][j] * prev[j][i + j] * prev[j][0];
+        row[i] /= row[0];
+      }
+      double g = inw[q];
+#pragma unroll
+      for (int i = 1; i < BW; ++i)
+        if (i < k + 1) g -= prev[i][i] * gprev[i];
+#pragma unroll
+      for (int j = 0; j < BW; ++j) base[(int64_t)j * plane + (int64_t)k * dim] = row[j];
+      pg[(int64_t)k * dim] = g;
+#pragma unroll
+      for (int i = BW - 1; i >= 2; --i) {
+        gprev[i] = gprev[i - 1];
+#pragma unroll
+        for (int j = 0; j < BW; ++j) prev[i][j] = prev[i - 1][j];
+      }
+      gprev[1] = g;
+#pragma unroll
+      for (int j = 0; j < BW; ++j) prev[1][j] = row[j];
+    }
+  }
+
+  // ---- backward substitution (mlpg.rs:106-113)
+  double* out = s.par + foff * dim + d;
+  const int32_t* const vidx = msd ? s.vidx + foff : nullptr;
+  if (!gv && msd)
+    for (int t = 0; t < T; ++t)
+      if (s.left[foff + t] < 0) out[(int64_t)t * dim] = kNoData;
+  double pn[BW];
+#pragma unroll
+  for (int i = 0; i < BW; ++i) pn[i] = 0.0;
+  for (int k0 = Tp - 1; k0 >= 0; k0 -= U) {
+    double fg[U], f[U][BW];
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      const int k = k0 - q;
+      if (k >= 0) {
+        fg[q] = pg[(int64_t)k * dim];
+#pragma unroll
+        for (int j = 0; j < BW; ++j) f[q][j] = base[(int64_t)j * plane + (int64_t)k * dim];
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      const int k = k0 - q;
+      if (k < 0) break;
+      double par = fg[q] / f[q][0];
+#pragma unroll
+      for (int i = 1; i < BW; ++i)
+        if (i < Tp - k) par -= f[q][i] * pn[i];
+      if (gv) spar[k] = par;
+      else out[(int64_t)(msd ? vidx[k] : k) * dim] = par;
+#pragma unroll
+      for (int i = BW - 1; i >= 2; --i) pn[i] = pn[i - 1];
+      pn[1] = par;
+    }
+  }
+}
+
+// Static window only (band width 1), no mask, no GV — the LPF stream: every frame is its own
+// 1 x 1 system, par = (c iv m) / (c iv c) with the operations of mlpg.rs:31-61,106-113.
+__global__ void __launch_bounds__(256) k_mlpg_static(BatchLayout b, StreamDev s, int64_t total) {
+  const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // frame * dim + d
+  if (e >= total) return;
+  const int dim = s.dim;
+  const int64_t gf = e / dim;
+  const int d = (int)(e - gf * dim);
+  int lo = 0, hi = b.n_utt;  // utterance of this frame
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (b.frame_off[mid] <= gf) lo = mid; else hi = mid;
+  }
+  const int64_t o = (b.state_off[lo] + b.frame_state[gf]) * (int64_t)(dim * s.nwin) + d;
+  const double coef = s.windows.coef[0][0];
+  double wum = 0.0, row = 0.0;
+  if (coef != 0.0) {
+    const double wu = coef * with_ivar(s.vari[o]);
+    wum += wu * s.mean[o];
+    row += wu * coef;
+  }
+  s.par[e] = wum / row;
+}
+
 // ---------------------------------------------------------------- GV adjustment, one CTA per system
 // MlpgGlobalVariance::{calc_gv, conv_gv, calc_hmmobj_derivative, next_step, parmgen}
 // (mlpg.rs:168-292) on the solution left in the `g` plane by k_mlpg_solve, using the un-factorised
@@ -561,7 +798,8 @@ __device__ __forceinline__ double block_sum(double v, double* red) {
 }
 
 template <int BW>
-__global__ void __launch_bounds__(256) k_mlpg_gv(BatchLayout b, StreamDev s, int64_t plane, int smem_frames) {
+__global__ void __launch_bounds__(256) k_mlpg_gv(BatchLayout b, StreamDev s, int64_t plane, int smem_frames,
+                                                 int sysmajor) {
   extern __shared__ double sm[];
   __shared__ double red[8];
   const int sys = blockIdx.x;
@@ -579,9 +817,11 @@ __global__ void __launch_bounds__(256) k_mlpg_gv(BatchLayout b, StreamDev s, int
       if (s.left[foff + t] < 0) out[(int64_t)t * dim] = kNoData;  // Mask::fill (mask.rs:34-49)
   if (Tp == 0) return;
 
-  double* const gbase = s.scratch + foff * dim + d;
-  double* const g_par = gbase + (int64_t)(BW + 1) * plane;
-  double* const g_wum = gbase + (int64_t)BW * plane;
+  // sysmajor (split path): the planes of this system are contiguous, see the plane map above
+  double* const gbase = sysmajor ? s.scratch + foff * dim + (int64_t)d * T : s.scratch + foff * dim + d;
+  const int64_t gst = sysmajor ? 1 : dim;
+  double* const g_par = gbase + (int64_t)(sysmajor ? 2 * BW + 2 : BW + 1) * plane;
+  double* const g_wum = gbase + (int64_t)(sysmajor ? BW + 1 : BW) * plane;
   const bool in_smem = Tp <= smem_frames;
   double *PAR, *WUM, *GRAD, *O[BW];
   int64_t st;  // element stride
@@ -595,10 +835,10 @@ __global__ void __launch_bounds__(256) k_mlpg_gv(BatchLayout b, StreamDev s, int
     SW = reinterpret_cast<uint8_t*>(sm + (int64_t)(3 + BW) * Tp);
     st = 1;
     for (int k = tid; k < Tp; k += nt) {
-      PAR[k] = g_par[(int64_t)k * dim];
-      WUM[k] = g_wum[(int64_t)k * dim];
+      PAR[k] = g_par[(int64_t)k * gst];
+      WUM[k] = g_wum[(int64_t)k * gst];
 #pragma unroll
-      for (int j = 0; j < BW; ++j) O[j][k] = gbase[(int64_t)(BW + 2 + j) * plane + (int64_t)k * dim];
+      for (int j = 0; j < BW; ++j) O[j][k] = gbase[(int64_t)(BW + 2 + j) * plane + (int64_t)k * gst];
       SW[k] = s.gv_switch[soff + fstate[msd ? vidx[k] : k]];
     }
     __syncthreads();
@@ -607,8 +847,8 @@ __global__ void __launch_bounds__(256) k_mlpg_gv(BatchLayout b, StreamDev s, int
     WUM = g_wum;
 #pragma unroll
     for (int j = 0; j < BW; ++j) O[j] = gbase + (int64_t)(BW + 2 + j) * plane;
-    GRAD = gbase + (int64_t)(2 * BW + 2) * plane;
-    st = dim;
+    GRAD = gbase + (int64_t)(sysmajor ? 2 * BW + 3 : 2 * BW + 2) * plane;
+    st = gst;
   }
   auto sw = [&](int k) -> bool { return in_smem ? SW[k] != 0 : s.gv_switch[soff + fstate[msd ? vidx[k] : k]] != 0; };
 
@@ -730,7 +970,8 @@ int launch_expand(const BatchLayout& b, const StreamSet& set, cudaStream_t strea
   return (int)cudaGetLastError();
 }
 
-int launch_mlpg(const BatchLayout& b, const StreamDev& s, int64_t total_frames, cudaStream_t stream) {
+int launch_mlpg(const BatchLayout& b, const StreamDev& s, int64_t total_frames, int64_t total_states,
+                cudaStream_t stream) {
   if (b.n_utt == 0 || s.dim == 0) return 0;
   const int64_t plane = total_frames * s.dim;
   const int64_t nthreads = (int64_t)b.n_utt * s.dim;
@@ -739,9 +980,23 @@ int launch_mlpg(const BatchLayout& b, const StreamDev& s, int64_t total_frames, 
   const WindowSet& w = s.windows;
   const bool shape1 = w.nwin == 1 && w.width[0] == 1;
   const bool shape133 = w.nwin == 3 && w.width[0] == 1 && w.width[1] == 3 && w.width[2] == 3;
+  if (shape1 && !s.is_msd && !s.has_gv) {  // every frame is its own system
+    const int64_t total = total_frames * s.dim;
+    if (total == 0) return 0;
+    k_mlpg_static<<<(unsigned)((total + 255) / 256), 256, 0, stream>>>(b, s, total);
+    return (int)cudaGetLastError();
+  }
   if (shape1 || shape133) {
-    if (shape1) k_mlpg_solve<kShape1><<<blocks, threads, 0, stream>>>(b, s, plane);
-    else k_mlpg_solve<kShape133><<<blocks, threads, 0, stream>>>(b, s, plane);
+    if (shape1) {
+      k_mlpg_solve<kShape1><<<blocks, threads, 0, stream>>>(b, s, plane);
+    } else {
+      if (s.ivar == nullptr) return (int)cudaErrorInvalidValue;
+      const int64_t nv = total_states * s.dim * s.nwin;
+      if (nv > 0) k_state_ivar<<<(unsigned)((nv + 255) / 256), 256, 0, stream>>>(s.vari, s.ivar, nv);
+      if (b.max_frames > 0)
+        k_band_build<<<dim3((unsigned)((b.max_frames + 127) / 128), (unsigned)b.n_utt), 128, 0, stream>>>(b, s, plane);
+      k_ldl<<<blocks, threads, 0, stream>>>(b, s, plane);
+    }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess || !s.has_gv) return (int)e;
     // GV: one CTA per system, the system in shared memory when it fits
@@ -754,8 +1009,8 @@ int launch_mlpg(const BatchLayout& b, const StreamDev& s, int64_t total_frames, 
     // per device and cheap, so set on every launch
     cudaFuncSetAttribute(k_mlpg_gv<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap);
     cudaFuncSetAttribute(k_mlpg_gv<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap);
-    if (bw == 1) k_mlpg_gv<1><<<(unsigned)nthreads, 256, smem, stream>>>(b, s, plane, smem_frames);
-    else k_mlpg_gv<3><<<(unsigned)nthreads, 256, smem, stream>>>(b, s, plane, smem_frames);
+    if (bw == 1) k_mlpg_gv<1><<<(unsigned)nthreads, 256, smem, stream>>>(b, s, plane, smem_frames, 0);
+    else k_mlpg_gv<3><<<(unsigned)nthreads, 256, smem, stream>>>(b, s, plane, smem_frames, 1);
     return (int)cudaGetLastError();
   }
   switch (s.windows.band_width()) {  // other window shapes: the general kernel

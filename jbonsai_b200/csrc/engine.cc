@@ -383,6 +383,9 @@ struct Engine::Resident {
     int n = 1 + 3 + 2 + 3 + (segs.n_seg > 0 ? (int)wave_seg_first.size() - 1 : 0) + (beta > 0.0 ? 2 : 0);
     for (int i = 0; i < 3; ++i) n += gathered[i] ? 1 : 0;
     for (int i = 0; i < streams.n; ++i) n += streams.s[i].has_gv ? 1 : 0;
+    // the 1-3-3 window shape runs as k_state_ivar + k_band_build + k_ldl instead of one solve kernel
+    for (int i = 0; i < streams.n; ++i)
+      n += (streams.s[i].nwin == 3 && streams.s[i].windows.width[1] == 3 && streams.s[i].windows.width[2] == 3) ? 2 : 0;
     return n;
   }
 };
@@ -625,6 +628,8 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
     sb = std::max(sb, (size_t)jbk::mlpg_scratch_planes(ws.band_width(), has_gv[s]) *
                                                 (size_t)TF * dim[s] * 8);
   }
+  size_t w_ivar[3] = {0};  // MeanVari::with_ivar per state, written by the MLPG split path
+  for (size_t s = 0; s < nstream; ++s) w_ivar[s] = wk.take((size_t)TS * dim[s] * nwin[s] * 8);
   size_t w_gmean[3] = {0}, w_gvari[3] = {0}, w_gmsd[3] = {0};
   for (size_t s = 0; s < nstream; ++s)
     if (gath[s]) {
@@ -668,6 +673,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
     sd.gv_weight = cond.gv_weight[s];
     sd.mean = gath[s] ? (const double*)(dw + w_gmean[s]) : (const double*)(di + o_mean[s]);
     sd.vari = gath[s] ? (const double*)(dw + w_gvari[s]) : (const double*)(di + o_vari[s]);
+    sd.ivar = (double*)(dw + w_ivar[s]);
     sd.msd = !is_msd[s] ? nullptr : gath[s] ? (const double*)(dw + w_gmsd[s]) : (const double*)(di + o_msd[s]);
     r->gathered[s] = gath[s];
     if (gath[s]) {
@@ -750,12 +756,12 @@ static void launch_mlpg_all(Engine::Resident* r, bool with_pulse) {
   JB_LAUNCH(jbk::launch_expand(r->layout, r->streams, st));
   JB_CUDA(cudaEventRecord(c->evx[0], st));
   JB_CUDA(cudaStreamWaitEvent(sb, c->evx[0], 0));
-  JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[1], r->total_frames, sb));
+  JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[1], r->total_frames, r->total_states, sb));
   JB_LAUNCH(jbk::launch_frame_prep(r->layout, r->vp, r->vd, r->total_frames, 1, sb));
   if (with_pulse) JB_LAUNCH(jbk::launch_pulse(r->layout, r->vp, r->vd, r->total_samples, sb));
   JB_CUDA(cudaEventRecord(c->evx[1], sb));
-  JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[0], r->total_frames, st));
-  JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[2], r->total_frames, st));
+  JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[0], r->total_frames, r->total_states, st));
+  JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[2], r->total_frames, r->total_states, st));
   JB_LAUNCH(jbk::launch_frame_prep(r->layout, r->vp, r->vd, r->total_frames, 2, st));
   if (r->beta > 0.0)  // MelCepstrum::postfilter_mcp (cepstrum.rs:23-37): rewrites vd.b in place
     JB_LAUNCH(jbk::launch_postfilter(r->layout, r->vp, r->vd, r->beta, const_cast<double*>(r->vd.b_first),
