@@ -131,6 +131,7 @@ struct VocoderDev {
                           // row 0 of `b` (identical when beta == 0)
   double* pitch;        // [total_frames]        p per frame (out of frame_prep)
   double* pulse;        // [total_samples]       pulse amplitude or 0 (out of pitch kernel)
+  int32_t* runs;        // [1 + total_frames]    work: number of voiced runs, then their first frames
   double* wave;         // [total_samples]       excitation*gain; variants 0-2 filter it in place
   double* out;          // [total_samples]       variant 3 only: filtered waveform (wave stays the input)
   double* state;        // [n_utt][kVocStateDoubles] or nullptr (whole-utterance synthesis)

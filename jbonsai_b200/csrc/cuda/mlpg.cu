@@ -644,7 +644,7 @@ __global__ void __launch_bounds__(128) k_band_build(BatchLayout b, StreamDev s, 
 }
 
 __global__ void __launch_bounds__(128) k_ldl(BatchLayout b, StreamDev s, int64_t plane) {
-  constexpr int BW = 3, U = 4;
+  constexpr int BW = 3, U = 8;
   const int gid = blockIdx.x * blockDim.x + threadIdx.x;
   const int u = gid / s.dim, d = gid - u * s.dim;
   if (u >= b.n_utt) return;
@@ -670,17 +670,31 @@ __global__ void __launch_bounds__(128) k_ldl(BatchLayout b, StreamDev s, int64_t
 #pragma unroll
     for (int j = 0; j < BW; ++j) prev[i][j] = 0.0;
   }
-  for (int k0 = 0; k0 < Tp; k0 += U) {
-    double in[U][BW], inw[U];
+  // the loads of batch k0 + U are in flight while batch k0 is factorised
+  double in[U][BW], inw[U], nin[U][BW], ninw[U];
+  auto load_fwd = [&](int k0, double (&a)[U][BW], double (&w)[U]) {
 #pragma unroll
     for (int q = 0; q < U; ++q) {
       const int k = k0 + q;
-      if (k < Tp) {
-        inw[q] = __ldg(swum + k);
+      w[q] = 0.0;
 #pragma unroll
-        for (int j = 0; j < BW; ++j) in[q][j] = __ldg(sband + (int64_t)j * plane + k);
+      for (int j = 0; j < BW; ++j) a[q][j] = 0.0;
+      if (k < Tp) {
+        w[q] = __ldg(swum + k);
+#pragma unroll
+        for (int j = 0; j < BW; ++j) a[q][j] = __ldg(sband + (int64_t)j * plane + k);
       }
     }
+  };
+  load_fwd(0, nin, ninw);
+  for (int k0 = 0; k0 < Tp; k0 += U) {
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      inw[q] = ninw[q];
+#pragma unroll
+      for (int j = 0; j < BW; ++j) in[q][j] = nin[q][j];
+    }
+    load_fwd(k0 + U, nin, ninw);
 #pragma unroll
     for (int q = 0; q < U; ++q) {
       const int k = k0 + q;
@@ -726,17 +740,30 @@ __global__ void __launch_bounds__(128) k_ldl(BatchLayout b, StreamDev s, int64_t
   double pn[BW];
 #pragma unroll
   for (int i = 0; i < BW; ++i) pn[i] = 0.0;
-  for (int k0 = Tp - 1; k0 >= 0; k0 -= U) {
-    double fg[U], f[U][BW];
+  double fg[U], f[U][BW], nfg[U], nf[U][BW];
+  auto load_bwd = [&](int k0, double (&a)[U][BW], double (&w)[U]) {
 #pragma unroll
     for (int q = 0; q < U; ++q) {
       const int k = k0 - q;
-      if (k >= 0) {
-        fg[q] = pg[(int64_t)k * dim];
+      w[q] = 0.0;
 #pragma unroll
-        for (int j = 0; j < BW; ++j) f[q][j] = base[(int64_t)j * plane + (int64_t)k * dim];
+      for (int j = 0; j < BW; ++j) a[q][j] = 1.0;
+      if (k >= 0) {
+        w[q] = pg[(int64_t)k * dim];
+#pragma unroll
+        for (int j = 0; j < BW; ++j) a[q][j] = base[(int64_t)j * plane + (int64_t)k * dim];
       }
     }
+  };
+  load_bwd(Tp - 1, nf, nfg);
+  for (int k0 = Tp - 1; k0 >= 0; k0 -= U) {
+#pragma unroll
+    for (int q = 0; q < U; ++q) {
+      fg[q] = nfg[q];
+#pragma unroll
+      for (int j = 0; j < BW; ++j) f[q][j] = nf[q][j];
+    }
+    load_bwd(k0 - U, nf, nfg);
 #pragma unroll
     for (int q = 0; q < U; ++q) {
       const int k = k0 - q;
@@ -797,9 +824,8 @@ __device__ __forceinline__ double block_sum(double v, double* red) {
   return t;
 }
 
-template <int BW>
-__global__ void __launch_bounds__(256) k_mlpg_gv(BatchLayout b, StreamDev s, int64_t plane, int smem_frames,
-                                                 int sysmajor) {
+template <int BW, bool sysmajor>
+__global__ void __launch_bounds__(256, 3) k_mlpg_gv(BatchLayout b, StreamDev s, int64_t plane, int smem_frames) {
   extern __shared__ double sm[];
   __shared__ double red[8];
   const int sys = blockIdx.x;
@@ -819,12 +845,12 @@ __global__ void __launch_bounds__(256) k_mlpg_gv(BatchLayout b, StreamDev s, int
 
   // sysmajor (split path): the planes of this system are contiguous, see the plane map above
   double* const gbase = sysmajor ? s.scratch + foff * dim + (int64_t)d * T : s.scratch + foff * dim + d;
-  const int64_t gst = sysmajor ? 1 : dim;
+  const int gst = sysmajor ? 1 : dim;
   double* const g_par = gbase + (int64_t)(sysmajor ? 2 * BW + 2 : BW + 1) * plane;
   double* const g_wum = gbase + (int64_t)(sysmajor ? BW + 1 : BW) * plane;
   const bool in_smem = Tp <= smem_frames;
   double *PAR, *WUM, *GRAD, *O[BW];
-  int64_t st;  // element stride
+  const int st = (sysmajor || in_smem) ? 1 : dim;  // element stride (compile-time 1 on the split path)
   uint8_t* SW = nullptr;
   if (in_smem) {
     PAR = sm;
@@ -833,7 +859,6 @@ __global__ void __launch_bounds__(256) k_mlpg_gv(BatchLayout b, StreamDev s, int
     WUM = sm + (int64_t)(1 + BW) * Tp;
     GRAD = sm + (int64_t)(2 + BW) * Tp;
     SW = reinterpret_cast<uint8_t*>(sm + (int64_t)(3 + BW) * Tp);
-    st = 1;
     for (int k = tid; k < Tp; k += nt) {
       PAR[k] = g_par[(int64_t)k * gst];
       WUM[k] = g_wum[(int64_t)k * gst];
@@ -848,7 +873,6 @@ __global__ void __launch_bounds__(256) k_mlpg_gv(BatchLayout b, StreamDev s, int
 #pragma unroll
     for (int j = 0; j < BW; ++j) O[j] = gbase + (int64_t)(BW + 2 + j) * plane;
     GRAD = gbase + (int64_t)(sysmajor ? 2 * BW + 3 : 2 * BW + 2) * plane;
-    st = gst;
   }
   auto sw = [&](int k) -> bool { return in_smem ? SW[k] != 0 : s.gv_switch[soff + fstate[msd ? vidx[k] : k]] != 0; };
 
@@ -1007,10 +1031,10 @@ int launch_mlpg(const BatchLayout& b, const StreamDev& s, int64_t total_frames, 
     if (smem_frames > b.max_frames) smem_frames = b.max_frames;
     const size_t smem = (size_t)smem_frames * per_frame + 16;
     // per device and cheap, so set on every launch
-    cudaFuncSetAttribute(k_mlpg_gv<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap);
-    cudaFuncSetAttribute(k_mlpg_gv<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap);
-    if (bw == 1) k_mlpg_gv<1><<<(unsigned)nthreads, 256, smem, stream>>>(b, s, plane, smem_frames, 0);
-    else k_mlpg_gv<3><<<(unsigned)nthreads, 256, smem, stream>>>(b, s, plane, smem_frames, 1);
+    cudaFuncSetAttribute(k_mlpg_gv<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap);
+    cudaFuncSetAttribute(k_mlpg_gv<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap);
+    if (bw == 1) k_mlpg_gv<1, false><<<(unsigned)nthreads, 256, smem, stream>>>(b, s, plane, smem_frames);
+    else k_mlpg_gv<3, true><<<(unsigned)nthreads, 256, smem, stream>>>(b, s, plane, smem_frames);
     return (int)cudaGetLastError();
   }
   switch (s.windows.band_width()) {  // other window shapes: the general kernel

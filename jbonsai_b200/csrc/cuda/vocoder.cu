@@ -113,19 +113,35 @@ __global__ void __launch_bounds__(32) k_pulse(BatchLayout b, VocoderParams p, Vo
 
 // Whole-utterance synthesis: the pitch counter restarts at every unvoiced -> voiced transition
 // (Excitation::start resets pitch_of_curr_point and pitch_counter when the previous frame was
-// unvoiced, excitation.rs:25-33), so each maximal run of voiced frames is an independent walk:
-// one thread per frame, the threads that sit on the first frame of a run walk it.
-__global__ void __launch_bounds__(128) k_pulse_runs(BatchLayout b, VocoderParams p, VocoderDev d,
-                                                    int64_t total_frames) {
+// unvoiced, excitation.rs:25-33), so each maximal run of voiced frames is an independent walk.
+// k_pulse_list collects the first frame of every run (d.runs[0] = count, d.runs[1..] = frames, in
+// no particular order); k_pulse_runs walks one run per thread, so that the 32 lanes of a warp all
+// carry a walk (with one thread per frame a warp held one walking lane and 31 idle ones, and the
+// kernel was bound by the issue slots of ~6000 such warps).
+__global__ void __launch_bounds__(256) k_pulse_list(BatchLayout b, VocoderDev d, int64_t total_frames) {
   const int64_t gf = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gf >= total_frames) return;
+  if (d.pitch[gf] == 0.0) return;
+  if (gf > 0 && d.pitch[gf - 1] != 0.0 && b.frame_off[find_utt(b.frame_off, b.n_utt, gf)] != gf) return;
+  const int slot = atomicAdd(d.runs, 1);
+  d.runs[1 + slot] = (int32_t)gf;
+}
+
+constexpr int kRunLanes = 4;
+__global__ void __launch_bounds__(128) k_pulse_runs(BatchLayout b, VocoderParams p, VocoderDev d,
+                                                    int64_t total_frames) {
+  // kRunLanes walks per warp: a walk leaves the 8-sample fast path about once in 30 blocks, and a
+  // warp pays for the slow path whenever any of its lanes does, so fewer walks per warp (and more
+  // warps) finish sooner than 32 walks in lockstep.
+  if (threadIdx.x % (32 / kRunLanes) != 0) return;
+  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / (32 / kRunLanes);
+  if (i >= d.runs[0]) return;
+  const int64_t gf = d.runs[1 + i];
   const double first = d.pitch[gf];
-  if (first == 0.0) return;
   const int u = find_utt(b.frame_off, b.n_utt, gf);
   const int64_t foff = b.frame_off[u];
   const int T = (int)(b.frame_off[u + 1] - foff);
   const int f = (int)(gf - foff);
-  if (f > 0 && d.pitch[gf - 1] != 0.0) return;  // not the start of a run
   const int fp = p.fperiod;
   const double fper = (double)fp;
   double p_cur = first, cnt = first, inc = 0.0, pitch = first;
@@ -782,7 +798,13 @@ int launch_pulse(const BatchLayout& b, const VocoderParams& p, const VocoderDev&
   if (whole && !d.state) {
     const int64_t total_frames = total_samples / p.fperiod;
     if (total_frames == 0) return 0;
-    k_pulse_runs<<<(unsigned)((total_frames + 127) / 128), 128, 0, stream>>>(b, p, d, total_frames);
+    if (d.runs == nullptr) return (int)cudaErrorInvalidValue;
+    cudaError_t e = cudaMemsetAsync(d.runs, 0, sizeof(int32_t), stream);
+    if (e != cudaSuccess) return (int)e;
+    k_pulse_list<<<(unsigned)((total_frames + 255) / 256), 256, 0, stream>>>(b, d, total_frames);
+    // at most every other frame starts a run
+    const int64_t max_threads = (total_frames / 2 + b.n_utt + 1) * (32 / kRunLanes);
+    k_pulse_runs<<<(unsigned)((max_threads + 127) / 128), 128, 0, stream>>>(b, p, d, total_frames);
     return (int)cudaGetLastError();
   }
   k_pulse<<<(b.n_utt + threads - 1) / threads, threads, 0, stream>>>(b, p, d, whole ? 0 : 1);

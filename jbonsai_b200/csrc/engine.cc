@@ -183,7 +183,14 @@ class DeviceCtx {
     if (dev < 0 || dev >= n) throw Error(kErrCuda, "CUDA device index out of range");
     JB_CUDA(cudaSetDevice(dev));
     JB_CUDA(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
-    JB_CUDA(cudaStreamCreateWithFlags(&stream2, cudaStreamNonBlocking));
+    {
+      // The LF0 -> pitch -> pulse chain is a string of small latency-bound kernels; at a higher
+      // priority its blocks slip in between those of the chip-filling MCP kernels instead of
+      // queueing behind them.
+      int least = 0, greatest = 0;
+      JB_CUDA(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+      JB_CUDA(cudaStreamCreateWithPriority(&stream2, cudaStreamNonBlocking, greatest));
+    }
     JB_CUDA(cudaStreamCreateWithFlags(&stream_copy, cudaStreamNonBlocking));
     for (auto& x : evx) JB_CUDA(cudaEventCreateWithFlags(&x, cudaEventDisableTiming));
     for (auto& x : evw) JB_CUDA(cudaEventCreateWithFlags(&x, cudaEventDisableTiming));
@@ -380,7 +387,7 @@ struct Engine::Resident {
   // kernels per pass: expand, 3 solves (+ GV kernels), 2 frame preps, pulse (memset excluded),
   // excitation, MLSA (+ cut check for variant 3)
   int launches() const {
-    int n = 1 + 3 + 2 + 3 + (segs.n_seg > 0 ? (int)wave_seg_first.size() - 1 : 0) + (beta > 0.0 ? 2 : 0);
+    int n = 1 + 3 + 2 + 4 + (segs.n_seg > 0 ? (int)wave_seg_first.size() - 1 : 0) + (beta > 0.0 ? 2 : 0);
     for (int i = 0; i < 3; ++i) n += gathered[i] ? 1 : 0;
     for (int i = 0; i < streams.n; ++i) n += streams.s[i].has_gv ? 1 : 0;
     // the 1-3-3 window shape runs as k_state_ivar + k_band_build + k_ldl instead of one solve kernel
@@ -643,6 +650,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   const size_t w_b = wk.take((size_t)TF * dim[0] * 8);
   const size_t w_pitch = wk.take((size_t)TF * 8);
   const size_t w_pulse = wk.take((size_t)r->total_samples * 8);
+  const size_t w_runs = wk.take(((size_t)TF + 1) * 4);
   const size_t w_wave = wk.take((size_t)r->total_samples * 8);
   const size_t w_state = streaming ? wk.take(n_utt * jbk::kVocStateDoubles * 8) : 0;
   const size_t w_out = segs.empty() ? 0 : wk.take((size_t)r->total_samples * 8);
@@ -718,6 +726,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   r->beta = postfilter ? cond.beta : 0.0;
   r->vd.pitch = (double*)(dw + w_pitch);
   r->vd.pulse = (double*)(dw + w_pulse);
+  r->vd.runs = (int32_t*)(dw + w_runs);
   r->vd.wave = (double*)(dw + w_wave);
   r->vd.state = streaming ? (double*)(dw + w_state) : nullptr;
   r->vd.out = segs.empty() ? nullptr : (double*)(dw + w_out);
