@@ -187,7 +187,7 @@ class Engine:
     def set_device_gather(self, enabled: bool) -> None:
         _check(lib.jb_engine_set_device_gather(self._h, int(bool(enabled))))
 
-    def set_mlsa_segmenting(self, warm_frames: int = 40, cut_tolerance: float = 1e-8) -> None:
+    def set_mlsa_segmenting(self, warm_frames: int = 40, cut_tolerance: float = 1e-7) -> None:
         _check(lib.jb_engine_set_mlsa_segmenting(self._h, int(warm_frames), C.c_double(cut_tolerance)))
 
     def set_output_mode(self, mode: int) -> None:

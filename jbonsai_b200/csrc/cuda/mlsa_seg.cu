@@ -13,7 +13,8 @@
 // utterance is cut into segments; every segment but the first runs `warm` extra frames in front of
 // its own range with its output discarded. Nothing is assumed: every segment stores its state at
 // the start of its own range and at its end, k_mlsa_seg_check compares the two sides of every cut,
-// and the host re-runs the sequential kernel (variant 2) when a cut disagrees by more than 1e-8.
+// and the host re-runs the sequential kernel (variant 2) when a cut disagrees by more than 1e-7
+// (Engine::mlsa_cut_tolerance; the rounding-noise floor of that comparison is ~3e-8).
 //
 // Layout. lane = 5 g + s: segment slot g = 0..5 of this warp, Pade stage s + 1 (s = 0..4); lanes
 // 30/31 shadow slot 5 and write to dump slots. A lane owns the whole 34-tap warped delay line of

@@ -282,12 +282,23 @@ def test_segmented_filter_cuts_are_checked(genji_labels, orc):
     w, off = e.synthesize_batch([labels, SAMPLE_SENTENCE_1], timings=tm)
     ow, _ = orc.synthesize_batch([labels, SAMPLE_SENTENCE_1], fma=True, nthreads=2)
     assert tm["mlsa_segments"] > 20 and tm["mlsa_seg_frames"] > tm["frames"]
-    assert tm["mlsa_fallback"] == 0 and 0.0 < tm["mlsa_cut_worst"] <= 1e-8
+    assert tm["mlsa_fallback"] == 0 and 0.0 < tm["mlsa_cut_worst"] <= 1e-7
     assert np.abs(w - ow).max() <= WAVE_ATOL
     e2 = jb.Engine.load([NITECH])
     e2.set_mlsa_variant(2)
     w2, _ = e2.synthesize_batch([labels, SAMPLE_SENTENCE_1])
     assert np.abs(w - w2).max() <= SCHED_ATOL
+
+
+def test_segmented_filter_tohoku_stays_segmented(genji_labels):
+    # the state comparison has a rounding-noise floor (~3e-8 on this voice): the default tolerance
+    # must sit above it, or every batch silently pays for the sequential kernel
+    labels = genji_labels[:150]
+    e, o = jb.Engine.load([TOHOKU_NEUTRAL]), Oracle([TOHOKU_NEUTRAL])
+    tm = {}
+    w, _ = e.synthesize_batch([labels], timings=tm)
+    assert tm["mlsa_segments"] > 20 and tm["mlsa_fallback"] == 0 and tm["mlsa_cut_worst"] <= 1e-7
+    assert np.abs(w - o.synthesize(labels, fma=True)).max() <= WAVE_ATOL
 
 
 def test_segmented_filter_short_warmup_falls_back(genji_labels, orc):
