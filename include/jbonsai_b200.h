@@ -99,6 +99,13 @@ int jb_engine_synthesize(const jb_engine* e, const char* const* lines, size_t n_
  * warm-up [16] largest state mismatch at a cut [17] 1 if the sequential kernel redid the batch. */
 int jb_engine_synthesize_batch(const jb_engine* e, const char* const* lines, const size_t* line_off,
                                size_t n_utt, double** out, size_t* out_off, double* timings);
+/* The same synthesis delivered as 16-bit PCM: every f64 sample x becomes
+ * (int16_t) min(max(x, -32768), 32767), truncated toward zero — what the reference's examples do with
+ * the Vec<f64> before writing a WAV file (examples/genji/main.rs:34-35, examples/is-bonsai/main.rs:47-48).
+ * The conversion runs on the device, so 2 instead of 8 bytes per sample cross PCIe. Release *out
+ * with jb_free(). */
+int jb_engine_synthesize_batch_pcm16(const jb_engine* e, const char* const* lines, const size_t* line_off,
+                                     size_t n_utt, int16_t** out, size_t* out_off, double* timings);
 void jb_free(void* p);
 
 /* Parity taps (tests): MlpgAdjust::create output of every utterance (src/mlpg_adjust/mod.rs:51)

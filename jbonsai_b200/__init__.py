@@ -24,7 +24,7 @@ C_ABI_SYMBOLS = [
     "jb_engine_load_from_bytes", "jb_engine_free", "jb_engine_set_condition",
     "jb_engine_get_condition", "jb_engine_set_interpolation_weight", "jb_engine_set_devices",
     "jb_engine_set_mlsa_variant", "jb_engine_set_mlsa_segmenting", "jb_engine_set_device_gather",
-    "jb_engine_set_output_mode", "jb_engine_synthesize", "jb_engine_synthesize_batch", "jb_free",
+    "jb_engine_set_output_mode", "jb_engine_synthesize", "jb_engine_synthesize_batch", "jb_engine_synthesize_batch_pcm16", "jb_free",
     "jb_engine_debug_batch", "jb_engine_noise", "jb_engine_durations", "jb_engine_tree_index",
     "jb_engine_stream_parameters", "jb_engine_duration_parameters", "jb_engine_gv_parameters",
     "jb_resident_prepare", "jb_resident_run", "jb_resident_fetch", "jb_resident_free",
@@ -215,15 +215,30 @@ class Engine:
             timings.update({k: tm[i] for i, k in enumerate(TIMING_KEYS)})
         return _take(out, int(off[-1])), off
 
-    def synthesize_batch_raw(self, flat):
+    def synthesize_batch_pcm16(self, utts: Sequence[Sequence[str]], timings: Optional[dict] = None):
+        """16-bit PCM (clamp, truncate toward zero: examples/genji/main.rs:34-35) -> (int16 samples, out_off)."""
+        arr, offs, n = _flatten(utts)
+        out = C.POINTER(C.c_int16)()
+        out_off = (C.c_size_t * (n + 1))()
+        tm = (C.c_double * 20)()
+        _check(lib.jb_engine_synthesize_batch_pcm16(self._h, arr, offs, C.c_size_t(n), C.byref(out), out_off, tm))
+        off = np.array(list(out_off), dtype=np.int64)
+        if timings is not None:
+            timings.update({k: tm[i] for i, k in enumerate(TIMING_KEYS)})
+        total = int(off[-1])
+        res = np.ctypeslib.as_array(out, shape=(total,)).copy() if total else np.zeros(0, dtype=np.int16)
+        lib.jb_free(out)
+        return res, off
+
+    def synthesize_batch_raw(self, flat, pcm16: bool = False):
         """Timed e2e call for bench.py: pre-flattened (arr, offs, n); returns the library-owned
         pinned host buffer (release with lib.jb_free) without copying it again."""
         arr, offs, n = flat
-        out = C.POINTER(C.c_double)()
+        out = C.POINTER(C.c_int16)() if pcm16 else C.POINTER(C.c_double)()
         out_off = (C.c_size_t * (n + 1))()
         tm = (C.c_double * 20)()
-        _check(lib.jb_engine_synthesize_batch(self._h, arr, offs, C.c_size_t(n), C.byref(out),
-                                              out_off, tm))
+        fn = lib.jb_engine_synthesize_batch_pcm16 if pcm16 else lib.jb_engine_synthesize_batch
+        _check(fn(self._h, arr, offs, C.c_size_t(n), C.byref(out), out_off, tm))
         return out, out_off, {k: tm[i] for i, k in enumerate(TIMING_KEYS)}
 
     # -- parity taps

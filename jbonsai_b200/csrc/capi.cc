@@ -172,6 +172,17 @@ int jb_engine_synthesize_batch(const jb_engine* e, const char* const* lines, con
   JB_CATCH
 }
 
+int jb_engine_synthesize_batch_pcm16(const jb_engine* e, const char* const* lines, const size_t* line_off,
+                                     size_t n_utt, int16_t** out, size_t* out_off, double* timings) {
+  JB_TRY
+  std::vector<size_t> off;
+  jb::BatchTimings tm;
+  e->e->synthesize_batch_pcm16(to_utts(lines, line_off, n_utt), out, &off, &tm);
+  memcpy(out_off, off.data(), off.size() * sizeof(size_t));
+  fill_timings(tm, timings);
+  JB_CATCH
+}
+
 int jb_engine_synthesize(const jb_engine* e, const char* const* lines, size_t n_lines, double** out,
                          size_t* out_len) {
   size_t line_off[2] = {0, n_lines}, out_off[2] = {0, 0};
@@ -185,7 +196,7 @@ void jb_free(void* p) {
   if (!p) return;
   cudaPointerAttributes attr;
   if (cudaPointerGetAttributes(&attr, p) == cudaSuccess && attr.type == cudaMemoryTypeHost) {
-    jb::Engine::free_output((double*)p);
+    jb::Engine::free_output(p);
     return;
   }
   cudaGetLastError();

@@ -182,6 +182,10 @@ int launch_mlsa_seg_check(const MlsaSegments& sg, double* worst, cudaStream_t st
 int launch_gather_chunk(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,
                         double* chunk, cudaStream_t stream);
 
+// f64 samples -> 16-bit PCM with the reference examples' convention (clamp to the i16 range, then
+// truncate toward zero; examples/genji/main.rs:34-35). n must be a multiple of 4.
+int launch_pcm16(const double* in, int16_t* out, int64_t n, cudaStream_t stream);
+
 // Roofline denominators measured on the current device (peaks.cu); not on the synthesis path.
 int measure_peaks(double* fp64_fma_tflops, double* hbm_copy_gbs);
 

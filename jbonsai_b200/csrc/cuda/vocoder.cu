@@ -767,6 +767,30 @@ __global__ void k_gather_chunk(BatchLayout b, VocoderParams p, VocoderDev d, dou
 
 }  // namespace
 
+namespace {
+// 16-bit PCM the way the reference's examples write WAV files (examples/genji/main.rs:34-35):
+// value.min(i16::MAX).max(i16::MIN) as i16, i.e. clamp, then truncate toward zero. Four samples per
+// thread (n and both pointers are multiples of 4 samples: offsets are whole frames).
+__global__ void __launch_bounds__(256) k_pcm16(const double* __restrict__ in, int16_t* __restrict__ out, int64_t n4) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n4) return;
+  const double2 a = reinterpret_cast<const double2*>(in)[2 * i];
+  const double2 c = reinterpret_cast<const double2*>(in)[2 * i + 1];
+  auto q = [](double v) -> short { return (short)(int)fmax(fmin(v, 32767.0), -32768.0); };
+  short4 o;
+  o.x = q(a.x); o.y = q(a.y); o.z = q(c.x); o.w = q(c.y);
+  reinterpret_cast<short4*>(out)[i] = o;
+}
+}  // namespace
+
+int launch_pcm16(const double* in, int16_t* out, int64_t n, cudaStream_t stream) {
+  if (n <= 0) return 0;
+  if (n % 4 != 0 || ((uintptr_t)in & 15) || ((uintptr_t)out & 7)) return (int)cudaErrorInvalidValue;
+  const int64_t n4 = n / 4;
+  k_pcm16<<<(unsigned)((n4 + 255) / 256), 256, 0, stream>>>(in, out, n4);
+  return (int)cudaGetLastError();
+}
+
 int launch_gather_chunk(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,
                         double* chunk, cudaStream_t stream) {
   if (b.n_utt == 0 || d.frame_count <= 0) return 0;

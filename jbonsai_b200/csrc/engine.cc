@@ -273,7 +273,7 @@ DeviceCtx* Engine::ctx(int device) const {
   return it->second.get();
 }
 
-void Engine::free_output(double* p) { pinned().release(p); }
+void Engine::free_output(void* p) { pinned().release(p); }
 
 // Random::{nrandom, fill_queue} + rnd (src/vocoder/excitation.rs:197-237), run on the host so
 // that ln/sqrt come from the same libm the reference uses; extended lazily, 64 values a time.
@@ -781,6 +781,8 @@ static void launch_mlpg_all(Engine::Resident* r, bool with_pulse) {
 // Where the waveform goes while the filter is still running: wave w's utterance range is copied to
 // host + its sample offset on `copy_stream` as soon as launch w has finished.
 struct WaveCopy {
+  int16_t* host16 = nullptr;  // 16-bit PCM delivery: quantise on the device (into dev16), copy 2 B per sample
+  int16_t* dev16 = nullptr;
   double* host = nullptr;  // destination of utterance 0 of this resident batch
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t done = nullptr;  // recorded after the last copy (or after the filter when `direct`)
@@ -802,7 +804,7 @@ static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_exc
                   r->vp.fperiod % 16 == 0 && r->vd.frame_begin == 0 && r->vd.frame_count < 0;
   if (v3) {
     const int waves = (int)r->wave_seg_first.size() - 1;
-    const bool direct = wc && wc->direct;
+    const bool direct = wc && wc->direct && !wc->host16;
     jbk::VocoderDev vd = r->vd;
     if (direct) vd.out = wc->host;  // zero-copy: output stores cross PCIe while the filter runs
     for (int w = 0; w < waves; ++w) {
@@ -812,9 +814,13 @@ static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_exc
         const int64_t f0 = r->frame_off[(size_t)r->wave_utt_first[w]];
         const int64_t f1 = r->frame_off[(size_t)r->wave_utt_first[w + 1]];
         const int64_t n0 = f0 * r->vp.fperiod, n1 = f1 * r->vp.fperiod;
+        if (wc->host16) JB_LAUNCH(jbk::launch_pcm16(r->vd.out + n0, wc->dev16 + n0, n1 - n0, st));
         JB_CUDA(cudaEventRecord(r->ctx->evw[w & 1], st));
         JB_CUDA(cudaStreamWaitEvent(wc->copy_stream, r->ctx->evw[w & 1], 0));
-        if (n1 > n0)
+        if (n1 > n0 && wc->host16)
+          JB_CUDA(cudaMemcpyAsync(wc->host16 + n0, wc->dev16 + n0, (size_t)(n1 - n0) * 2,
+                                  cudaMemcpyDeviceToHost, wc->copy_stream));
+        else if (n1 > n0)
           JB_CUDA(cudaMemcpyAsync(wc->host + n0, r->vd.out + n0, (size_t)(n1 - n0) * 8,
                                   cudaMemcpyDeviceToHost, wc->copy_stream));
       }
@@ -930,6 +936,17 @@ void Engine::release(Resident* r) const {
 // balanced by frame count, go to the engine's GPUs; no collective is involved.
 void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts, double** out,
                               std::vector<size_t>* out_off, BatchDebug* dbg, BatchTimings* tm) const {
+  synthesize_batch_impl(utts, reinterpret_cast<void**>(out), out_off, dbg, tm, false);
+}
+
+void Engine::synthesize_batch_pcm16(const std::vector<std::vector<std::string>>& utts, int16_t** out,
+                                    std::vector<size_t>* out_off, BatchTimings* tm) const {
+  synthesize_batch_impl(utts, reinterpret_cast<void**>(out), out_off, nullptr, tm, true);
+}
+
+void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& utts, void** out,
+                                   std::vector<size_t>* out_off, BatchDebug* dbg, BatchTimings* tm,
+                                   bool pcm16) const {
   const double t0 = now_ms();
   std::vector<UtterancePack> packs = build_packs(utts);
   const double t1 = now_ms();
@@ -941,7 +958,10 @@ void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts,
   // touch the device even for an empty batch: there is no CPU path to fall back to
   std::vector<DeviceCtx*> ctxs;
   for (int d : devices_) ctxs.push_back(ctx(d));
-  double* host = (double*)pinned().alloc(total * 8);
+  const size_t sample_bytes = pcm16 ? 2 : 8;
+  void* const host_raw = pinned().alloc(total * sample_bytes);
+  double* const host = pcm16 ? nullptr : (double*)host_raw;
+  int16_t* const host16 = pcm16 ? (int16_t*)host_raw : nullptr;
 
   // shard boundaries by cumulative frames
   const size_t ndev = dbg ? 1 : std::min(ctxs.size(), std::max<size_t>(n, 1));
@@ -983,8 +1003,26 @@ void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts,
       JB_CUDA(cudaEventRecord(c->ev[2], c->stream));
       launch_mlpg_all(r, true);
       JB_CUDA(cudaEventRecord(c->ev[3], c->stream));
+      // copy the (whole) result of this shard to the host on the main stream, as f64 or as PCM
+      auto copy_result = [&]() {
+        if (!r->total_samples) return;
+        if (pcm16) {
+          int16_t* dev16 = reinterpret_cast<int16_t*>(r->vd.pulse);  // the pulse train is consumed by now
+          JB_LAUNCH(jbk::launch_pcm16(r->result, dev16, r->total_samples, c->stream));
+          JB_CUDA(cudaMemcpyAsync(host16 + (*out_off)[u0], dev16, (size_t)r->total_samples * 2,
+                                  cudaMemcpyDeviceToHost, c->stream));
+        } else {
+          JB_CUDA(cudaMemcpyAsync(host + (*out_off)[u0], r->result, (size_t)r->total_samples * 8,
+                                  cudaMemcpyDeviceToHost, c->stream));
+        }
+      };
       WaveCopy wc;
-      wc.host = host + (*out_off)[u0];
+      if (pcm16) {
+        wc.host16 = host16 + (*out_off)[u0];
+        wc.dev16 = reinterpret_cast<int16_t*>(r->vd.pulse);
+      } else {
+        wc.host = host + (*out_off)[u0];
+      }
       wc.copy_stream = c->stream_copy;
       wc.done = c->ev[6];
       wc.direct = output_mode == 2;
@@ -992,9 +1030,7 @@ void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts,
                      (dbg || output_mode == 0) ? nullptr : &wc);
       JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
       if (!r->copied_by_waves) {
-        if (r->total_samples)
-          JB_CUDA(cudaMemcpyAsync(host + (*out_off)[u0], r->result, (size_t)r->total_samples * 8,
-                                  cudaMemcpyDeviceToHost, c->stream));
+        copy_result();
         JB_CUDA(cudaEventRecord(c->ev[6], c->stream));
       }
       if (dbg) {
@@ -1020,8 +1056,7 @@ void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts,
         // the copy above carried a waveform with a bad cut: redo the filter sequentially, copy again
         mlsa_sequential_rerun(r);
         JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
-        JB_CUDA(cudaMemcpyAsync(host + (*out_off)[u0], r->result, (size_t)r->total_samples * 8,
-                                cudaMemcpyDeviceToHost, c->stream));
+        copy_result();
         JB_CUDA(cudaEventRecord(c->ev[6], c->stream));
         JB_CUDA(cudaStreamSynchronize(c->stream));
       }
@@ -1039,7 +1074,7 @@ void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts,
       // with two filter waves the first copy runs under the second launch: this is the tail only
       JB_CUDA(cudaEventElapsedTime(&f, kend, c->ev[6])); t.d2h_ms = f > 0 ? f : 0;
       t.h2d_bytes = r->h2d_bytes;
-      t.d2h_bytes = r->total_samples * 8;
+      t.d2h_bytes = r->total_samples * (int64_t)sample_bytes;
       t.total_frames = r->total_frames;
       t.total_samples = r->total_samples;
       t.voiced_samples = r->voiced_samples;
@@ -1059,7 +1094,7 @@ void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts,
   }
   for (auto& e : errs)
     if (e) {
-      pinned().release(host);
+      pinned().release(host_raw);
       throw *e;
     }
   if (tm) {
@@ -1085,7 +1120,7 @@ void Engine::synthesize_batch(const std::vector<std::vector<std::string>>& utts,
       tm->mlsa_fallback += t.mlsa_fallback;
     }
   }
-  *out = host;
+  *out = host_raw;
 }
 
 // ---------------------------------------------------------------- streaming

@@ -79,6 +79,10 @@ class Engine {
   void synthesize_batch(const std::vector<std::vector<std::string>>& utts, double** out,
                         std::vector<size_t>* out_off, BatchDebug* dbg = nullptr,
                         BatchTimings* tm = nullptr) const;
+  // Same synthesis, delivered as 16-bit PCM (clamp, then truncate toward zero: what the reference's
+  // examples do with the Vec<f64>, examples/genji/main.rs:34-35): a quarter of the bytes cross PCIe.
+  void synthesize_batch_pcm16(const std::vector<std::vector<std::string>>& utts, int16_t** out,
+                              std::vector<size_t>* out_off, BatchTimings* tm = nullptr) const;
 
   // Hot path only: packs already built (bench "value": inputs resident on the device is handled
   // inside by `resident` handles, see prepare/run below).
@@ -91,11 +95,13 @@ class Engine {
   void fetch_resident(Resident* r, double** out, std::vector<size_t>* out_off) const;
   void release(Resident* r) const;
 
-  static void free_output(double* p);
+  static void free_output(void* p);
 
   std::vector<double> noise_prefix(size_t n) const;  // first n Gaussians (host table)
 
  private:
+  void synthesize_batch_impl(const std::vector<std::vector<std::string>>& utts, void** out,
+                             std::vector<size_t>* out_off, BatchDebug* dbg, BatchTimings* tm, bool pcm16) const;
   friend class DeviceCtx;
   friend class Stream;
   explicit Engine(VoiceSet v);

@@ -210,6 +210,23 @@ def test_unsupported_is_loud():
     assert ei.value.kind == "Unsupported"
 
 
+def test_pcm16_is_the_reference_clamp_of_the_f64_waveform(eng):
+    # examples/genji/main.rs:34-35: value.min(i16::MAX).max(i16::MIN) as i16 (truncation toward zero)
+    utts = [SAMPLE_SENTENCE_1, [], SAMPLE_SENTENCE_2[:7]]
+    e = jb.Engine.load([NITECH])
+    e.set("volume", 6.0)  # loud enough to clip
+    w, off = e.synthesize_batch(utts)
+    tm = {}
+    q, off2 = e.synthesize_batch_pcm16(utts, tm)
+    assert q.dtype == np.int16 and list(off) == list(off2) and tm["d2h_bytes"] == 2 * len(w)
+    want = np.trunc(np.clip(w, -32768.0, 32767.0)).astype(np.int16)
+    assert np.array_equal(q, want)
+    assert (want == 32767).any() or (want == -32768).any()
+    e.set_output_mode(0)
+    q0, _ = e.synthesize_batch_pcm16(utts)
+    assert np.array_equal(q0, want)
+
+
 # ---- resident batch and streaming
 def test_resident_equals_batch(eng):
     utts = wl.synthetic_batch(5, wl.SEED_NITECH, lmin=4, lmax=10)
