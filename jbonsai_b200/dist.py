@@ -4,7 +4,25 @@ for the barrier and for the max / sum over ranks of the timing and sample counte
 GPU box, `gloo` in the CPU tests."""
 from __future__ import annotations
 
+import contextlib
 import os
+import sys
+
+
+@contextlib.contextmanager
+def _stdout_to_stderr():
+    """NCCL prints its version banner on stdout when the first communicator is created; bench.py's
+    stdout must carry exactly one JSON line, so the banner is sent to stderr (file-descriptor level:
+    the print comes from C)."""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    try:
+        os.dup2(2, 1)
+        yield
+    finally:
+        sys.stdout.flush()
+        os.dup2(saved, 1)
+        os.close(saved)
 
 
 def dist_env():
@@ -29,7 +47,9 @@ class Reducer:
             if backend == "nccl":
                 torch.cuda.set_device(local_rank)
                 self.device = f"cuda:{local_rank}"
-                dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+                with _stdout_to_stderr():
+                    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+                    dist.barrier()  # creates the communicator now, inside the redirect
             else:
                 dist.init_process_group(backend)
             self.dist = dist
