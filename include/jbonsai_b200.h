@@ -80,9 +80,10 @@ int jb_engine_set_device_gather(jb_engine* e, int enabled);
  * tap error d moves the output by at most ~8 d) the batch is filtered again by the sequential kernel. */
 int jb_engine_set_mlsa_segmenting(jb_engine* e, int warm_frames, double cut_tolerance);
 /* How jb_engine_synthesize_batch brings the waveform (8 B per sample, the Vec<f64> of
- * engine.rs:294) to the host. 1 (default): two filter launches, the first half of the batch copied
- * under the second; 2: the filter kernel stores straight into the pinned, device-visible output
- * buffer (measured slower); 0: one copy after the filter. Same samples either way. */
+ * engine.rs:294) to the host. 1 (default): the batch is filtered in four launches, each quarter copied
+ * under the next launch (10 + w selects w launches instead); 2: the filter kernel stores straight into
+ * the pinned, device-visible output buffer (measured slower); 0: one copy after the filter. Same
+ * samples (to rounding of the segment cuts) either way. */
 int jb_engine_set_output_mode(jb_engine* e, int mode);
 
 /* Engine::synthesize (src/engine.rs:294-296): labels -> raw f64 samples (not clipped).

@@ -191,7 +191,7 @@ class Engine:
         _check(lib.jb_engine_set_mlsa_segmenting(self._h, int(warm_frames), C.c_double(cut_tolerance)))
 
     def set_output_mode(self, mode: int) -> None:
-        """1 (default): two filter waves, first half copied under the second; 2: zero-copy stores; 0: one copy."""
+        """1 (default): four filter waves, each copied under the next (10 + w: w waves); 2: zero-copy stores; 0: one copy."""
         _check(lib.jb_engine_set_output_mode(self._h, int(mode)))
 
     # -- Engine::synthesize (src/engine.rs:294-296)

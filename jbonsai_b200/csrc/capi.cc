@@ -147,8 +147,15 @@ int jb_engine_set_device_gather(jb_engine* e, int enabled) {
 
 int jb_engine_set_output_mode(jb_engine* e, int mode) {
   JB_TRY
-  if (mode < 0 || mode > 2) throw jb::Error(jb::kErrArgument, "output mode must be 0, 1 or 2");
+  // mode 1 with another number of filter launches: 10 + waves (e.g. 14 = four waves)
+  if (mode >= 11 && mode <= 26) {
+    e->e->output_mode = 1;
+    e->e->output_waves = mode - 10;
+    return JB_OK;
+  }
+  if (mode < 0 || mode > 2) throw jb::Error(jb::kErrArgument, "output mode must be 0, 1, 2 or 10 + waves");
   e->e->output_mode = mode;
+  if (mode == 1) e->e->output_waves = 4;
   JB_CATCH
 }
 

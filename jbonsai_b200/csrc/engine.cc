@@ -453,7 +453,8 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
     const int64_t W = e.mlsa_warm_frames;
     const int64_t target = (int64_t)ctx->sm_count * 4 * kSegWarpsPerSmsp * 6;
     int waves = std::max(1, mlsa_waves);
-    if (TF < (int64_t)waves * target * kSegMinFrames) waves = 1;  // too small to fill two waves
+    // every wave should still fill the chip with segments of at least kSegMinFrames / 2 own frames
+    while (waves > 1 && TF < (int64_t)waves * target * (kSegMinFrames / 2)) --waves;
     std::vector<size_t> ucut(waves + 1, n_utt);
     ucut[0] = 0;
     for (int wv = 1; wv < waves; ++wv) {
@@ -489,7 +490,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
           }
         }
       };
-      int64_t S = std::max<int64_t>(kSegMinFrames, (TFw + target - 1) / target);
+      int64_t S = std::max<int64_t>(waves > 1 ? kSegMinFrames / 2 : kSegMinFrames, (TFw + target - 1) / target);
       cut(S);
       // One wave: all segments run about equally long, so a grid slightly larger than the chip holds
       // (target segments) would leave a second, nearly empty wave as long as the first.
@@ -986,7 +987,7 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
       const double p0 = now_ms();
       // two filter waves: the copy of the first half of the waveform overlaps the second launch
       Resident* r = make_resident(*this, c, packs.data() + u0, u1 - u0, false, condition,
-                                  (!dbg && output_mode == 1) ? 2 : 1);
+                                  (!dbg && output_mode == 1) ? (pcm16 ? 1 : output_waves) : 1);
       struct Guard {
         DeviceCtx* c;
         Resident* r;
