@@ -227,6 +227,27 @@ def test_pcm16_is_the_reference_clamp_of_the_f64_waveform(eng):
     assert np.array_equal(q0, want)
 
 
+def test_output_waves_equal_single_copy():
+    # a batch big enough for the default output mode to cut it into several filter waves (each copied
+    # to the host under the next one): same samples as one launch + one copy, to rounding of the cuts
+    e = jb.Engine.load([TOHOKU_NEUTRAL])
+    utts = wl.timed_batch(e, 720, wl.SEED_TOHOKU)
+    tm = {}
+    w, off = e.synthesize_batch(utts, tm)
+    assert tm["mlsa_fallback"] == 0 and tm["launches"] >= 20
+    e.set_output_mode(0)
+    tm0 = {}
+    w0, off0 = e.synthesize_batch(utts, tm0)
+    assert tm0["mlsa_segments"] < tm["mlsa_segments"]  # the waves really were cut separately
+    assert list(off) == list(off0) and np.abs(w - w0).max() <= SCHED_ATOL
+    e.set_output_mode(2)
+    w2, _ = e.synthesize_batch(utts)
+    assert np.array_equal(w2, w0)  # zero-copy stores: same launch, other destination
+    e.set_output_mode(1)
+    q, _ = e.synthesize_batch_pcm16(utts)
+    assert np.array_equal(q, np.trunc(np.clip(w0, -32768.0, 32767.0)).astype(np.int16))
+
+
 # ---- resident batch and streaming
 def test_resident_equals_batch(eng):
     utts = wl.synthetic_batch(5, wl.SEED_NITECH, lmin=4, lmax=10)
