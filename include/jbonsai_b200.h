@@ -85,6 +85,10 @@ int jb_engine_set_mlsa_segmenting(jb_engine* e, int warm_frames, double cut_tole
  * the pinned, device-visible output buffer (measured slower); 0: one copy after the filter. Same
  * samples (to rounding of the segment cuts) either way. */
 int jb_engine_set_output_mode(jb_engine* e, int mode);
+/* Sub-batches of one jb_engine_synthesize_batch call on one device (default 2, used for batches of
+ * 64+ utterances that fill the chip more than once): the host looks up the stream parameters of
+ * chunk k + 1 while the GPU works on chunk k. 1 = the whole batch in one pass. Same samples. */
+int jb_engine_set_pipeline_chunks(jb_engine* e, int chunks);
 
 /* Engine::synthesize (src/engine.rs:294-296): labels -> raw f64 samples (not clipped).
  * *out is owned by the library: release with jb_free(). Empty input -> *out_len = 0. */

@@ -1,6 +1,8 @@
 // extern "C" layer over jb::Engine (declarations + reference citations: include/jbonsai_b200.h).
 #include <cstring>
 #include <string>
+#include <thread>
+#include <vector>
 
 #include <cuda_runtime.h>
 
@@ -42,9 +44,19 @@ int fail(const std::exception& ex) {
 std::vector<std::vector<std::string>> to_utts(const char* const* lines, const size_t* line_off,
                                               size_t n_utt) {
   std::vector<std::vector<std::string>> utts(n_utt);
-  for (size_t u = 0; u < n_utt; ++u) {
+  for (size_t u = 0; u < n_utt; ++u)
     if (line_off[u + 1] < line_off[u]) throw jb::Error(jb::kErrArgument, "line_off must be non-decreasing");
-    utts[u].assign(lines + line_off[u], lines + line_off[u + 1]);
+  auto copy_range = [&](size_t a, size_t b) {
+    for (size_t u = a; u < b; ++u) utts[u].assign(lines + line_off[u], lines + line_off[u + 1]);
+  };
+  // ~40 label strings per utterance: for a big batch the copies are worth a few threads
+  const size_t nt = n_utt >= 256 ? std::min<size_t>(8, std::max(1u, std::thread::hardware_concurrency())) : 1;
+  if (nt <= 1) {
+    copy_range(0, n_utt);
+  } else {
+    std::vector<std::thread> th;
+    for (size_t t = 0; t < nt; ++t) th.emplace_back(copy_range, n_utt * t / nt, n_utt * (t + 1) / nt);
+    for (auto& t : th) t.join();
   }
   return utts;
 }
@@ -156,6 +168,13 @@ int jb_engine_set_output_mode(jb_engine* e, int mode) {
   if (mode < 0 || mode > 2) throw jb::Error(jb::kErrArgument, "output mode must be 0, 1, 2 or 10 + waves");
   e->e->output_mode = mode;
   if (mode == 1) e->e->output_waves = 4;
+  JB_CATCH
+}
+
+int jb_engine_set_pipeline_chunks(jb_engine* e, int chunks) {
+  JB_TRY
+  if (chunks < 1 || chunks > 4) throw jb::Error(jb::kErrArgument, "pipeline chunks must be 1..4");
+  e->e->pipeline_chunks = chunks;
   JB_CATCH
 }
 

@@ -175,7 +175,8 @@ int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDe
                    int seg_first, int seg_count, cudaStream_t stream);
 // After every wave has run: the largest state mismatch over all cuts -> *worst (device), for the
 // host to compare with its tolerance.
-int launch_mlsa_seg_check(const MlsaSegments& sg, double* worst, cudaStream_t stream);
+// `host_mirror` (pinned, device-visible, or nullptr): also stored there by the device, no copy engine.
+int launch_mlsa_seg_check(const MlsaSegments& sg, double* worst, double* host_mirror, cudaStream_t stream);
 
 // Streaming: copy frames [frame_begin, frame_begin+frame_count) of every utterance into
 // chunk[n_utt][frame_count*fperiod] (zero padded past the end of an utterance).

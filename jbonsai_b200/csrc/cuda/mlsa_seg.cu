@@ -298,6 +298,14 @@ __global__ void k_mlsa_seg_check(MlsaSegments sg, double* worst) {
     atomicMax(reinterpret_cast<unsigned long long*>(worst), (unsigned long long)__double_as_longlong(m));
 }
 
+// The result goes to pinned host memory by a plain store from the device: a cudaMemcpy on this
+// stream would queue in the copy engine behind the waveform copies of the copy stream and hold up
+// everything launched after it.
+__global__ void k_publish(const double* src, double* host_dst) {
+  *host_dst = *src;
+  __threadfence_system();
+}
+
 }  // namespace
 
 int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, const MlsaSegments& sg,
@@ -312,11 +320,12 @@ int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDe
   return (int)cudaGetLastError();
 }
 
-int launch_mlsa_seg_check(const MlsaSegments& sg, double* worst, cudaStream_t stream) {
+int launch_mlsa_seg_check(const MlsaSegments& sg, double* worst, double* host_mirror, cudaStream_t stream) {
   if (sg.n_seg == 0 || worst == nullptr || sg.state == nullptr) return 0;
   cudaError_t e = cudaMemsetAsync(worst, 0, sizeof(double), stream);
   if (e != cudaSuccess) return (int)e;
   k_mlsa_seg_check<<<sg.n_seg, 64, 0, stream>>>(sg, worst);
+  if (host_mirror) k_publish<<<1, 1, 0, stream>>>(worst, host_mirror);
   return (int)cudaGetLastError();
 }
 

@@ -147,10 +147,19 @@ class DeviceCtx {
   std::mutex mu;  // one in-flight batch per (engine, device)
   double* d_noise = nullptr;
   size_t noise_len = 0;
-  cudaEvent_t ev[8];
+  // Timing events and the pinned cut-check word come in kMaxChunks slots: synthesize_batch keeps
+  // several sub-batches in flight on one device and reads each one's numbers at the end.
+  static constexpr int kMaxChunks = 4;
+  cudaEvent_t evsets[kMaxChunks][8];
+  cudaEvent_t* ev = evsets[0];
+  void use_slot(int i) {
+    ev = evsets[i];
+    h_worst = h_worst_base + i;
+  }
   std::multimap<size_t, void*> cached;  // freed device blocks
   int sm_count = 148;
-  double* h_worst = nullptr;  // pinned: MLSA variant 3 cut-check result
+  double* h_worst_base = nullptr;
+  double* h_worst = nullptr;  // pinned: MLSA variant 3 cut-check result (of the current slot)
   // leaf pdf tables of the engine's voices, resident for the life of the context (device gather)
   double* d_tab_mean[3] = {nullptr, nullptr, nullptr};
   double* d_tab_vari[3] = {nullptr, nullptr, nullptr};
@@ -194,10 +203,12 @@ class DeviceCtx {
     JB_CUDA(cudaStreamCreateWithFlags(&stream_copy, cudaStreamNonBlocking));
     for (auto& x : evx) JB_CUDA(cudaEventCreateWithFlags(&x, cudaEventDisableTiming));
     for (auto& x : evw) JB_CUDA(cudaEventCreateWithFlags(&x, cudaEventDisableTiming));
-    for (auto& x : ev) JB_CUDA(cudaEventCreate(&x));
+    for (auto& set : evsets)
+      for (auto& x : set) JB_CUDA(cudaEventCreate(&x));
     JB_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
-    JB_CUDA(cudaMallocHost((void**)&h_worst, sizeof(double)));
-    *h_worst = 0.0;
+    JB_CUDA(cudaMallocHost((void**)&h_worst_base, kMaxChunks * sizeof(double)));
+    for (int i = 0; i < kMaxChunks; ++i) h_worst_base[i] = 0.0;
+    use_slot(0);
   }
   ~DeviceCtx() {
     cudaSetDevice(device);
@@ -208,8 +219,9 @@ class DeviceCtx {
       if (d_tab_vari[s]) cudaFree(d_tab_vari[s]);
       if (d_tab_msd[s]) cudaFree(d_tab_msd[s]);
     }
-    if (h_worst) cudaFreeHost(h_worst);
-    for (auto& x : ev) cudaEventDestroy(x);
+    if (h_worst_base) cudaFreeHost(h_worst_base);
+    for (auto& set : evsets)
+      for (auto& x : set) cudaEventDestroy(x);
     for (auto& x : evx) cudaEventDestroy(x);
     for (auto& x : evw) cudaEventDestroy(x);
     if (stream_copy) cudaStreamDestroy(stream_copy);
@@ -314,7 +326,16 @@ std::vector<double> Engine::noise_prefix(size_t n) const {
   return std::vector<double>(t.begin(), t.begin() + n);
 }
 
-std::vector<UtterancePack> Engine::build_packs(const std::vector<std::vector<std::string>>& utts) const {
+std::vector<UtterancePack> Engine::build_packs(const std::vector<std::vector<std::string>>& all, size_t first,
+                                               size_t count) const {
+  if (first > all.size()) first = all.size();
+  if (count > all.size() - first) count = all.size() - first;
+  struct Range {  // utterances [first, first + count) of `all`, indexed from 0
+    const std::vector<std::string>* p;
+    size_t n;
+    size_t size() const { return n; }
+    const std::vector<std::string>& operator[](size_t i) const { return p[i]; }
+  } utts{all.data() + first, count};
   if (condition.stage != 0)
     throw Error(kErrUnsupported, "stage != 0 (GAMMA option: LSP/MGLSA vocoder) is not built yet");
   if (voices_.global_metadata().num_streams < 3 || voices_.stream_metadata(2).vector_length == 0)
@@ -383,6 +404,7 @@ struct Engine::Resident {
   bool used_fallback = false;      // the last pass re-ran the sequential kernel
   bool copied_by_waves = false;    // the last pass already queued its device-to-host copies
   cudaEvent_t kernels_end = nullptr;  // recorded after the last kernel of the last pass (variant 3)
+  double* h_worst = nullptr;          // pinned word the last pass copies its cut-check result to
   const double* result = nullptr;  // device waveform of the last pass
   // kernels per pass: expand, 3 solves (+ GV kernels), 2 frame preps, pulse (memset excluded),
   // excitation, MLSA (+ cut check for variant 3)
@@ -826,11 +848,10 @@ static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_exc
                                   cudaMemcpyDeviceToHost, wc->copy_stream));
       }
     }
-    JB_LAUNCH(jbk::launch_mlsa_seg_check(r->segs, r->d_worst, st));
-    // end of the kernels for the timers: the 8-byte copy below can queue behind a wave copy
+    r->h_worst = r->ctx->h_worst;
+    JB_LAUNCH(jbk::launch_mlsa_seg_check(r->segs, r->d_worst, r->h_worst, st));
     JB_CUDA(cudaEventRecord(r->ctx->ev[7], st));
     r->kernels_end = r->ctx->ev[7];
-    JB_CUDA(cudaMemcpyAsync(r->ctx->h_worst, r->d_worst, sizeof(double), cudaMemcpyDeviceToHost, st));
     r->result = r->vd.out;
     if (wc) {
       JB_CUDA(cudaEventRecord(wc->done, direct ? st : wc->copy_stream));
@@ -846,7 +867,7 @@ static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_exc
 // Returns true when it did; the caller then repeats whatever it had queued behind the filter.
 static bool mlsa_cut_check_failed(Engine::Resident* r, double tol) {
   if (r->result != r->vd.out || r->vd.out == nullptr) return false;
-  const double w = *r->ctx->h_worst;
+  const double w = r->h_worst ? *r->h_worst : 0.0;
   return !(w <= tol);  // NaN counts as a failed cut
 }
 static void mlsa_sequential_rerun(Engine::Resident* r) {
@@ -898,7 +919,7 @@ double Engine::run_resident(Resident* r, BatchTimings* tm) const {
     tm->launches = r->launches() + (r->used_fallback ? 1 : 0);
     tm->mlsa_segments = r->segs.n_seg;
     tm->mlsa_seg_frames = r->seg_frames;
-    tm->mlsa_cut_worst = r->segs.n_seg > 0 ? *c->h_worst : 0.0;
+    tm->mlsa_cut_worst = (r->segs.n_seg > 0 && r->h_worst) ? *r->h_worst : 0.0;
     tm->mlsa_fallback = r->used_fallback ? 1 : 0;
   }
   return total;
@@ -949,140 +970,240 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
                                    std::vector<size_t>* out_off, BatchDebug* dbg, BatchTimings* tm,
                                    bool pcm16) const {
   const double t0 = now_ms();
-  std::vector<UtterancePack> packs = build_packs(utts);
-  const double t1 = now_ms();
-  const size_t n = packs.size();
+  const size_t n = utts.size();
   const int fperiod = (int)condition.fperiod;
-  out_off->assign(n + 1, 0);
-  for (size_t u = 0; u < n; ++u) (*out_off)[u + 1] = (*out_off)[u] + packs[u].nframes * (size_t)fperiod;
-  const size_t total = (*out_off)[n];
   // touch the device even for an empty batch: there is no CPU path to fall back to
   std::vector<DeviceCtx*> ctxs;
   for (int d : devices_) ctxs.push_back(ctx(d));
+  const size_t ndev = dbg ? 1 : std::min(ctxs.size(), std::max<size_t>(n, 1));
+
+  // ---- frames per utterance -> output offsets. One device and a large batch: only the label and
+  // duration part of the front-end runs here (utterance_frames); the stream parameters are looked
+  // up chunk by chunk below, so that the host works on chunk k + 1 while the GPU filters chunk k.
+  // Otherwise the whole front-end runs now.
+  const bool pipelined = !dbg && ndev == 1 && n >= 64 && pipeline_chunks > 1;
+  std::vector<UtterancePack> all_packs;
+  std::vector<size_t> nframes(n, 0);
+  if (pipelined) {
+    if (condition.stage != 0 || voices_.global_metadata().num_streams < 3)
+      build_packs(utts, 0, 0);  // raises the proper Unsupported error
+    std::unique_ptr<Error> err;
+    std::mutex emu;
+    parallel_for(n, [&](size_t u) {
+      try {
+        nframes[u] = utterance_frames(voices_, condition, utts[u]);
+      } catch (const Error& e) {
+        std::lock_guard<std::mutex> g(emu);
+        if (!err) err.reset(new Error(e));
+      } catch (const std::exception& e) {
+        std::lock_guard<std::mutex> g(emu);
+        if (!err) err.reset(new Error(kErrArgument, e.what()));
+      }
+    });
+    if (err) throw *err;
+  } else {
+    all_packs = build_packs(utts);
+    for (size_t u = 0; u < n; ++u) nframes[u] = all_packs[u].nframes;
+  }
+  double front_ms = now_ms() - t0;  // exposed front-end time (later chunks run under the GPU)
+  out_off->assign(n + 1, 0);
+  for (size_t u = 0; u < n; ++u) (*out_off)[u + 1] = (*out_off)[u] + nframes[u] * (size_t)fperiod;
+  const size_t total = (*out_off)[n];
   const size_t sample_bytes = pcm16 ? 2 : 8;
   void* const host_raw = pinned().alloc(total * sample_bytes);
   double* const host = pcm16 ? nullptr : (double*)host_raw;
   int16_t* const host16 = pcm16 ? (int16_t*)host_raw : nullptr;
 
-  // shard boundaries by cumulative frames
-  const size_t ndev = dbg ? 1 : std::min(ctxs.size(), std::max<size_t>(n, 1));
-  std::vector<size_t> cut(ndev + 1, n);
-  cut[0] = 0;
-  {
-    size_t u = 0;
-    for (size_t k = 1; k < ndev; ++k) {
-      const size_t target = total / ndev * k;
-      while (u < n && (*out_off)[u] < target) ++u;
+  // contiguous utterance ranges of about equal frame count
+  auto split = [&](size_t a, size_t b, size_t parts) {
+    std::vector<size_t> cut(parts + 1, b);
+    cut[0] = a;
+    const size_t s0 = (*out_off)[a], span = (*out_off)[b] - s0;
+    size_t u = a;
+    for (size_t k = 1; k < parts; ++k) {
+      const size_t target = s0 + span / parts * k;
+      while (u < b && (*out_off)[u] < target) ++u;
       cut[k] = u;
     }
-  }
+    return cut;
+  };
+  const std::vector<size_t> cut = split(0, n, ndev);
   std::vector<BatchTimings> tms(ndev);
   std::vector<std::unique_ptr<Error>> errs(ndev);
+
+  struct Chunk {
+    Resident* r = nullptr;
+    size_t u0 = 0, u1 = 0;
+    int slot = 0;
+    double pack_ms = 0;
+  };
   auto work = [&](size_t k) {
+    DeviceCtx* c = ctxs[k];
+    std::vector<Chunk> chunks;
+    auto free_chunks = [&]() {
+      cudaStreamSynchronize(c->stream);
+      cudaStreamSynchronize(c->stream_copy);
+      for (Chunk& ch : chunks)
+        if (ch.r) {
+          c->dfree(ch.r->d_in, ch.r->in_cap);
+          c->dfree(ch.r->d_work, ch.r->work_cap);
+          delete ch.r;
+          ch.r = nullptr;
+        }
+      c->use_slot(0);
+    };
     try {
       const size_t u0 = cut[k], u1 = cut[k + 1];
       if (u1 <= u0) return;
-      DeviceCtx* c = ctxs[k];
       std::lock_guard<std::mutex> g(c->mu);
-      const double p0 = now_ms();
-      // two filter waves: the copy of the first half of the waveform overlaps the second launch
-      Resident* r = make_resident(*this, c, packs.data() + u0, u1 - u0, false, condition,
-                                  (!dbg && output_mode == 1) ? (pcm16 ? 1 : output_waves) : 1);
-      struct Guard {
-        DeviceCtx* c;
-        Resident* r;
-        ~Guard() {
-          cudaStreamSynchronize(c->stream);
-          cudaStreamSynchronize(c->stream_copy);
-          c->dfree(r->d_in, r->in_cap);
-          c->dfree(r->d_work, r->work_cap);
-          delete r;
-        }
-      } guard{c, r};
-      BatchTimings& t = tms[k];
-      t.pack_ms = now_ms() - p0;
-      JB_CUDA(cudaEventRecord(c->ev[2], c->stream));
-      launch_mlpg_all(r, true);
-      JB_CUDA(cudaEventRecord(c->ev[3], c->stream));
-      // copy the (whole) result of this shard to the host on the main stream, as f64 or as PCM
-      auto copy_result = [&]() {
+      // chunks of this device: each is a complete pass (gather ... filter ... copy) of its own
+      size_t nchunks = 1;
+      if (pipelined) {
+        const int64_t frames = (int64_t)(((*out_off)[u1] - (*out_off)[u0]) / (size_t)fperiod);
+        const int64_t wave = (int64_t)c->sm_count * 4 * kSegWarpsPerSmsp * 6 * (kSegMinFrames / 2);
+        nchunks = (size_t)std::max<int64_t>(1, std::min<int64_t>({(int64_t)pipeline_chunks, (int64_t)DeviceCtx::kMaxChunks,
+                                                                  frames / std::max<int64_t>(wave, 1)}));
+      }
+      // Two chunks: a small first one (one filter wave's worth of frames), so that the GPU starts
+      // after a short front-end and its waveform is crossing PCIe early, then the rest.
+      std::vector<size_t> ccut = split(u0, u1, nchunks);
+      std::vector<int> chunk_waves(nchunks, 1);
+      const int waves_total = (!dbg && output_mode == 1 && !pcm16) ? std::max(1, output_waves) : 1;
+      if (nchunks == 2 && waves_total >= 2) {
+        ccut = split(u0, u1, (size_t)waves_total);
+        ccut = {ccut[0], ccut[1], ccut[(size_t)waves_total]};
+        chunk_waves = {1, waves_total - 1};
+      } else {
+        for (auto& w : chunk_waves) w = std::max(1, (waves_total + (int)nchunks - 1) / (int)nchunks);
+      }
+
+      auto copy_result = [&](Chunk& ch) {  // whole result of a chunk on the main stream, f64 or PCM
+        Resident* r = ch.r;
         if (!r->total_samples) return;
         if (pcm16) {
           int16_t* dev16 = reinterpret_cast<int16_t*>(r->vd.pulse);  // the pulse train is consumed by now
           JB_LAUNCH(jbk::launch_pcm16(r->result, dev16, r->total_samples, c->stream));
-          JB_CUDA(cudaMemcpyAsync(host16 + (*out_off)[u0], dev16, (size_t)r->total_samples * 2,
+          JB_CUDA(cudaMemcpyAsync(host16 + (*out_off)[ch.u0], dev16, (size_t)r->total_samples * 2,
                                   cudaMemcpyDeviceToHost, c->stream));
         } else {
-          JB_CUDA(cudaMemcpyAsync(host + (*out_off)[u0], r->result, (size_t)r->total_samples * 8,
+          JB_CUDA(cudaMemcpyAsync(host + (*out_off)[ch.u0], r->result, (size_t)r->total_samples * 8,
                                   cudaMemcpyDeviceToHost, c->stream));
         }
       };
-      WaveCopy wc;
-      if (pcm16) {
-        wc.host16 = host16 + (*out_off)[u0];
-        wc.dev16 = reinterpret_cast<int16_t*>(r->vd.pulse);
-      } else {
-        wc.host = host + (*out_off)[u0];
-      }
-      wc.copy_stream = c->stream_copy;
-      wc.done = c->ev[6];
-      wc.direct = output_mode == 2;
-      launch_vocoder(r, mlsa_variant, dbg && dbg->stop_after_excitation, c->ev[4], true,
-                     (dbg || output_mode == 0) ? nullptr : &wc);
-      JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
-      if (!r->copied_by_waves) {
-        copy_result();
-        JB_CUDA(cudaEventRecord(c->ev[6], c->stream));
-      }
-      if (dbg) {
-        const jbk::StreamSet& ss = r->streams;
-        const size_t TF = (size_t)r->total_frames;
-        if (dbg->want_parameters) {
-          dbg->mcp.resize(TF * ss.s[0].dim);
-          dbg->lf0.resize(TF * ss.s[1].dim);
-          dbg->lpf.resize(TF * ss.s[2].dim);
-          JB_CUDA(cudaMemcpyAsync(dbg->mcp.data(), ss.s[0].par, dbg->mcp.size() * 8, cudaMemcpyDeviceToHost, c->stream));
-          JB_CUDA(cudaMemcpyAsync(dbg->lf0.data(), ss.s[1].par, dbg->lf0.size() * 8, cudaMemcpyDeviceToHost, c->stream));
-          JB_CUDA(cudaMemcpyAsync(dbg->lpf.data(), ss.s[2].par, dbg->lpf.size() * 8, cudaMemcpyDeviceToHost, c->stream));
+
+      for (size_t q = 0; q < nchunks; ++q) {
+        Chunk ch;
+        ch.u0 = ccut[q];
+        ch.u1 = ccut[q + 1];
+        ch.slot = (int)q;
+        if (ch.u1 <= ch.u0) continue;
+        std::vector<UtterancePack> local;
+        const UtterancePack* packs = nullptr;
+        if (pipelined) {
+          const double f0 = now_ms();
+          local = build_packs(utts, ch.u0, ch.u1 - ch.u0);  // under the GPU work of the chunk before
+          for (size_t u = ch.u0; u < ch.u1; ++u)
+            if (local[u - ch.u0].nframes != nframes[u]) throw Error(kErrArgument, "front-end frame count changed");
+          packs = local.data();
+          if (q == 0) front_ms += now_ms() - f0;
+        } else {
+          packs = all_packs.data() + ch.u0;
         }
-        if (dbg->want_pulse) {
-          dbg->pulse.resize((size_t)r->total_samples);
-          JB_CUDA(cudaMemcpyAsync(dbg->pulse.data(), r->vd.pulse, dbg->pulse.size() * 8, cudaMemcpyDeviceToHost, c->stream));
+        c->use_slot(ch.slot);
+        const double p0 = now_ms();
+        ch.r = make_resident(*this, c, packs, ch.u1 - ch.u0, false, condition, chunk_waves[q]);
+        ch.pack_ms = now_ms() - p0;
+        chunks.push_back(ch);
+        Resident* r = ch.r;
+        JB_CUDA(cudaEventRecord(c->ev[2], c->stream));
+        launch_mlpg_all(r, true);
+        JB_CUDA(cudaEventRecord(c->ev[3], c->stream));
+        WaveCopy wc;
+        if (pcm16) {
+          wc.host16 = host16 + (*out_off)[ch.u0];
+          wc.dev16 = reinterpret_cast<int16_t*>(r->vd.pulse);
+        } else {
+          wc.host = host + (*out_off)[ch.u0];
         }
-        dbg->frame_off = r->frame_off;
+        wc.copy_stream = c->stream_copy;
+        wc.done = c->ev[6];
+        wc.direct = output_mode == 2;
+        launch_vocoder(r, mlsa_variant, dbg && dbg->stop_after_excitation, c->ev[4], true,
+                       (dbg || output_mode == 0) ? nullptr : &wc);
+        JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
+        if (!r->copied_by_waves) {
+          copy_result(chunks.back());
+          JB_CUDA(cudaEventRecord(c->ev[6], c->stream));
+        }
+        if (dbg) {
+          const jbk::StreamSet& ss = r->streams;
+          const size_t TF = (size_t)r->total_frames;
+          if (dbg->want_parameters) {
+            dbg->mcp.resize(TF * ss.s[0].dim);
+            dbg->lf0.resize(TF * ss.s[1].dim);
+            dbg->lpf.resize(TF * ss.s[2].dim);
+            JB_CUDA(cudaMemcpyAsync(dbg->mcp.data(), ss.s[0].par, dbg->mcp.size() * 8, cudaMemcpyDeviceToHost, c->stream));
+            JB_CUDA(cudaMemcpyAsync(dbg->lf0.data(), ss.s[1].par, dbg->lf0.size() * 8, cudaMemcpyDeviceToHost, c->stream));
+            JB_CUDA(cudaMemcpyAsync(dbg->lpf.data(), ss.s[2].par, dbg->lpf.size() * 8, cudaMemcpyDeviceToHost, c->stream));
+          }
+          if (dbg->want_pulse) {
+            dbg->pulse.resize((size_t)r->total_samples);
+            JB_CUDA(cudaMemcpyAsync(dbg->pulse.data(), r->vd.pulse, dbg->pulse.size() * 8, cudaMemcpyDeviceToHost, c->stream));
+          }
+          dbg->frame_off = r->frame_off;
+        }
       }
       JB_CUDA(cudaStreamSynchronize(c->stream));
-      if (r->copied_by_waves) JB_CUDA(cudaStreamSynchronize(c->stream_copy));
-      if (mlsa_cut_check_failed(r, mlsa_cut_tolerance)) {
-        // the copy above carried a waveform with a bad cut: redo the filter sequentially, copy again
-        mlsa_sequential_rerun(r);
-        JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
-        copy_result();
-        JB_CUDA(cudaEventRecord(c->ev[6], c->stream));
-        JB_CUDA(cudaStreamSynchronize(c->stream));
+      JB_CUDA(cudaStreamSynchronize(c->stream_copy));
+
+      BatchTimings& t = tms[k];
+      for (Chunk& ch : chunks) {
+        Resident* r = ch.r;
+        c->use_slot(ch.slot);
+        if (mlsa_cut_check_failed(r, mlsa_cut_tolerance)) {
+          // the copies above carried a waveform with a bad cut: redo the filter sequentially, copy again
+          mlsa_sequential_rerun(r);
+          JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
+          copy_result(ch);
+          JB_CUDA(cudaEventRecord(c->ev[6], c->stream));
+          JB_CUDA(cudaStreamSynchronize(c->stream));
+        }
+        t.mlsa_segments += r->segs.n_seg;
+        t.mlsa_seg_frames += r->seg_frames;
+        const double worst = r->segs.n_seg > 0 && r->h_worst && !(dbg && dbg->stop_after_excitation) ? *r->h_worst : 0.0;
+        t.mlsa_cut_worst = std::max(t.mlsa_cut_worst, worst);
+        t.mlsa_fallback += r->used_fallback ? 1 : 0;
+        float f = 0;
+        cudaEvent_t kend = (r->kernels_end && !r->used_fallback) ? r->kernels_end : c->ev[5];
+        JB_CUDA(cudaEventElapsedTime(&f, c->ev[0], c->ev[1])); t.h2d_ms += f;
+        JB_CUDA(cudaEventElapsedTime(&f, c->ev[2], c->ev[3])); t.mlpg_ms += f;
+        JB_CUDA(cudaEventElapsedTime(&f, c->ev[3], c->ev[4])); t.excitation_ms += f;
+        JB_CUDA(cudaEventElapsedTime(&f, c->ev[4], kend)); t.mlsa_ms += f;
+        if (ch.slot == chunks.front().slot) t.pack_ms = ch.pack_ms;  // later chunks pack under the GPU
+        t.h2d_bytes += r->h2d_bytes;
+        t.d2h_bytes += r->total_samples * (int64_t)sample_bytes;
+        t.total_frames += r->total_frames;
+        t.total_samples += r->total_samples;
+        t.voiced_samples += r->voiced_samples;
+        t.launches += r->launches() + (r->used_fallback ? 1 : 0);
       }
-      t.mlsa_segments = r->segs.n_seg;
-      t.mlsa_seg_frames = r->seg_frames;
-      t.mlsa_cut_worst = r->segs.n_seg > 0 && !(dbg && dbg->stop_after_excitation) ? *c->h_worst : 0.0;
-      t.mlsa_fallback = r->used_fallback ? 1 : 0;
-      float f = 0;
-      JB_CUDA(cudaEventElapsedTime(&f, c->ev[0], c->ev[1])); t.h2d_ms = f;
-      cudaEvent_t kend = (r->kernels_end && !r->used_fallback) ? r->kernels_end : c->ev[5];
-      JB_CUDA(cudaEventElapsedTime(&f, c->ev[2], kend)); t.kernels_ms = f;
-      JB_CUDA(cudaEventElapsedTime(&f, c->ev[2], c->ev[3])); t.mlpg_ms = f;
-      JB_CUDA(cudaEventElapsedTime(&f, c->ev[3], c->ev[4])); t.excitation_ms = f;
-      JB_CUDA(cudaEventElapsedTime(&f, c->ev[4], kend)); t.mlsa_ms = f;
-      // with two filter waves the first copy runs under the second launch: this is the tail only
-      JB_CUDA(cudaEventElapsedTime(&f, kend, c->ev[6])); t.d2h_ms = f > 0 ? f : 0;
-      t.h2d_bytes = r->h2d_bytes;
-      t.d2h_bytes = r->total_samples * (int64_t)sample_bytes;
-      t.total_frames = r->total_frames;
-      t.total_samples = r->total_samples;
-      t.voiced_samples = r->voiced_samples;
-      t.launches = r->launches() + (r->used_fallback ? 1 : 0);
+      if (!chunks.empty()) {
+        // span of all kernels (first chunk's start to the last chunk's last kernel), then the copy tail
+        Chunk& a = chunks.front();
+        Chunk& z = chunks.back();
+        cudaEvent_t* eva = c->evsets[a.slot];
+        cudaEvent_t* evz = c->evsets[z.slot];
+        cudaEvent_t kend = (z.r->kernels_end && !z.r->used_fallback) ? z.r->kernels_end : evz[5];
+        float f = 0;
+        JB_CUDA(cudaEventElapsedTime(&f, eva[2], kend)); t.kernels_ms = f;
+        JB_CUDA(cudaEventElapsedTime(&f, kend, evz[6])); t.d2h_ms = f > 0 ? f : 0;
+      }
+      free_chunks();
     } catch (const Error& e) {
+      free_chunks();
       errs[k].reset(new Error(e));
     } catch (const std::exception& e) {
+      free_chunks();
       errs[k].reset(new Error(kErrCuda, e.what()));
     }
   };
@@ -1100,7 +1221,7 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
     }
   if (tm) {
     *tm = BatchTimings();
-    tm->host_frontend_ms = t1 - t0;
+    tm->host_frontend_ms = front_ms;
     for (const auto& t : tms) {
       tm->pack_ms = std::max(tm->pack_ms, t.pack_ms);
       tm->h2d_ms = std::max(tm->h2d_ms, t.h2d_ms);

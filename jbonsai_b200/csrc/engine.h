@@ -76,6 +76,10 @@ class Engine {
   // PCIe transfer earlier but shorten the segments, so the warm-up share of the filter grows:
   // measured e2e for 1024 x 5 s: 1 wave 86 ms, 2: 73, 3: 70.8, 4: 70.3, 6: 78.
   int output_waves = 4;
+  // Sub-batches of one synthesize_batch call on one device (large batches only): the stream-parameter
+  // look-ups of chunk k + 1 run on the host while the GPU works on chunk k, and chunk k's waveform
+  // crosses PCIe under chunk k + 1's kernels. 1 = the whole batch in one pass.
+  int pipeline_chunks = 2;
 
   // Engine::synthesize for a batch: utterance u = lines[line_off[u] .. line_off[u+1]).
   // `out` is a pinned host buffer owned by the engine's pool: release with free_output().
@@ -120,7 +124,8 @@ class Engine {
   mutable std::vector<double> noise_;
   mutable uint64_t rng_next_ = 1;
   const std::vector<double>& noise_table(size_t n) const;
-  std::vector<UtterancePack> build_packs(const std::vector<std::vector<std::string>>& utts) const;
+  std::vector<UtterancePack> build_packs(const std::vector<std::vector<std::string>>& utts, size_t first = 0,
+                                         size_t count = (size_t)-1) const;
   static Resident* make_resident(const Engine& e, DeviceCtx* ctx, const UtterancePack* packs,
                                  size_t n_utt, bool streaming, const Condition& cond, int mlsa_waves = 1);
 };

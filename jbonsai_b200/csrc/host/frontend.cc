@@ -417,6 +417,18 @@ std::vector<StreamTable> build_stream_tables(const VoiceSet& voices) {
   return out;
 }
 
+size_t utterance_frames(const VoiceSet& voices, const Condition& cond, const std::vector<std::string>& lines) {
+  Labels labels = Labels::load_from_strings(cond.sampling_frequency, cond.fperiod, lines);
+  Models models{labels.labels, voices, cond.interporation_weight};
+  std::vector<MeanVari> dur = models.duration();
+  std::vector<size_t> durations = cond.phoneme_alignment_flag
+                                      ? durations_create_with_alignment(dur, models.nstate(), labels.times)
+                                      : durations_create(dur, cond.speed);
+  size_t n = 0;
+  for (size_t d : durations) n += d;
+  return n;
+}
+
 UtterancePack build_utterance(const VoiceSet& voices, const Condition& cond,
                               const std::vector<std::string>& lines,
                               const std::vector<StreamTable>* tables) {

@@ -162,4 +162,8 @@ UtterancePack build_utterance(const VoiceSet& voices, const Condition& cond,
                               const std::vector<std::string>& lines,
                               const std::vector<StreamTable>* tables = nullptr);
 
+// Frames of one utterance: the label and duration part of build_utterance only (one tree walk per
+// label instead of sixteen). Lets a batch lay out its output before the stream parameters exist.
+size_t utterance_frames(const VoiceSet& voices, const Condition& cond, const std::vector<std::string>& lines);
+
 }  // namespace jb

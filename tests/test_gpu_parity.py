@@ -243,6 +243,15 @@ def test_output_waves_equal_single_copy():
     e.set_output_mode(2)
     w2, _ = e.synthesize_batch(utts)
     assert np.array_equal(w2, w0)  # zero-copy stores: same launch, other destination
+    # the same batch as one pass instead of two pipelined sub-batches (front-end of the second under
+    # the kernels of the first): same samples, to rounding of the segment cuts
+    e.set_pipeline_chunks(1)
+    e.set_output_mode(0)
+    tm1 = {}
+    w1, off1 = e.synthesize_batch(utts, tm1)
+    assert tm1["launches"] < tm0["launches"]
+    assert list(off1) == list(off0) and np.abs(w1 - w0).max() <= SCHED_ATOL
+    e.set_pipeline_chunks(2)
     e.set_output_mode(1)
     q, _ = e.synthesize_batch_pcm16(utts)
     assert np.array_equal(q, np.trunc(np.clip(w0, -32768.0, 32767.0)).astype(np.int16))
