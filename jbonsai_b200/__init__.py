@@ -24,7 +24,7 @@ C_ABI_SYMBOLS = [
     "jb_engine_load_from_bytes", "jb_engine_free", "jb_engine_set_condition",
     "jb_engine_get_condition", "jb_engine_set_interpolation_weight", "jb_engine_set_devices",
     "jb_engine_set_mlsa_variant", "jb_engine_set_mlsa_segmenting", "jb_engine_set_device_gather",
-    "jb_engine_set_output_mode", "jb_engine_set_pipeline_chunks", "jb_engine_synthesize", "jb_engine_synthesize_batch", "jb_engine_synthesize_batch_pcm16", "jb_free",
+    "jb_engine_set_output_mode", "jb_engine_set_output_fractions", "jb_engine_set_pipeline_chunks", "jb_engine_synthesize", "jb_engine_synthesize_batch", "jb_engine_synthesize_batch_pcm16", "jb_free",
     "jb_engine_debug_batch", "jb_engine_noise", "jb_engine_durations", "jb_engine_tree_index",
     "jb_engine_stream_parameters", "jb_engine_duration_parameters", "jb_engine_gv_parameters",
     "jb_resident_prepare", "jb_resident_run", "jb_resident_fetch", "jb_resident_free",
@@ -191,8 +191,12 @@ class Engine:
         _check(lib.jb_engine_set_mlsa_segmenting(self._h, int(warm_frames), C.c_double(cut_tolerance)))
 
     def set_output_mode(self, mode: int) -> None:
-        """1 (default): four filter waves, each copied under the next (10 + w: w waves); 2: zero-copy stores; 0: one copy."""
+        """1 (default): three filter waves, each copied under the next (10 + w: w equal waves); 2: zero-copy stores; 0: one copy."""
         _check(lib.jb_engine_set_output_mode(self._h, int(mode)))
+
+    def set_output_fractions(self, fractions: Sequence[float]) -> None:
+        arr = (C.c_double * len(fractions))(*fractions)
+        _check(lib.jb_engine_set_output_fractions(self._h, arr, C.c_size_t(len(fractions))))
 
     def set_pipeline_chunks(self, chunks: int) -> None:
         _check(lib.jb_engine_set_pipeline_chunks(self._h, int(chunks)))

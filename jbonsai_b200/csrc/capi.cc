@@ -162,12 +162,22 @@ int jb_engine_set_output_mode(jb_engine* e, int mode) {
   // mode 1 with another number of filter launches: 10 + waves (e.g. 14 = four waves)
   if (mode >= 11 && mode <= 26) {
     e->e->output_mode = 1;
-    e->e->output_waves = mode - 10;
+    e->e->output_fractions.assign((size_t)(mode - 10), 1.0);  // equal shares
     return JB_OK;
   }
   if (mode < 0 || mode > 2) throw jb::Error(jb::kErrArgument, "output mode must be 0, 1, 2 or 10 + waves");
   e->e->output_mode = mode;
-  if (mode == 1) e->e->output_waves = 4;
+  if (mode == 1) e->e->output_fractions = jb::Engine::default_output_fractions();
+  JB_CATCH
+}
+
+int jb_engine_set_output_fractions(jb_engine* e, const double* fractions, size_t n) {
+  JB_TRY
+  if (n < 1 || n > 16) throw jb::Error(jb::kErrArgument, "1..16 output fractions");
+  for (size_t i = 0; i < n; ++i)
+    if (!(fractions[i] > 0.0)) throw jb::Error(jb::kErrArgument, "output fractions must be positive");
+  e->e->output_mode = 1;
+  e->e->output_fractions.assign(fractions, fractions + n);
   JB_CATCH
 }
 

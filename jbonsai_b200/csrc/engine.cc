@@ -435,7 +435,8 @@ static jbk::WindowSet make_windows(const Windows& w) {
 // Batching layer: pack the state-level parameters of `packs` into one pinned blob, copy it to
 // the device, and lay out every work array of the pipeline in one arena.
 Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const UtterancePack* packs,
-                                        size_t n_utt, bool streaming, const Condition& cond, int mlsa_waves) {
+                                        size_t n_utt, bool streaming, const Condition& cond,
+                                        const std::vector<double>& wave_weights) {
   std::unique_ptr<Engine::Resident> r(new Engine::Resident());
   r->ctx = ctx;
   r->n_utt = (int)n_utt;
@@ -465,23 +466,39 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   // MLSA variant 3: cut every utterance into time segments (kernels.h). The target is enough
   // segments for kSegWarpsPerSmsp warps of six on every warp scheduler; a segment is never shorter
   // than kSegMinFrames of its own, so small batches simply run fewer warps.
-  // With `mlsa_waves` = 2 (Engine::synthesize_batch) the utterances form two groups of about equal
-  // frame count, each cut into its own full wave of segments and filtered by its own launch, so that
-  // the device-to-host copy of the first group overlaps the filter of the second.
+  // With more than one entry in `wave_weights` (Engine::synthesize_batch) the utterances form that many
+  // groups, with frame counts in proportion to the weights; each group is cut into its own full wave of
+  // segments and filtered by its own launch, so that the device-to-host copy of one group overlaps
+  // the filter of the next.
   std::vector<jbk::MlsaSegment> segs;
   r->wave_seg_first.assign(1, 0);
   r->wave_utt_first.assign(1, 0);
   if (!streaming && TF > 0) {
     const int64_t W = e.mlsa_warm_frames;
     const int64_t target = (int64_t)ctx->sm_count * 4 * kSegWarpsPerSmsp * 6;
-    int waves = std::max(1, mlsa_waves);
-    // every wave should still fill the chip with segments of at least kSegMinFrames / 2 own frames
-    while (waves > 1 && TF < (int64_t)waves * target * (kSegMinFrames / 2)) --waves;
+    std::vector<double> ww = wave_weights;
+    if (ww.empty()) ww.assign(1, 1.0);
+    // every wave should still fill the chip with segments of at least kSegMinFrames / 2 own frames:
+    // merge the last two waves until the smallest one does
+    auto smallest = [&]() {
+      double s = 0, m = 1e300;
+      for (double x : ww) s += x;
+      for (double x : ww) m = std::min(m, x / s);
+      return m;
+    };
+    while (ww.size() > 1 && smallest() * (double)TF < (double)(target * (kSegMinFrames / 2))) {
+      ww[ww.size() - 2] += ww.back();
+      ww.pop_back();
+    }
+    const int waves = (int)ww.size();
+    double wsum = 0, wacc = 0;
+    for (double x : ww) wsum += x;
     std::vector<size_t> ucut(waves + 1, n_utt);
     ucut[0] = 0;
     for (int wv = 1; wv < waves; ++wv) {
+      wacc += ww[(size_t)wv - 1];
       size_t u = ucut[wv - 1];
-      while (u < n_utt && r->frame_off[u] < TF * wv / waves) ++u;
+      while (u < n_utt && (double)r->frame_off[u] < (double)TF * (wacc / wsum)) ++u;
       ucut[wv] = u;
     }
     for (int wv = 0; wv < waves; ++wv) {
@@ -884,7 +901,7 @@ Engine::Resident* Engine::prepare(const std::vector<std::vector<std::string>>& u
     throw Error(kErrArgument, "device index out of range");
   DeviceCtx* c = ctx(devices_[(size_t)device_index]);
   std::lock_guard<std::mutex> g(c->mu);
-  return make_resident(*this, c, packs.data(), packs.size(), false, condition);
+  return make_resident(*this, c, packs.data(), packs.size(), false, condition, {});
 }
 
 double Engine::run_resident(Resident* r, BatchTimings* tm) const {
@@ -1067,14 +1084,21 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
       // Two chunks: a small first one (one filter wave's worth of frames), so that the GPU starts
       // after a short front-end and its waveform is crossing PCIe early, then the rest.
       std::vector<size_t> ccut = split(u0, u1, nchunks);
-      std::vector<int> chunk_waves(nchunks, 1);
-      const int waves_total = (!dbg && output_mode == 1 && !pcm16) ? std::max(1, output_waves) : 1;
-      if (nchunks == 2 && waves_total >= 2) {
-        ccut = split(u0, u1, (size_t)waves_total);
-        ccut = {ccut[0], ccut[1], ccut[(size_t)waves_total]};
-        chunk_waves = {1, waves_total - 1};
-      } else {
-        for (auto& w : chunk_waves) w = std::max(1, (waves_total + (int)nchunks - 1) / (int)nchunks);
+      std::vector<std::vector<double>> chunk_waves(nchunks);
+      std::vector<double> fr = (!dbg && output_mode == 1 && !pcm16) ? output_fractions : std::vector<double>{1.0};
+      if (fr.empty()) fr.assign(1, 1.0);
+      if (nchunks == 2 && fr.size() >= 2) {
+        // chunk 0 = the first wave, chunk 1 = all the others
+        double sum = 0;
+        for (double x : fr) sum += x;
+        const size_t s0 = (*out_off)[u0], span = (*out_off)[u1] - s0;
+        size_t u = u0;
+        while (u < u1 && (double)((*out_off)[u] - s0) < (double)span * (fr[0] / sum)) ++u;
+        ccut = {u0, u, u1};
+        chunk_waves[0] = {1.0};
+        chunk_waves[1].assign(fr.begin() + 1, fr.end());
+      } else if (nchunks == 1) {
+        chunk_waves[0] = fr;
       }
 
       auto copy_result = [&](Chunk& ch) {  // whole result of a chunk on the main stream, f64 or PCM
@@ -1251,7 +1275,7 @@ Stream::Stream(const Engine* e, const std::vector<std::vector<std::string>>& utt
   std::vector<UtterancePack> packs = e->build_packs(utts);
   DeviceCtx* c = e->ctx(device);
   std::lock_guard<std::mutex> g(c->mu);
-  r_ = Engine::make_resident(*e, c, packs.data(), packs.size(), true, e->condition);
+  r_ = Engine::make_resident(*e, c, packs.data(), packs.size(), true, e->condition, {});
   // MLPG for the whole utterance up front, like Engine::generator (engine.rs:333-357)
   launch_mlpg_all(r_, false);
   if (r_->n_utt)

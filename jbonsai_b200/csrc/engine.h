@@ -72,10 +72,14 @@ class Engine {
   // straight into the pinned output buffer (zero-copy; measured slower: SM stores reach ~34 GB/s
   // over PCIe against ~52 GB/s for the copy engine).
   int output_mode = 1;
-  // Filter launches per batch in output mode 1 (fewer when the batch is small). More waves start the
-  // PCIe transfer earlier but shorten the segments, so the warm-up share of the filter grows:
-  // measured e2e for 1024 x 5 s: 1 wave 86 ms, 2: 73, 3: 70.8, 4: 70.3, 6: 78.
-  int output_waves = 4;
+  // Output mode 1: shares of the batch (by frames) filtered by successive launches; fewer when the
+  // batch is small. More waves start the PCIe transfer earlier but shorten the segments, so the
+  // warm-up share of the filter grows (measured e2e for 1024 x 5 s with equal waves: 1 wave 86 ms,
+  // 2: 73, 3: 70.8, 4: 70.3, 6: 78). A filter launch over a share f costs ~(18.3 f + 5) ms and its copy
+  // 38 f ms on a B200 behind PCIe 5: a mid-sized first wave, a large second one and a small last one
+  // (whose copy nothing hides) finish earliest.
+  static std::vector<double> default_output_fractions() { return {0.35, 0.40, 0.25}; }
+  std::vector<double> output_fractions = default_output_fractions();
   // Sub-batches of one synthesize_batch call on one device (large batches only): the stream-parameter
   // look-ups of chunk k + 1 run on the host while the GPU works on chunk k, and chunk k's waveform
   // crosses PCIe under chunk k + 1's kernels. 1 = the whole batch in one pass.
@@ -127,7 +131,8 @@ class Engine {
   std::vector<UtterancePack> build_packs(const std::vector<std::vector<std::string>>& utts, size_t first = 0,
                                          size_t count = (size_t)-1) const;
   static Resident* make_resident(const Engine& e, DeviceCtx* ctx, const UtterancePack* packs,
-                                 size_t n_utt, bool streaming, const Condition& cond, int mlsa_waves = 1);
+                                 size_t n_utt, bool streaming, const Condition& cond,
+                                 const std::vector<double>& wave_weights);
 };
 
 // SpeechGenerator (src/speech.rs) for many utterances at once: MLPG up front, then the
