@@ -84,7 +84,8 @@ struct WarpShared {
 
 template <int WPB>
 __global__ void __launch_bounds__(32 * WPB, 2)
-k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg_first, int seg_end) {
+k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg_first, int seg_end,
+          const double iaa) {
   __shared__ __align__(16) WarpShared sh[WPB];
 
   const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -123,7 +124,7 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
   const int g5 = 5 * g;
   const int prev_lane = s > 0 ? g5 + s - 1 : g5;
   const bool head = lane < 30 && s == 0;
-  const double a = p.alpha, ma = -a, iaa = 1.0 - a * a;
+  const double a = p.alpha, ma = -a;  // iaa = 1 - a^2 is a kernel parameter (see the launcher)
   const double pp1 = c_pp3[1], pp2 = c_pp3[2], pp3 = c_pp3[3], pp4 = c_pp3[4], pp5 = c_pp3[5];
   const double fper = (double)fp;
   const SlotInfo me = info[g];
@@ -315,8 +316,11 @@ int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDe
       seg_first + seg_count > sg.n_seg)
     return (int)cudaErrorInvalidValue;
   const int warps = (seg_count + kSlots - 1) / kSlots;
+  // 1 - alpha^2 as a parameter: derived in the kernel it was re-computed from the constant bank at the
+  // top of every sample (254 registers leave no room to keep it): a load and two dependent FP64
+  // operations on the serial path of the filter
   k_mlsa_v3<kWPB><<<(warps + kWPB - 1) / kWPB, 32 * kWPB, 0, stream>>>(b, p, d, sg, seg_first,
-                                                                        seg_first + seg_count);
+                                                                        seg_first + seg_count, 1.0 - p.alpha * p.alpha);
   return (int)cudaGetLastError();
 }
 
