@@ -155,7 +155,7 @@ def ncu_traffic_bytes():
     try:
         tot = 0.0
         for line in open(os.path.join(ROOT, "profiles", "r1_mlsa_v3_full_summary.txt")):
-            if line.startswith("dram__bytes_read.sum") or line.startswith("dram__bytes_write.sum"):
+            if line.startswith("dram__bytes_read.sum [") or line.startswith("dram__bytes_write.sum ["):
                 unit = line.split("[")[1].split("]")[0]
                 val = float(line.split("=")[1])
                 tot += val * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}[unit]
