@@ -145,6 +145,36 @@ int jb_engine_gv_parameters(const jb_engine* e, const char* const* lines, size_t
 typedef struct jb_resident jb_resident;
 int jb_resident_prepare(const jb_engine* e, const char* const* lines, const size_t* line_off,
                         size_t n_utt, int device_index, jb_resident** out);
+/* The vocoder seam below the engine: Vocoder::new(nmcp, nlpf, stage, use_log_gain, rate, alpha, beta,
+ * volume, fperiod) (src/vocoder/mod.rs:45-70) driven over whole parameter tracks as
+ * SpeechGenerator::new(fperiod, vocoder, spectrum, lf0, lpf).generate_all() does (src/speech.rs:25-96),
+ * for n_utt independent utterances at once. frame_off[n_utt + 1] (frames, ascending from 0);
+ * spectrum[frames][nmcp] = mel-cepstrum rows, or line spectral pairs with the gain in column 0 when
+ * stage > 0 (Stage::NonZero, vocoder/mod.rs:142-176: MGLSA filter of `stage` sections, gamma = -1/stage);
+ * lf0[frames] with -1e10 (NODATA) in unvoiced frames; lpf[frames][nlpf]. nlpf == 0 drives the
+ * vocoder without LPF stream (excitation.rs:87-99; lpf may be NULL). An even nlpf > 0 is the
+ * reference's panic (speech.rs:38-40) and returns JB_ERR_ARGUMENT. */
+typedef struct jb_vocoder_config {
+  size_t nmcp, nlpf, stage;
+  int use_log_gain;
+  size_t rate;
+  double alpha, beta, volume;
+  size_t fperiod;
+  int coefficient_rows; /* test seam, normally 0. 1: `spectrum` holds filter coefficient rows instead,
+                           [frames][nmcp] followed by the [n_utt][nmcp] rows the first frames start from
+                           (the `coefficients` of vocoder/mod.rs:79-109); the spectrum transform is skipped */
+} jb_vocoder_config;
+/* One call: host tracks in, waveform out (library-owned buffer, jb_free; out_off[n_utt + 1] optional). */
+int jb_engine_vocoder_synthesize(const jb_engine* e, const jb_vocoder_config* cfg, size_t n_utt,
+                                 const size_t* frame_off, const double* spectrum, const double* lf0,
+                                 const double* lpf, double** out, size_t* out_off);
+/* The same as a resident batch for jb_resident_run / _fetch / _free (run() skips MLPG). */
+int jb_resident_prepare_tracks(const jb_engine* e, const jb_vocoder_config* cfg, size_t n_utt, const size_t* frame_off,
+                               const double* spectrum, const double* lf0, const double* lpf, int device_index,
+                               jb_resident** out);
+/* After jb_resident_run: the per-frame filter coefficient rows the run used, [frames][nmcp], then the
+ * [n_utt][nmcp] rows the first frames started from (cap = doubles available in out). */
+int jb_resident_rows(const jb_engine* e, jb_resident* r, double* out, size_t cap);
 /* Runs MLPG + vocoder kernels; device time in ms by CUDA events; timings as above (optional). */
 int jb_resident_run(const jb_engine* e, jb_resident* r, double* device_ms, double* timings);
 int jb_resident_fetch(const jb_engine* e, jb_resident* r, double** out, size_t* out_off);

@@ -27,7 +27,7 @@ C_ABI_SYMBOLS = [
     "jb_engine_set_output_mode", "jb_engine_set_output_fractions", "jb_engine_set_pipeline_chunks", "jb_engine_synthesize", "jb_engine_synthesize_batch", "jb_engine_synthesize_batch_pcm16", "jb_free",
     "jb_engine_debug_batch", "jb_engine_noise", "jb_engine_durations", "jb_engine_tree_index",
     "jb_engine_stream_parameters", "jb_engine_duration_parameters", "jb_engine_gv_parameters",
-    "jb_resident_prepare", "jb_resident_run", "jb_resident_fetch", "jb_resident_free",
+    "jb_resident_prepare", "jb_resident_prepare_tracks", "jb_resident_rows", "jb_engine_vocoder_synthesize", "jb_resident_run", "jb_resident_fetch", "jb_resident_free",
     "jb_stream_open", "jb_stream_fperiod", "jb_stream_synthesized_frames", "jb_stream_step",
     "jb_stream_close",
 ]
@@ -38,6 +38,13 @@ STATUS_NAMES = {
     -9: "LengthMismatch", -10: "WeightError", -11: "IndexNotFound", -12: "Argument",
     -13: "Cuda", -14: "Unsupported",
 }
+
+
+class VocoderConfig(C.Structure):
+    """jb_vocoder_config: the arguments of Vocoder::new (src/vocoder/mod.rs:45-70)."""
+    _fields_ = [("nmcp", C.c_size_t), ("nlpf", C.c_size_t), ("stage", C.c_size_t), ("use_log_gain", C.c_int),
+                ("rate", C.c_size_t), ("alpha", C.c_double), ("beta", C.c_double), ("volume", C.c_double),
+                ("fperiod", C.c_size_t), ("coefficient_rows", C.c_int)]
 
 
 class JbError(RuntimeError):
@@ -336,6 +343,59 @@ class Engine:
         _check(lib.jb_resident_prepare(self._h, arr, offs, C.c_size_t(n), int(device_index), C.byref(r)))
         return Resident(self, r, n)
 
+    # -- the vocoder seam: Vocoder::new + SpeechGenerator::generate_all over parameter tracks
+    @staticmethod
+    def _tracks(spectrum, lf0, lpf, stage, use_log_gain, rate, alpha, beta, volume, fperiod, first_rows=None):
+        """-> (config struct, n_utt, frame_off array, the three concatenated tracks)."""
+        if isinstance(spectrum, np.ndarray) and spectrum.ndim == 2:
+            spectrum, lf0, lpf = [spectrum], [lf0], [lpf]
+        spec = [np.ascontiguousarray(s, dtype=np.float64) for s in spectrum]
+        nmcp = spec[0].shape[1] if spec else 0
+        lf = [np.ascontiguousarray(x, dtype=np.float64).reshape(-1) for x in lf0]
+        lp = [np.ascontiguousarray(x, dtype=np.float64) for x in lpf]
+        nlpf = max([x.shape[1] for x in lp if x.ndim == 2] + [0])
+        lp = [x.reshape(len(s), nlpf) for x, s in zip(lp, spec)]
+        for s, a, b in zip(spec, lf, lp):
+            if len(a) != len(s) or len(b) != len(s):  # speech.rs:32-34
+                raise ValueError("The length of spectrum, lf0, and lpf must be the same.")
+        off = np.zeros(len(spec) + 1, dtype=np.uint64)
+        off[1:] = np.cumsum([len(s) for s in spec])
+        cat = lambda xs, w: np.ascontiguousarray(np.concatenate(xs).reshape(-1)) if xs and w else np.zeros(1)
+        cfg = VocoderConfig(nmcp, nlpf, int(stage), int(bool(use_log_gain)), int(rate), float(alpha), float(beta),
+                            float(volume), int(fperiod), int(first_rows is not None))
+        if first_rows is not None:  # test seam: spectrum = coefficient rows, then the first rows
+            spec = spec + [np.ascontiguousarray(first_rows, dtype=np.float64).reshape(len(spec), nmcp)]
+        return cfg, len(lf), off, cat(spec, nmcp), cat(lf, 1), cat(lp, nlpf)
+
+    def vocoder_synthesize(self, spectrum, lf0, lpf, stage=0, use_log_gain=False, rate=48000, alpha=0.55,
+                           beta=0.0, volume=1.0, fperiod=240):
+        """``SpeechGenerator::new(fperiod, Vocoder::new(...), spectrum, lf0, lpf).generate_all()``
+        (src/speech.rs:25-96, src/vocoder/mod.rs:45-70) for one track set ([T, nmcp], [T], [T, nlpf]) or a
+        list of them; ``stage > 0`` takes LSP frames. Returns one waveform or a list of waveforms."""
+        single = isinstance(spectrum, np.ndarray) and spectrum.ndim == 2
+        cfg, n, off, sp, lf, lp = self._tracks(spectrum, lf0, lpf, stage, use_log_gain, rate, alpha, beta, volume, fperiod)
+        D = C.POINTER(C.c_double)
+        out = D()
+        out_off = (C.c_size_t * (n + 1))()
+        _check(lib.jb_engine_vocoder_synthesize(self._h, C.byref(cfg), C.c_size_t(n),
+                                                off.ctypes.data_as(C.POINTER(C.c_size_t)), sp.ctypes.data_as(D),
+                                                lf.ctypes.data_as(D), lp.ctypes.data_as(D), C.byref(out), out_off))
+        o = list(out_off)
+        w = _take(out, int(o[-1]))
+        waves = [w[o[i]:o[i + 1]] for i in range(n)]
+        return waves[0] if single else waves
+
+    def prepare_tracks(self, spectrum, lf0, lpf, device_index: int = 0, **kw) -> "Resident":
+        k = dict(stage=0, use_log_gain=False, rate=48000, alpha=0.55, beta=0.0, volume=1.0, fperiod=240, first_rows=None)
+        k.update(kw)
+        cfg, n, off, sp, lf, lp = self._tracks(spectrum, lf0, lpf, **k)
+        D = C.POINTER(C.c_double)
+        r = C.c_void_p()
+        _check(lib.jb_resident_prepare_tracks(self._h, C.byref(cfg), C.c_size_t(n),
+                                              off.ctypes.data_as(C.POINTER(C.c_size_t)), sp.ctypes.data_as(D),
+                                              lf.ctypes.data_as(D), lp.ctypes.data_as(D), int(device_index), C.byref(r)))
+        return Resident(self, r, n)
+
     # -- Engine::generator (src/engine.rs:301-366), batched
     def generator(self, utts: Sequence[Sequence[str]], device: int = 0) -> "SpeechGenerator":
         if utts and isinstance(utts[0], str):
@@ -357,6 +417,12 @@ class Resident:
         d = {k: tm[i] for i, k in enumerate(TIMING_KEYS)}
         d["device_ms"] = ms.value
         return d
+
+    def rows(self, frames: int, nmcp: int):
+        """Filter coefficient rows of the last run: ([frames, nmcp], [n_utt, nmcp] first rows)."""
+        buf = np.zeros((frames + self.n_utt) * nmcp)
+        _check(lib.jb_resident_rows(self._e._h, self._h, buf.ctypes.data_as(C.POINTER(C.c_double)), C.c_size_t(buf.size)))
+        return buf[:frames * nmcp].reshape(frames, nmcp), buf[frames * nmcp:].reshape(self.n_utt, nmcp)
 
     def fetch(self):
         out = C.POINTER(C.c_double)()

@@ -360,6 +360,56 @@ int jb_resident_prepare(const jb_engine* e, const char* const* lines, const size
   JB_CATCH
 }
 
+static jb::Engine::VocoderConfig to_cfg(const jb_vocoder_config* c) {
+  if (!c) throw jb::Error(jb::kErrArgument, "null vocoder config");
+  jb::Engine::VocoderConfig v;
+  v.nmcp = c->nmcp;
+  v.nlpf = c->nlpf;
+  v.stage = c->stage;
+  v.use_log_gain = c->use_log_gain != 0;
+  v.rate = c->rate;
+  v.alpha = c->alpha;
+  v.beta = c->beta;
+  v.volume = c->volume;
+  v.fperiod = c->fperiod;
+  v.coefficient_rows = c->coefficient_rows != 0;
+  return v;
+}
+
+int jb_resident_prepare_tracks(const jb_engine* e, const jb_vocoder_config* cfg, size_t n_utt, const size_t* frame_off,
+                               const double* spectrum, const double* lf0, const double* lpf, int device_index,
+                               jb_resident** out) {
+  JB_TRY
+  *out = new jb_resident{e->e, e->e->prepare_tracks(to_cfg(cfg), n_utt, frame_off, spectrum, lf0, lpf, device_index)};
+  JB_CATCH
+}
+
+int jb_engine_vocoder_synthesize(const jb_engine* e, const jb_vocoder_config* cfg, size_t n_utt,
+                                 const size_t* frame_off, const double* spectrum, const double* lf0,
+                                 const double* lpf, double** out, size_t* out_off) {
+  JB_TRY
+  jb::Engine::Resident* r = e->e->prepare_tracks(to_cfg(cfg), n_utt, frame_off, spectrum, lf0, lpf, 0);
+  try {
+    e->e->run_resident(r, nullptr);
+    std::vector<size_t> off;
+    e->e->fetch_resident(r, out, &off);
+    if (out_off) memcpy(out_off, off.data(), off.size() * sizeof(size_t));
+  } catch (...) {
+    e->e->release(r);
+    throw;
+  }
+  e->e->release(r);
+  JB_CATCH
+}
+
+int jb_resident_rows(const jb_engine* e, jb_resident* r, double* out, size_t cap) {
+  JB_TRY
+  std::vector<double> v = r->e->resident_rows(r->r);
+  if (v.size() > cap) throw jb::Error(jb::kErrArgument, "jb_resident_rows: buffer too small");
+  if (!v.empty()) memcpy(out, v.data(), v.size() * sizeof(double));
+  JB_CATCH
+}
+
 int jb_resident_run(const jb_engine* e, jb_resident* r, double* device_ms, double* timings) {
   JB_TRY
   jb::BatchTimings tm;

@@ -108,6 +108,9 @@ struct VocoderParams {
   double rate;  // 48000
   double alpha;
   double volume;
+  int stage = 0;         // 0: mel-cepstrum in, MLSA filter; n > 0: line spectral pairs in, MGLSA filter of n
+                         // sections, gamma = -1/n (stage.rs:28-38)
+  int use_log_gain = 0;  // stage > 0: the gain slot holds ln(gain) (lsp.rs:92-96)
 };
 
 // Per-utterance vocoder state carried between chunked launches (streaming, speech.rs:65-83).
@@ -129,6 +132,8 @@ struct VocoderDev {
   const double* b_first;  // [n_utt][nmcp] or nullptr. beta > 0 only: mc2b of the un-filtered first frame, the
                           // coefficients the reference starts from (is_first, vocoder/mod.rs:79-88); nullptr =
                           // row 0 of `b` (identical when beta == 0)
+  double* binc;         // stage != 0 only: [total_frames][nmcp] per-sample coefficient increments of every frame
+                        // (launch_row_increments), else nullptr
   double* pitch;        // [total_frames]        p per frame (out of frame_prep)
   double* pulse;        // [total_samples]       pulse amplitude or 0 (out of pitch kernel)
   int32_t* runs;        // [1 + total_frames]    work: number of voiced runs, then their first frames
@@ -176,7 +181,27 @@ int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDe
 // After every wave has run: the largest state mismatch over all cuts -> *worst (device), for the
 // host to compare with its tolerance.
 // `host_mirror` (pinned, device-visible, or nullptr): also stored there by the device, no copy engine.
-int launch_mlsa_seg_check(const MlsaSegments& sg, double* worst, double* host_mirror, cudaStream_t stream);
+// `stride` / `count`: doubles per (segment, side) slot and how many of them are compared.
+int launch_mlsa_seg_check(const MlsaSegments& sg, double* worst, double* host_mirror, cudaStream_t stream,
+                          int stride = kMlsaSegStateDoubles, int count = 5 * 37);
+
+// Stage != 0 (mglsa.cu). launch_lsp_prep: rows of d.b = filter coefficients of every LSP frame of d.mcp
+// (postfilter_lsp(beta), check_lsp_stability, lsp2mgc, mc2b, gnorm, [1..] *= gamma; vocoder/mod.rs:148-155)
+// and b_first[n_utt][nmcp] = the same transform of every first frame without post-filter and stability
+// check (mod.rs:92-107). nmcp <= 64.
+int launch_lsp_prep(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, double beta, double* b_first,
+                    int64_t total_frames, cudaStream_t stream);
+// MGLSA filter (mglsa.rs:15-41) over time segments like launch_mlsa_v3: d.wave (excitation times
+// coefficients[0]) -> d.out. 32 / stage segments share a warp. nmcp <= kMglsaMaxOrder, stage <= 8,
+// fperiod % 16 == 0. Cut-check state: mglsa_state_doubles(stage) doubles per (segment, side).
+// After the rows of d.b / d.b_first are final: d.binc[f][k] = (b[f][k] - row before)[k] / fperiod (vocoder/mod.rs:156-160).
+int launch_row_increments(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, int64_t total_frames,
+                          cudaStream_t stream);
+constexpr int kMglsaMaxOrder = 36;
+constexpr int kMglsaMaxStage = 8;
+constexpr int mglsa_state_doubles(int stage) { return stage * kMglsaMaxOrder; }
+int launch_mglsa(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, const MlsaSegments& sg,
+                 int seg_first, int seg_count, cudaStream_t stream);
 
 // Streaming: copy frames [frame_begin, frame_begin+frame_count) of every utterance into
 // chunk[n_utt][frame_count*fperiod] (zero padded past the end of an utterance).

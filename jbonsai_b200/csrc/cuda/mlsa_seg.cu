@@ -21,10 +21,10 @@
 // its stage in registers and runs the tap recurrence serially in the "q form"
 //   t'_1 = (1-a^2) u + a t_1 ;  t'_j = (t_{j-1} + a t_j) - a t'_{j-1}   (== iaa*rem + a*d of mlsa.rs:141-153)
 // with two dot-product accumulators like the reference (y0/y1). No scan, no carry exchange: three
-// FMAs per tap, which is the arithmetic floor of the recurrence. The 35 interpolated coefficients
-// of a segment live in shared memory (double-buffered by sample parity) and are advanced by the
-// whole warp, 7 values per lane, so that the c += cinc additions (mod.rs:133-135) are not repeated
-// by each of the five stage lanes. One shared-memory exchange per sample carries the five stage
+// FMAs per tap, which is the arithmetic floor of the recurrence. Every lane also keeps the 34
+// interpolated coefficients of its segment and their per-sample increments in registers and
+// advances them itself (mod.rs:133-135): sharing them through shared memory cost more issue slots
+// than the repeated additions. One shared-memory exchange per sample carries the five stage
 // outputs and the five df1 outputs to the lanes of the segment; the Pade combine
 // (d[0] = (x + A) - B, x' = x + 2A with A/B the odd/even weighted sums; mlsa.rs:54-79) is done
 // redundantly by each lane.
@@ -282,14 +282,14 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
 
 // Compares the two sides of every cut: state of segment g at the top of its own range (after its
 // warm-up from zero) against the end state of the segment before it. max |difference| -> *worst.
-__global__ void k_mlsa_seg_check(MlsaSegments sg, double* worst) {
+__global__ void k_mlsa_seg_check(MlsaSegments sg, double* worst, int stride, int count) {
   const int sid = blockIdx.x;
   const MlsaSegment s = sg.seg[sid];
   if (s.prev < 0) return;
-  const double* A = sg.state + ((long long)sid * 2 + 0) * kMlsaSegStateDoubles;
-  const double* B = sg.state + ((long long)s.prev * 2 + 1) * kMlsaSegStateDoubles;
+  const double* A = sg.state + ((long long)sid * 2 + 0) * stride;
+  const double* B = sg.state + ((long long)s.prev * 2 + 1) * stride;
   double m = 0.0;
-  for (int i = threadIdx.x; i < 5 * 37; i += blockDim.x) {
+  for (int i = threadIdx.x; i < count; i += blockDim.x) {
     const double dd = fabs(A[i] - B[i]);
     m = (dd > m || dd != dd) ? (dd != dd ? __longlong_as_double(0x7ff0000000000000ll) : dd) : m;
   }
@@ -324,11 +324,12 @@ int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDe
   return (int)cudaGetLastError();
 }
 
-int launch_mlsa_seg_check(const MlsaSegments& sg, double* worst, double* host_mirror, cudaStream_t stream) {
+int launch_mlsa_seg_check(const MlsaSegments& sg, double* worst, double* host_mirror, cudaStream_t stream,
+                          int stride, int count) {
   if (sg.n_seg == 0 || worst == nullptr || sg.state == nullptr) return 0;
   cudaError_t e = cudaMemsetAsync(worst, 0, sizeof(double), stream);
   if (e != cudaSuccess) return (int)e;
-  k_mlsa_seg_check<<<sg.n_seg, 64, 0, stream>>>(sg, worst);
+  k_mlsa_seg_check<<<sg.n_seg, 64, 0, stream>>>(sg, worst, stride, count);
   if (host_mirror) k_publish<<<1, 1, 0, stream>>>(worst, host_mirror);
   return (int)cudaGetLastError();
 }

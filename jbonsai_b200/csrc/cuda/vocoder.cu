@@ -224,6 +224,16 @@ __global__ void __launch_bounds__(256) k_excitation(BatchLayout b, VocoderParams
   const bool voiced_prev = f > 0 && d.pitch[gf - 1] != 0.0;
   const double* pulse = d.pulse + foff * fp + n0 - hist;
   const double* noise = d.noise + n0 - hist;
+  if (nl == 0 && !voiced_cur) {
+    // no LPF stream (excitation.rs:87-99): noise is drawn on unvoiced samples only, so this frame
+    // reads the sequence at fperiod * (unvoiced frames before it)
+    int before = 0;
+    for (int j0 = 0; j0 < f; j0 += blockDim.x) {
+      const int j = j0 + threadIdx.x;
+      before += __syncthreads_count(j < f && d.pitch[foff + j] == 0.0);
+    }
+    noise = d.noise + (int64_t)before * fp;
+  }
 
   for (int i = threadIdx.x; i < fp + hist; i += blockDim.x) {
     const bool in = n0 - hist + i >= 0;
@@ -266,7 +276,8 @@ __global__ void __launch_bounds__(256) k_excitation(BatchLayout b, VocoderParams
     } else {
       x = voiced_cur ? s_diff[i] : s_noise[i];
     }
-    if (x != 0.0) x *= exp(s_c0[i]);
+    if (p.stage != 0) x *= s_c0[i];  // Stage::NonZero gain (mod.rs:163)
+    else if (x != 0.0) x *= exp(s_c0[i]);
     wave[i] = x;
   }
 }
@@ -354,7 +365,8 @@ __global__ void __launch_bounds__(32 * kExWarps) k_excitation_w(BatchLayout b, V
 #pragma unroll
   for (int r = 0; r < R; ++r) {
     double v = x[r];
-    if (v != 0.0) v *= exp(s_c0[w][i0 + r]);  // mod.rs:129-131
+    if (p.stage != 0) v *= s_c0[w][i0 + r];  // Stage::NonZero gain (mod.rs:163)
+    else if (v != 0.0) v *= exp(s_c0[w][i0 + r]);  // mod.rs:129-131
     wave[r] = v;
   }
 }

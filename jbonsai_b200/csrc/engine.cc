@@ -30,6 +30,8 @@ namespace jb {
 namespace {
 
 constexpr int kSegWarpsPerSmsp = 2;  // resident warps per scheduler of k_mlsa_v3 (206 registers)
+constexpr int kMglsaWarmFactor = 2;  // stage != 0: the all-pole MGLSA filter of an LSP frame forgets more slowly than the
+                                     // MLSA filter (synthetic tracks: 40 frames leave 1e0, 80 frames 1e-12 at the cuts)
 constexpr int kSegMinFrames = 48;    // shortest own range worth a segment of its own
 
 double now_ms() {
@@ -336,8 +338,12 @@ std::vector<UtterancePack> Engine::build_packs(const std::vector<std::vector<std
     size_t size() const { return n; }
     const std::vector<std::string>& operator[](size_t i) const { return p[i]; }
   } utts{all.data() + first, count};
-  if (condition.stage != 0)
-    throw Error(kErrUnsupported, "stage != 0 (GAMMA option: LSP/MGLSA vocoder) is not built yet");
+  if (condition.stage > (size_t)jbk::kMglsaMaxStage)
+    throw Error(kErrUnsupported, "stage (GAMMA option) > 8");
+  if (condition.stage != 0 && voices_.stream_metadata(0).vector_length > (size_t)jbk::kMglsaMaxOrder)
+    throw Error(kErrUnsupported, "stage != 0 with a spectrum vector longer than 36");
+  if (condition.stage == 0 && voices_.stream_metadata(0).vector_length != 35)
+    throw Error(kErrUnsupported, "the MLSA kernels are built for 35 mel-cepstral coefficients");
   if (voices_.global_metadata().num_streams < 3 || voices_.stream_metadata(2).vector_length == 0)
     throw Error(kErrUnsupported, "voices without an LPF stream are not built yet");
   std::vector<UtterancePack> packs(utts.size());
@@ -396,6 +402,10 @@ struct Engine::Resident {
   bool gathered[3] = {false, false, false};
   // MLSA variant 3: time segments (empty when the batch is streamed)
   jbk::MlsaSegments segs{};
+  bool rows_given = false;         // prepare_tracks with coefficient_rows: vd.mcp holds the rows to copy into vd.b
+  bool from_tracks = false;        // built by prepare_tracks: no MLPG inputs, run() starts at the vocoder
+  jbk::MlsaSegments whole{};       // stage != 0: one segment per utterance (no cuts), for the repeat pass
+  double lsp_beta = 0.0;           // stage != 0: beta of postfilter_lsp
   double* d_worst = nullptr;
   int64_t seg_frames = 0;          // frames filtered including warm-up
   std::vector<int32_t> wave_seg_first;  // [waves+1] segment range of every filter launch
@@ -409,6 +419,9 @@ struct Engine::Resident {
   // kernels per pass: expand, 3 solves (+ GV kernels), 2 frame preps, pulse (memset excluded),
   // excitation, MLSA (+ cut check for variant 3)
   int launches() const {
+    if (from_tracks)
+      return 2 + (rows_given ? 0 : 1) + (vp.stage != 0 ? 1 : 0) + 2 + (segs.n_seg > 0 ? (int)wave_seg_first.size() : 1) +
+             (beta > 0.0 ? 2 : 0);
     int n = 1 + 3 + 2 + 4 + (segs.n_seg > 0 ? (int)wave_seg_first.size() - 1 : 0) + (beta > 0.0 ? 2 : 0);
     for (int i = 0; i < 3; ++i) n += gathered[i] ? 1 : 0;
     for (int i = 0; i < streams.n; ++i) n += streams.s[i].has_gv ? 1 : 0;
@@ -430,6 +443,109 @@ static jbk::WindowSet make_windows(const Windows& w) {
     for (size_t k = 0; k < w.windows[i].width(); ++k) ws.coef[i][k] = w.windows[i].coefficients[k];
   }
   return ws;
+}
+
+// Time segments of the filter kernels (MLSA variant 3, MGLSA): what make_resident uploads.
+struct SegmentPlan {
+  std::vector<jbk::MlsaSegment> segs;
+  std::vector<int32_t> wave_seg_first, wave_utt_first;  // [waves + 1]
+  int64_t seg_frames = 0;                               // frames filtered including warm-up
+};
+
+// Cuts every utterance into segments with W warm-up frames; `target` = how many segments fill the chip
+// once (warps per scheduler x segments per warp x schedulers).
+static SegmentPlan cut_segments(const std::vector<int64_t>& frame_off, size_t n_utt, int64_t W, int64_t target,
+                                const std::vector<double>& wave_weights) {
+  SegmentPlan pl;
+  std::vector<jbk::MlsaSegment>& segs = pl.segs;
+  pl.wave_seg_first.assign(1, 0);
+  pl.wave_utt_first.assign(1, 0);
+  const int64_t TF = frame_off[n_utt];
+  if (TF > 0) {
+    std::vector<double> ww = wave_weights;
+    if (ww.empty()) ww.assign(1, 1.0);
+    // every wave should still fill the chip with segments of at least kSegMinFrames / 2 own frames:
+    // merge the last two waves until the smallest one does
+    auto smallest = [&]() {
+      double s = 0, m = 1e300;
+      for (double x : ww) s += x;
+      for (double x : ww) m = std::min(m, x / s);
+      return m;
+    };
+    while (ww.size() > 1 && smallest() * (double)TF < (double)(target * (kSegMinFrames / 2))) {
+      ww[ww.size() - 2] += ww.back();
+      ww.pop_back();
+    }
+    const int waves = (int)ww.size();
+    double wsum = 0, wacc = 0;
+    for (double x : ww) wsum += x;
+    std::vector<size_t> ucut(waves + 1, n_utt);
+    ucut[0] = 0;
+    for (int wv = 1; wv < waves; ++wv) {
+      wacc += ww[(size_t)wv - 1];
+      size_t u = ucut[wv - 1];
+      while (u < n_utt && (double)frame_off[u] < (double)TF * (wacc / wsum)) ++u;
+      ucut[wv] = u;
+    }
+    for (int wv = 0; wv < waves; ++wv) {
+      const size_t ua = ucut[wv], ub = ucut[wv + 1];
+      const int64_t TFw = frame_off[ub] - frame_off[ua];
+      if (TFw <= 0) continue;
+      std::vector<jbk::MlsaSegment> ws;
+      auto cut = [&](int64_t S) {
+        ws.clear();
+        for (size_t u = ua; u < ub; ++u) {
+          const int64_t T = frame_off[u + 1] - frame_off[u];
+          if (T <= 0) continue;
+          int64_t G = std::max<int64_t>(1, (T + S / 2) / S);
+          // equal filtered length L for every segment: the first owns L frames, the others L - W
+          while (G > 1 && (T + (G - 1) * W) / G - W < kSegMinFrames / 2) --G;
+          const int64_t L = (T + (G - 1) * W + G - 1) / G;
+          int64_t begin = 0;
+          for (int64_t k = 0; k < G && begin < T; ++k) {
+            int64_t end = (k == G - 1) ? T : std::min<int64_t>(T, begin + (k == 0 ? L : L - W));
+            jbk::MlsaSegment sg;
+            sg.utt = (int32_t)u;
+            sg.begin = (int32_t)begin;
+            sg.end = (int32_t)end;
+            sg.warm = (int32_t)std::max<int64_t>(0, begin - W);
+            sg.prev = k == 0 ? -1 : (int32_t)(ws.size() - 1);  // index before sorting, remapped below
+            ws.push_back(sg);
+            begin = end;
+          }
+        }
+      };
+      int64_t S = std::max<int64_t>(waves > 1 ? kSegMinFrames / 2 : kSegMinFrames, (TFw + target - 1) / target);
+      cut(S);
+      // One wave: all segments run about equally long, so a grid slightly larger than the chip holds
+      // (target segments) would leave a second, nearly empty wave as long as the first.
+      for (int it = 0; it < 64 && (int64_t)ws.size() > target && (int64_t)ws.size() < 2 * target; ++it) {
+        S += std::max<int64_t>(1, S / 50);
+        cut(S);
+      }
+      // six consecutive segments share a warp and run as long as the longest of them
+      std::vector<int32_t> perm(ws.size()), where(ws.size());
+      for (size_t i = 0; i < ws.size(); ++i) perm[i] = (int32_t)i;
+      std::stable_sort(perm.begin(), perm.end(), [&](int32_t x, int32_t y) {
+        return ws[x].end - ws[x].warm > ws[y].end - ws[y].warm;
+      });
+      for (size_t i = 0; i < perm.size(); ++i) where[perm[i]] = (int32_t)i;
+      const int32_t base = (int32_t)segs.size();
+      if (wv > 0) {
+        pl.wave_seg_first.push_back(base);
+        pl.wave_utt_first.push_back((int32_t)ua);
+      }
+      for (size_t i = 0; i < perm.size(); ++i) {
+        jbk::MlsaSegment sg = ws[perm[i]];
+        if (sg.prev >= 0) sg.prev = base + where[sg.prev];
+        pl.seg_frames += sg.end - sg.warm;
+        segs.push_back(sg);
+      }
+    }
+  }
+  pl.wave_seg_first.push_back((int32_t)segs.size());
+  pl.wave_utt_first.push_back((int32_t)n_utt);
+  return pl;
 }
 
 // Batching layer: pack the state-level parameters of `packs` into one pinned blob, copy it to
@@ -470,96 +586,27 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   // groups, with frame counts in proportion to the weights; each group is cut into its own full wave of
   // segments and filtered by its own launch, so that the device-to-host copy of one group overlaps
   // the filter of the next.
-  std::vector<jbk::MlsaSegment> segs;
-  r->wave_seg_first.assign(1, 0);
-  r->wave_utt_first.assign(1, 0);
-  if (!streaming && TF > 0) {
-    const int64_t W = e.mlsa_warm_frames;
-    const int64_t target = (int64_t)ctx->sm_count * 4 * kSegWarpsPerSmsp * 6;
-    std::vector<double> ww = wave_weights;
-    if (ww.empty()) ww.assign(1, 1.0);
-    // every wave should still fill the chip with segments of at least kSegMinFrames / 2 own frames:
-    // merge the last two waves until the smallest one does
-    auto smallest = [&]() {
-      double s = 0, m = 1e300;
-      for (double x : ww) s += x;
-      for (double x : ww) m = std::min(m, x / s);
-      return m;
-    };
-    while (ww.size() > 1 && smallest() * (double)TF < (double)(target * (kSegMinFrames / 2))) {
-      ww[ww.size() - 2] += ww.back();
-      ww.pop_back();
-    }
-    const int waves = (int)ww.size();
-    double wsum = 0, wacc = 0;
-    for (double x : ww) wsum += x;
-    std::vector<size_t> ucut(waves + 1, n_utt);
-    ucut[0] = 0;
-    for (int wv = 1; wv < waves; ++wv) {
-      wacc += ww[(size_t)wv - 1];
-      size_t u = ucut[wv - 1];
-      while (u < n_utt && (double)r->frame_off[u] < (double)TF * (wacc / wsum)) ++u;
-      ucut[wv] = u;
-    }
-    for (int wv = 0; wv < waves; ++wv) {
-      const size_t ua = ucut[wv], ub = ucut[wv + 1];
-      const int64_t TFw = r->frame_off[ub] - r->frame_off[ua];
-      if (TFw <= 0) continue;
-      std::vector<jbk::MlsaSegment> ws;
-      auto cut = [&](int64_t S) {
-        ws.clear();
-        for (size_t u = ua; u < ub; ++u) {
-          const int64_t T = (int64_t)packs[u].nframes;
-          if (T <= 0) continue;
-          int64_t G = std::max<int64_t>(1, (T + S / 2) / S);
-          // equal filtered length L for every segment: the first owns L frames, the others L - W
-          while (G > 1 && (T + (G - 1) * W) / G - W < kSegMinFrames / 2) --G;
-          const int64_t L = (T + (G - 1) * W + G - 1) / G;
-          int64_t begin = 0;
-          for (int64_t k = 0; k < G && begin < T; ++k) {
-            int64_t end = (k == G - 1) ? T : std::min<int64_t>(T, begin + (k == 0 ? L : L - W));
-            jbk::MlsaSegment sg;
-            sg.utt = (int32_t)u;
-            sg.begin = (int32_t)begin;
-            sg.end = (int32_t)end;
-            sg.warm = (int32_t)std::max<int64_t>(0, begin - W);
-            sg.prev = k == 0 ? -1 : (int32_t)(ws.size() - 1);  // index before sorting, remapped below
-            ws.push_back(sg);
-            begin = end;
-          }
-        }
-      };
-      int64_t S = std::max<int64_t>(waves > 1 ? kSegMinFrames / 2 : kSegMinFrames, (TFw + target - 1) / target);
-      cut(S);
-      // One wave: all segments run about equally long, so a grid slightly larger than the chip holds
-      // (target segments) would leave a second, nearly empty wave as long as the first.
-      for (int it = 0; it < 64 && (int64_t)ws.size() > target && (int64_t)ws.size() < 2 * target; ++it) {
-        S += std::max<int64_t>(1, S / 50);
-        cut(S);
-      }
-      // six consecutive segments share a warp and run as long as the longest of them
-      std::vector<int32_t> perm(ws.size()), where(ws.size());
-      for (size_t i = 0; i < ws.size(); ++i) perm[i] = (int32_t)i;
-      std::stable_sort(perm.begin(), perm.end(), [&](int32_t x, int32_t y) {
-        return ws[x].end - ws[x].warm > ws[y].end - ws[y].warm;
-      });
-      for (size_t i = 0; i < perm.size(); ++i) where[perm[i]] = (int32_t)i;
-      const int32_t base = (int32_t)segs.size();
-      if (wv > 0) {
-        r->wave_seg_first.push_back(base);
-        r->wave_utt_first.push_back((int32_t)ua);
-      }
-      for (size_t i = 0; i < perm.size(); ++i) {
-        jbk::MlsaSegment sg = ws[perm[i]];
-        if (sg.prev >= 0) sg.prev = base + where[sg.prev];
-        r->seg_frames += sg.end - sg.warm;
-        segs.push_back(sg);
-      }
-    }
-  }
-  r->wave_seg_first.push_back((int32_t)segs.size());
-  r->wave_utt_first.push_back((int32_t)n_utt);
+  SegmentPlan plan;
+  plan.wave_seg_first.assign(2, 0);
+  plan.wave_utt_first = {0, (int32_t)n_utt};
+  const int seg_slots = cond.stage != 0 ? 32 / (int)cond.stage : 6;  // segments per warp of the filter kernel
+  if (!streaming && TF > 0)
+    plan = cut_segments(r->frame_off, n_utt, e.mlsa_warm_frames * (cond.stage != 0 ? kMglsaWarmFactor : 1),
+                        (int64_t)ctx->sm_count * 4 * kSegWarpsPerSmsp * seg_slots, wave_weights);
+  const std::vector<jbk::MlsaSegment>& segs = plan.segs;
+  r->wave_seg_first = plan.wave_seg_first;
+  r->wave_utt_first = plan.wave_utt_first;
+  r->seg_frames = plan.seg_frames;
   const size_t o_segs = in.take(segs.size() * sizeof(jbk::MlsaSegment));
+  // stage != 0: one segment per utterance, longest first, for the pass that repeats a failed cut check
+  std::vector<jbk::MlsaSegment> whole;
+  if (cond.stage != 0 && !streaming) {
+    for (size_t u = 0; u < n_utt; ++u)
+      if (packs[u].nframes > 0) whole.push_back(jbk::MlsaSegment{(int32_t)u, 0, (int32_t)packs[u].nframes, 0, -1});
+    std::stable_sort(whole.begin(), whole.end(),
+                     [](const jbk::MlsaSegment& x, const jbk::MlsaSegment& y) { return x.end > y.end; });
+  }
+  const size_t o_whole = in.take(whole.size() * sizeof(jbk::MlsaSegment));
   size_t o_mean[3], o_vari[3], o_msd[3], o_gvm[3], o_gvv[3], o_gsw[3], o_rows[3];
   int dim[3], nwin[3], is_msd[3], has_gv[3], nvoice[3];
   bool gath[3];
@@ -590,6 +637,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   memcpy(h + o_soff, state_off.data(), (n_utt + 1) * 8);
   memcpy(h + o_foff, r->frame_off.data(), (n_utt + 1) * 8);
   if (!segs.empty()) memcpy(h + o_segs, segs.data(), segs.size() * sizeof(jbk::MlsaSegment));
+  if (!whole.empty()) memcpy(h + o_whole, whole.data(), whole.size() * sizeof(jbk::MlsaSegment));
   {  // longest utterance first: the per-utterance kernels are scheduled block by block in this order
     std::vector<int32_t> order(n_utt);
     for (size_t u = 0; u < n_utt; ++u) order[u] = (int32_t)u;
@@ -694,10 +742,14 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   const size_t w_wave = wk.take((size_t)r->total_samples * 8);
   const size_t w_state = streaming ? wk.take(n_utt * jbk::kVocStateDoubles * 8) : 0;
   const size_t w_out = segs.empty() ? 0 : wk.take((size_t)r->total_samples * 8);
-  const size_t w_segstate = segs.empty() ? 0 : wk.take(segs.size() * 2 * jbk::kMlsaSegStateDoubles * 8);
+  const size_t seg_state_doubles =
+      cond.stage != 0 ? (size_t)jbk::mglsa_state_doubles((int)cond.stage) : (size_t)jbk::kMlsaSegStateDoubles;
+  const size_t w_segstate = segs.empty() ? 0 : wk.take(segs.size() * 2 * seg_state_doubles * 8);
   const size_t w_worst = wk.take(8);
-  const bool postfilter = cond.beta > 0.0 && dim[0] > 2;  // cepstrum.rs:24
-  const size_t w_bfirst = postfilter ? wk.take(n_utt * (size_t)dim[0] * 8) : 0;
+  const bool postfilter = cond.stage == 0 && cond.beta > 0.0 && dim[0] > 2;  // cepstrum.rs:24
+  const bool first_rows = postfilter || cond.stage != 0;  // rows the first frame starts from (mod.rs:79-109)
+  const size_t w_bfirst = first_rows ? wk.take(n_utt * (size_t)dim[0] * 8) : 0;
+  const size_t w_binc = cond.stage != 0 ? wk.take((size_t)TF * dim[0] * 8) : 0;
   r->d_work = ctx->dalloc(wk.off, &r->work_cap);
   uint8_t* di = (uint8_t*)r->d_in;
   uint8_t* dw = (uint8_t*)r->d_work;
@@ -758,11 +810,15 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   r->vp.rate = (double)cond.sampling_frequency;
   r->vp.alpha = cond.alpha;
   r->vp.volume = cond.volume;
+  r->vp.stage = (int)cond.stage;
+  r->vp.use_log_gain = cond.use_log_gain ? 1 : 0;
+  r->lsp_beta = cond.stage != 0 ? cond.beta : 0.0;
   r->vd.mcp = r->streams.s[0].par;
   r->vd.lf0 = r->streams.s[1].par;
   r->vd.lpf = r->streams.s[2].par;
   r->vd.b = (double*)(dw + w_b);
-  r->vd.b_first = postfilter ? (const double*)(dw + w_bfirst) : nullptr;
+  r->vd.b_first = first_rows ? (const double*)(dw + w_bfirst) : nullptr;
+  r->vd.binc = cond.stage != 0 ? (double*)(dw + w_binc) : nullptr;
   r->beta = postfilter ? cond.beta : 0.0;
   r->vd.pitch = (double*)(dw + w_pitch);
   r->vd.pulse = (double*)(dw + w_pulse);
@@ -773,6 +829,9 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   r->segs.n_seg = (int)segs.size();
   r->segs.seg = (const jbk::MlsaSegment*)(di + o_segs);
   r->segs.state = segs.empty() ? nullptr : (double*)(dw + w_segstate);
+  r->whole.n_seg = (int)whole.size();
+  r->whole.seg = (const jbk::MlsaSegment*)(di + o_whole);
+  r->whole.state = nullptr;
   r->d_worst = (double*)(dw + w_worst);
   r->result = r->vd.wave;
   r->vd.frame_begin = 0;
@@ -794,6 +853,20 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   return r.release();
 }
 
+// Spectrum frames -> filter coefficient rows vd.b (and vd.b_first).
+static void launch_spectrum_prep(Engine::Resident* r, cudaStream_t st) {
+  if (r->vp.stage != 0) {  // Stage::NonZero: LSP frames (vocoder/mod.rs:92-107,148-155)
+    JB_LAUNCH(jbk::launch_lsp_prep(r->layout, r->vp, r->vd, r->lsp_beta, const_cast<double*>(r->vd.b_first),
+                                   r->total_frames, st));
+    JB_LAUNCH(jbk::launch_row_increments(r->layout, r->vp, r->vd, r->total_frames, st));
+    return;
+  }
+  JB_LAUNCH(jbk::launch_frame_prep(r->layout, r->vp, r->vd, r->total_frames, 2, st));
+  if (r->beta > 0.0)  // MelCepstrum::postfilter_mcp (cepstrum.rs:23-37): rewrites vd.b in place
+    JB_LAUNCH(jbk::launch_postfilter(r->layout, r->vp, r->vd, r->beta, const_cast<double*>(r->vd.b_first),
+                                     r->total_frames, st));
+}
+
 // MLPG for the three streams + the per-frame vocoder inputs. The LF0 chain (solve, GV, pitch
 // period and, for whole-utterance synthesis, the pulse train) only has n_utt systems, so it runs
 // on the side stream beside the MCP/LPF solves instead of in front of them.
@@ -811,10 +884,7 @@ static void launch_mlpg_all(Engine::Resident* r, bool with_pulse) {
   JB_CUDA(cudaEventRecord(c->evx[1], sb));
   JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[0], r->total_frames, r->total_states, st));
   JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[2], r->total_frames, r->total_states, st));
-  JB_LAUNCH(jbk::launch_frame_prep(r->layout, r->vp, r->vd, r->total_frames, 2, st));
-  if (r->beta > 0.0)  // MelCepstrum::postfilter_mcp (cepstrum.rs:23-37): rewrites vd.b in place
-    JB_LAUNCH(jbk::launch_postfilter(r->layout, r->vp, r->vd, r->beta, const_cast<double*>(r->vd.b_first),
-                                     r->total_frames, st));
+  launch_spectrum_prep(r, st);
   JB_CUDA(cudaStreamWaitEvent(st, c->evx[1], 0));
 }
 
@@ -840,8 +910,12 @@ static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_exc
   r->copied_by_waves = false;
   r->kernels_end = nullptr;
   if (stop_after_excitation) return;
-  const bool v3 = (variant < 0 || variant == 3) && r->segs.n_seg > 0 && r->vp.nmcp == 35 &&
-                  r->vp.fperiod % 16 == 0 && r->vd.frame_begin == 0 && r->vd.frame_count < 0;
+  const bool mg = r->vp.stage != 0;  // MGLSA (mglsa.cu): segmented unless the sequential variant is forced
+  if (mg && (r->vd.out == nullptr || r->vp.fperiod % 16 != 0))
+    throw Error(kErrUnsupported, "stage != 0: streaming synthesis / fperiod not a multiple of 16 are not built");
+  const bool v3 = mg ? (variant < 0 || variant == 3) && r->segs.n_seg > 0
+                     : (variant < 0 || variant == 3) && r->segs.n_seg > 0 && r->vp.nmcp == 35 &&
+                           r->vp.fperiod % 16 == 0 && r->vd.frame_begin == 0 && r->vd.frame_count < 0;
   if (v3) {
     const int waves = (int)r->wave_seg_first.size() - 1;
     const bool direct = wc && wc->direct && !wc->host16;
@@ -849,7 +923,8 @@ static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_exc
     if (direct) vd.out = wc->host;  // zero-copy: output stores cross PCIe while the filter runs
     for (int w = 0; w < waves; ++w) {
       const int s0 = r->wave_seg_first[w], s1 = r->wave_seg_first[w + 1];
-      JB_LAUNCH(jbk::launch_mlsa_v3(r->layout, r->vp, vd, r->segs, s0, s1 - s0, st));
+      if (mg) JB_LAUNCH(jbk::launch_mglsa(r->layout, r->vp, vd, r->segs, s0, s1 - s0, st));
+      else JB_LAUNCH(jbk::launch_mlsa_v3(r->layout, r->vp, vd, r->segs, s0, s1 - s0, st));
       if (wc && !direct) {
         const int64_t f0 = r->frame_off[(size_t)r->wave_utt_first[w]];
         const int64_t f1 = r->frame_off[(size_t)r->wave_utt_first[w + 1]];
@@ -866,7 +941,12 @@ static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_exc
       }
     }
     r->h_worst = r->ctx->h_worst;
-    JB_LAUNCH(jbk::launch_mlsa_seg_check(r->segs, r->d_worst, r->h_worst, st));
+    if (mg) {
+      const int n = jbk::mglsa_state_doubles(r->vp.stage);
+      JB_LAUNCH(jbk::launch_mlsa_seg_check(r->segs, r->d_worst, r->h_worst, st, n, n));
+    } else {
+      JB_LAUNCH(jbk::launch_mlsa_seg_check(r->segs, r->d_worst, r->h_worst, st));
+    }
     JB_CUDA(cudaEventRecord(r->ctx->ev[7], st));
     r->kernels_end = r->ctx->ev[7];
     r->result = r->vd.out;
@@ -874,6 +954,9 @@ static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_exc
       JB_CUDA(cudaEventRecord(wc->done, direct ? st : wc->copy_stream));
       r->copied_by_waves = true;
     }
+  } else if (mg) {
+    JB_LAUNCH(jbk::launch_mglsa(r->layout, r->vp, r->vd, r->whole, 0, r->whole.n_seg, st));
+    r->result = r->vd.out;
   } else {
     JB_LAUNCH(jbk::launch_mlsa(r->layout, r->vp, r->vd, variant == 3 ? -1 : variant, st));
   }
@@ -883,14 +966,19 @@ static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_exc
 // disagree (the warm-up was too short for this input) the sequential kernel redoes the batch.
 // Returns true when it did; the caller then repeats whatever it had queued behind the filter.
 static bool mlsa_cut_check_failed(Engine::Resident* r, double tol) {
-  if (r->result != r->vd.out || r->vd.out == nullptr) return false;
+  if (r->result != r->vd.out || r->vd.out == nullptr || r->kernels_end == nullptr) return false;
   const double w = r->h_worst ? *r->h_worst : 0.0;
   return !(w <= tol);  // NaN counts as a failed cut
 }
 static void mlsa_sequential_rerun(Engine::Resident* r) {
   cudaStream_t st = r->ctx->stream;
-  JB_LAUNCH(jbk::launch_mlsa(r->layout, r->vp, r->vd, 2, st));
-  r->result = r->vd.wave;
+  if (r->vp.stage != 0) {
+    JB_LAUNCH(jbk::launch_mglsa(r->layout, r->vp, r->vd, r->whole, 0, r->whole.n_seg, st));
+    r->result = r->vd.out;
+  } else {
+    JB_LAUNCH(jbk::launch_mlsa(r->layout, r->vp, r->vd, 2, st));
+    r->result = r->vd.wave;
+  }
   r->used_fallback = true;
 }
 
@@ -904,12 +992,174 @@ Engine::Resident* Engine::prepare(const std::vector<std::vector<std::string>>& u
   return make_resident(*this, c, packs.data(), packs.size(), false, condition, {});
 }
 
+Engine::Resident* Engine::prepare_tracks(const VocoderConfig& cfg, size_t n_utt, const size_t* frame_off,
+                                         const double* spectrum, const double* lf0, const double* lpf,
+                                         int device_index) const {
+  if (device_index < 0 || (size_t)device_index >= devices_.size())
+    throw Error(kErrArgument, "device index out of range");
+  if (cfg.nmcp < 1 || cfg.fperiod < 1 || cfg.fperiod > 1024 || cfg.nlpf > 63)
+    throw Error(kErrArgument, "vocoder: nmcp >= 1, 1 <= fperiod <= 1024, nlpf <= 63");
+  if (cfg.nlpf > 0 && cfg.nlpf % 2 == 0)
+    throw Error(kErrArgument, "The number of low-pass filter coefficient must be odd numbers.");  // speech.rs:38-40
+  if (cfg.stage > (size_t)jbk::kMglsaMaxStage || (cfg.stage != 0 && (cfg.nmcp > (size_t)jbk::kMglsaMaxOrder || cfg.nmcp < 3)))
+    throw Error(kErrUnsupported, "vocoder: stage <= 8, and 3 <= nmcp <= 36 when stage != 0");
+  if (cfg.stage != 0 && cfg.fperiod % 16 != 0)
+    throw Error(kErrUnsupported, "vocoder: stage != 0 needs fperiod % 16 == 0");
+  if (cfg.stage == 0 && cfg.nmcp != 35)
+    throw Error(kErrUnsupported, "vocoder: the MLSA kernels are built for 35 mel-cepstral coefficients");
+  DeviceCtx* ctx = this->ctx(devices_[(size_t)device_index]);
+  std::lock_guard<std::mutex> g(ctx->mu);
+  JB_CUDA(cudaSetDevice(ctx->device));
+  std::unique_ptr<Resident> r(new Resident());
+  r->ctx = ctx;
+  r->n_utt = (int)n_utt;
+  r->from_tracks = true;
+  r->frame_off.assign(n_utt + 1, 0);
+  for (size_t u = 0; u < n_utt; ++u) {
+    if (frame_off[u + 1] < frame_off[u] || frame_off[0] != 0) throw Error(kErrArgument, "vocoder: frame_off must ascend from 0");
+    r->frame_off[u + 1] = (int64_t)frame_off[u + 1];
+    r->max_frames = std::max<int64_t>(r->max_frames, (int64_t)(frame_off[u + 1] - frame_off[u]));
+  }
+  const int64_t TF = r->total_frames = r->frame_off[n_utt];
+  const int fp = (int)cfg.fperiod;
+  r->total_samples = TF * fp;
+  if (r->max_frames * (int64_t)fp > (int64_t)INT32_MAX) throw Error(kErrUnsupported, "utterance longer than 2^31 samples");
+  const size_t M = cfg.nmcp, NL = cfg.nlpf;
+
+  const int seg_slots = cfg.stage != 0 ? 32 / (int)cfg.stage : 6;
+  SegmentPlan plan;
+  plan.wave_seg_first.assign(2, 0);
+  plan.wave_utt_first = {0, (int32_t)n_utt};
+  if (TF > 0)
+    plan = cut_segments(r->frame_off, n_utt, mlsa_warm_frames * (cfg.stage != 0 ? kMglsaWarmFactor : 1),
+                        (int64_t)ctx->sm_count * 4 * kSegWarpsPerSmsp * seg_slots, {});
+  r->wave_seg_first = plan.wave_seg_first;
+  r->wave_utt_first = plan.wave_utt_first;
+  r->seg_frames = plan.seg_frames;
+  std::vector<jbk::MlsaSegment> whole;
+  std::vector<int32_t> order(n_utt);
+  for (size_t u = 0; u < n_utt; ++u) order[u] = (int32_t)u;
+  std::stable_sort(order.begin(), order.end(), [&](int32_t x, int32_t y) {
+    return r->frame_off[(size_t)x + 1] - r->frame_off[(size_t)x] > r->frame_off[(size_t)y + 1] - r->frame_off[(size_t)y];
+  });
+  if (cfg.stage != 0)
+    for (int32_t u : order) {
+      const int64_t T = r->frame_off[(size_t)u + 1] - r->frame_off[(size_t)u];
+      if (T > 0) whole.push_back(jbk::MlsaSegment{u, 0, (int32_t)T, 0, -1});
+    }
+
+  Carver in;
+  const size_t o_foff = in.take((n_utt + 1) * 8), o_order = in.take(n_utt * 4);
+  const size_t o_segs = in.take(plan.segs.size() * sizeof(jbk::MlsaSegment));
+  const size_t o_whole = in.take(whole.size() * sizeof(jbk::MlsaSegment));
+  const size_t o_spec = in.take(((size_t)TF + (cfg.coefficient_rows ? n_utt : 0)) * M * 8), o_lf0 = in.take((size_t)TF * 8), o_lpf = in.take((size_t)TF * NL * 8);
+  r->in_bytes = in.off;
+  uint8_t* h = (uint8_t*)pinned().alloc(r->in_bytes);
+  struct Release {
+    void* p;
+    ~Release() { pinned().release(p); }
+  } rel{h};
+  memcpy(h + o_foff, r->frame_off.data(), (n_utt + 1) * 8);
+  if (n_utt) memcpy(h + o_order, order.data(), n_utt * 4);
+  if (!plan.segs.empty()) memcpy(h + o_segs, plan.segs.data(), plan.segs.size() * sizeof(jbk::MlsaSegment));
+  if (!whole.empty()) memcpy(h + o_whole, whole.data(), whole.size() * sizeof(jbk::MlsaSegment));
+  if (TF > 0) {
+    memcpy(h + o_spec, spectrum, ((size_t)TF + (cfg.coefficient_rows ? n_utt : 0)) * M * 8);
+    memcpy(h + o_lf0, lf0, (size_t)TF * 8);
+    if (NL) memcpy(h + o_lpf, lpf, (size_t)TF * NL * 8);
+  }
+  r->d_in = ctx->dalloc(r->in_bytes, &r->in_cap);
+  JB_CUDA(cudaMemcpyAsync(r->d_in, h, r->in_bytes, cudaMemcpyHostToDevice, ctx->stream));
+  JB_CUDA(cudaEventRecord(ctx->ev[1], ctx->stream));
+  r->h2d_bytes = (int64_t)r->in_bytes;
+
+  Carver wk;
+  const size_t w_b = wk.take((size_t)TF * M * 8), w_pitch = wk.take((size_t)TF * 8);
+  const size_t w_pulse = wk.take((size_t)r->total_samples * 8), w_runs = wk.take(((size_t)TF + 1) * 4);
+  const size_t w_wave = wk.take((size_t)r->total_samples * 8), w_out = wk.take((size_t)r->total_samples * 8);
+  const size_t seg_state_doubles =
+      cfg.stage != 0 ? (size_t)jbk::mglsa_state_doubles((int)cfg.stage) : (size_t)jbk::kMlsaSegStateDoubles;
+  const size_t w_segstate = wk.take(plan.segs.size() * 2 * seg_state_doubles * 8);
+  const size_t w_worst = wk.take(8);
+  const bool postfilter = cfg.stage == 0 && cfg.beta > 0.0 && M > 2;
+  const bool first_rows = postfilter || cfg.stage != 0 || cfg.coefficient_rows;
+  r->rows_given = cfg.coefficient_rows;
+  const size_t w_bfirst = first_rows ? wk.take(n_utt * M * 8) : 0;
+  const size_t w_binc = cfg.stage != 0 ? wk.take((size_t)TF * M * 8) : 0;
+  r->d_work = ctx->dalloc(wk.off, &r->work_cap);
+  uint8_t* di = (uint8_t*)r->d_in;
+  uint8_t* dw = (uint8_t*)r->d_work;
+
+  r->layout.n_utt = (int)n_utt;
+  r->layout.frame_off = (const int64_t*)(di + o_foff);
+  r->layout.order = (const int32_t*)(di + o_order);
+  r->layout.max_frames = (int)r->max_frames;
+  r->vp.nmcp = (int)M;
+  r->vp.nlpf = (int)NL;
+  r->vp.fperiod = fp;
+  r->vp.rate = (double)cfg.rate;
+  r->vp.alpha = cfg.alpha;
+  r->vp.volume = cfg.volume;
+  r->vp.stage = (int)cfg.stage;
+  r->vp.use_log_gain = cfg.use_log_gain ? 1 : 0;
+  r->lsp_beta = cfg.stage != 0 ? cfg.beta : 0.0;
+  r->beta = postfilter ? cfg.beta : 0.0;
+  r->vd.mcp = (const double*)(di + o_spec);
+  r->vd.lf0 = (const double*)(di + o_lf0);
+  r->vd.lpf = (const double*)(di + o_lpf);
+  r->vd.b = (double*)(dw + w_b);
+  r->vd.b_first = first_rows ? (const double*)(dw + w_bfirst) : nullptr;
+  r->vd.binc = cfg.stage != 0 ? (double*)(dw + w_binc) : nullptr;
+  r->vd.pitch = (double*)(dw + w_pitch);
+  r->vd.pulse = (double*)(dw + w_pulse);
+  r->vd.runs = (int32_t*)(dw + w_runs);
+  r->vd.wave = (double*)(dw + w_wave);
+  r->vd.out = (double*)(dw + w_out);
+  r->vd.state = nullptr;
+  r->vd.frame_begin = 0;
+  r->vd.frame_count = -1;
+  r->segs.n_seg = (int)plan.segs.size();
+  r->segs.seg = (const jbk::MlsaSegment*)(di + o_segs);
+  r->segs.state = plan.segs.empty() ? nullptr : (double*)(dw + w_segstate);
+  r->whole.n_seg = (int)whole.size();
+  r->whole.seg = (const jbk::MlsaSegment*)(di + o_whole);
+  r->d_worst = (double*)(dw + w_worst);
+  r->result = r->vd.wave;
+
+  const size_t need = (size_t)r->max_frames * fp;
+  if (need > ctx->noise_len) {
+    std::lock_guard<std::mutex> gn(noise_mu_);
+    const std::vector<double>& tbl = noise_table(need + need / 2);
+    if (ctx->d_noise) JB_CUDA(cudaFree(ctx->d_noise));
+    JB_CUDA(cudaMalloc((void**)&ctx->d_noise, tbl.size() * 8));
+    JB_CUDA(cudaMemcpy(ctx->d_noise, tbl.data(), tbl.size() * 8, cudaMemcpyHostToDevice));
+    ctx->noise_len = tbl.size();
+  }
+  r->vd.noise = ctx->d_noise;
+  JB_CUDA(cudaEventSynchronize(ctx->ev[1]));
+  return r.release();
+}
+
 double Engine::run_resident(Resident* r, BatchTimings* tm) const {
   DeviceCtx* c = r->ctx;
   std::lock_guard<std::mutex> g(c->mu);
   JB_CUDA(cudaSetDevice(c->device));
   JB_CUDA(cudaEventRecord(c->ev[2], c->stream));
-  launch_mlpg_all(r, true);
+  if (r->from_tracks) {  // the parameter tracks are the input: per-frame prep only
+    JB_LAUNCH(jbk::launch_frame_prep(r->layout, r->vp, r->vd, r->total_frames, 1, c->stream));
+    JB_LAUNCH(jbk::launch_pulse(r->layout, r->vp, r->vd, r->total_samples, c->stream));
+    if (r->rows_given) {
+      const size_t rows = (size_t)r->total_frames * r->vp.nmcp * 8;
+      JB_CUDA(cudaMemcpyAsync(r->vd.b, r->vd.mcp, rows, cudaMemcpyDeviceToDevice, c->stream));
+      JB_CUDA(cudaMemcpyAsync(const_cast<double*>(r->vd.b_first), (const uint8_t*)r->vd.mcp + rows,
+                              (size_t)r->n_utt * r->vp.nmcp * 8, cudaMemcpyDeviceToDevice, c->stream));
+      if (r->vp.stage != 0) JB_LAUNCH(jbk::launch_row_increments(r->layout, r->vp, r->vd, r->total_frames, c->stream));
+    } else {
+      launch_spectrum_prep(r, c->stream);
+    }
+  } else {
+    launch_mlpg_all(r, true);
+  }
   JB_CUDA(cudaEventRecord(c->ev[3], c->stream));
   launch_vocoder(r, mlsa_variant, false, c->ev[4], true);
   JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
@@ -957,6 +1207,22 @@ void Engine::fetch_resident(Resident* r, double** out, std::vector<size_t>* out_
   out_off->assign((size_t)r->n_utt + 1, 0);
   for (int u = 0; u <= r->n_utt; ++u) (*out_off)[(size_t)u] = (size_t)(r->frame_off[(size_t)u] * r->vp.fperiod);
   *out = h;
+}
+
+std::vector<double> Engine::resident_rows(Resident* r) const {
+  DeviceCtx* c = r->ctx;
+  std::lock_guard<std::mutex> g(c->mu);
+  JB_CUDA(cudaSetDevice(c->device));
+  JB_CUDA(cudaStreamSynchronize(c->stream));
+  const size_t M = (size_t)r->vp.nmcp, nf = (size_t)r->total_frames * M, nu = (size_t)r->n_utt * M;
+  std::vector<double> out(nf + nu, 0.0);
+  if (nf) JB_CUDA(cudaMemcpy(out.data(), r->vd.b, nf * 8, cudaMemcpyDeviceToHost));
+  if (nu && r->vd.b_first) JB_CUDA(cudaMemcpy(out.data() + nf, r->vd.b_first, nu * 8, cudaMemcpyDeviceToHost));
+  else if (nu)  // beta == 0, stage 0: the first rows are rows of vd.b
+    for (int u = 0; u < r->n_utt; ++u)
+      if (r->frame_off[(size_t)u + 1] > r->frame_off[(size_t)u])
+        memcpy(out.data() + nf + (size_t)u * M, out.data() + (size_t)r->frame_off[(size_t)u] * M, M * 8);
+  return out;
 }
 
 void Engine::release(Resident* r) const {

@@ -100,6 +100,25 @@ class Engine {
   // inside by `resident` handles, see prepare/run below).
   struct Resident;  // a batch whose packed inputs already sit in HBM
   Resident* prepare(const std::vector<std::vector<std::string>>& utts, int device_index) const;
+  // The vocoder seam (Vocoder::new, vocoder/mod.rs:45-70, driven frame by frame as SpeechGenerator does,
+  // speech.rs:65-96) for n_utt independent parameter tracks: a resident batch whose run() skips MLPG.
+  // frame_off[n_utt + 1]; spectrum [frames][nmcp] (mel-cepstrum, or LSP with the gain in column 0 when
+  // stage > 0), lf0 [frames] (NODATA = -1e10 in unvoiced frames), lpf [frames][nlpf] (nlpf == 0: no LPF
+  // stream, excitation.rs:87-99). Throws kErrArgument for an even nlpf > 0 (speech.rs:38-40).
+  struct VocoderConfig {
+    size_t nmcp = 0, nlpf = 0, stage = 0;
+    bool use_log_gain = false;
+    size_t rate = 48000;
+    double alpha = 0.0, beta = 0.0, volume = 1.0;
+    size_t fperiod = 240;
+    // test seam: `spectrum` already holds filter coefficient rows, [frames][nmcp] followed by the
+    // [n_utt][nmcp] rows the first frames start from; the spectrum transform is skipped
+    bool coefficient_rows = false;
+  };
+  // Filter coefficient rows of a resident batch after run(): [frames][nmcp] then [n_utt][nmcp] first rows.
+  std::vector<double> resident_rows(Resident* r) const;
+  Resident* prepare_tracks(const VocoderConfig& cfg, size_t n_utt, const size_t* frame_off, const double* spectrum,
+                           const double* lf0, const double* lpf, int device_index) const;
   // Runs MLPG + vocoder kernels on the resident batch; waveform stays on the device.
   // Returns device time in ms (CUDA events on the launching stream).
   double run_resident(Resident* r, BatchTimings* tm = nullptr) const;

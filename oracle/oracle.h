@@ -58,7 +58,9 @@ struct Random {
   void fill_queue();
 };
 
-// ---- vocoder (src/vocoder/{mod,excitation,mlsa,cepstrum,coefficients}.rs), stage 0 (MLSA)
+// ---- vocoder (src/vocoder/{mod,excitation,mlsa,mglsa,lsp,generalized,cepstrum,coefficients}.rs)
+// Parity status of the stage != 0 arm (LSP -> MGLSA): UNPINNED. The reference holds no test, golden or
+// shipped voice for it (no .htsvoice under models/ sets GAMMA); it is a literal restatement only.
 struct Vocoder {
   Vocoder(size_t nmcp, size_t nlpf, size_t stage, bool use_log_gain, size_t rate, double alpha,
           double beta, double volume, size_t fperiod, bool fma_fir);
@@ -73,6 +75,9 @@ struct Vocoder {
   size_t nmcp, nlpf, rate, fperiod;
   double alpha, beta, volume;
   bool fma_fir;
+  size_t stage = 0;           // 0: MLSA; n > 0: LSP input, MGLSA filter of n sections with gamma = -1/n (stage.rs:28-38)
+  bool use_log_gain = false;
+  std::vector<std::vector<double>> mglsa_d;  // MelGeneralizedLogSpectrumApproximation::d (mglsa.rs:5-13)
   bool is_first = true;
   std::vector<double> coefficients;  // Stage::Zero coefficients
   // MelLogSpectrumApproximation<6> state (mlsa.rs:5-10)
@@ -91,6 +96,10 @@ void postfilter_mcp(std::vector<double>* c, double alpha, double beta);  // ceps
 double b2en(const std::vector<double>& b, double alpha);                // coefficients.rs:75-78
 double fir(double* d, size_t dlen, double x, double alpha, const double* coefficients,
            bool fma);                                                    // mlsa.rs:128-163
+// Stage::NonZero: one LSP frame -> MGLSA filter coefficients (vocoder/mod.rs:92-107 when !filtered,
+// :148-155 when filtered: postfilter_lsp + check_lsp_stability first).
+std::vector<double> lsp_frame_coefficients(const double* spectrum, size_t n, double alpha, bool use_log_gain,
+                                           size_t stage, double beta, bool filtered);
 
 // SpeechGenerator::generate_all (speech.rs:87-96) over [T][dim] parameter arrays.
 std::vector<double> generate_all(Vocoder* v, size_t nframes, const double* mcp, const double* lf0,

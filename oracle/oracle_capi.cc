@@ -249,6 +249,36 @@ int orc_vocoder(size_t nframes, size_t nmcp, size_t nlpf, const double* mcp, con
   }
 }
 
+// The same with Vocoder::new's stage / use_log_gain arguments (stage > 0: `mcp` holds LSP frames).
+int orc_vocoder_ex(size_t nframes, size_t nmcp, size_t nlpf, size_t stage, int use_log_gain, const double* mcp,
+                   const double* lf0, const double* lpf, size_t rate, size_t fperiod, double alpha, double beta,
+                   double volume, int fma, double* out, double* exc_or_null) {
+  try {
+    oracle::Vocoder v(nmcp, nlpf, stage, use_log_gain != 0, rate, alpha, beta, volume, fperiod, fma != 0);
+    std::vector<double> tap;
+    if (exc_or_null) v.excitation_tap = &tap;
+    std::vector<double> w = oracle::generate_all(&v, nframes, mcp, lf0, lpf);
+    memcpy(out, w.data(), w.size() * sizeof(double));
+    if (exc_or_null) memcpy(exc_or_null, tap.data(), tap.size() * sizeof(double));
+    return 0;
+  } catch (const std::exception& e) {
+    return fail(e);
+  }
+}
+
+// Stage::NonZero frame transform: one LSP frame [n] -> coefficients [n] (vocoder/mod.rs:92-107, 148-155).
+int orc_lsp_coefficients(const double* spectrum, size_t n, double alpha, int use_log_gain, size_t stage,
+                         double beta, int filtered, double* out) {
+  try {
+    std::vector<double> c = oracle::lsp_frame_coefficients(spectrum, n, alpha, use_log_gain != 0, stage, beta,
+                                                           filtered != 0);
+    memcpy(out, c.data(), c.size() * sizeof(double));
+    return 0;
+  } catch (const std::exception& e) {
+    return fail(e);
+  }
+}
+
 // MlpgAdjust::create over caller-provided state-level parameters. windows: nwin rows, row w has
 // win_len[w] coefficients, concatenated in win_coef. out: [T][dim], T = sum(durations).
 int orc_mlpg(size_t nstates, const int32_t* durations, size_t dim, size_t nwin,

@@ -165,12 +165,202 @@ double fir(double* d, size_t dlen, double x, double alpha, const double* coeffic
   return y0 + y1;
 }
 
-Vocoder::Vocoder(size_t nmcp_, size_t nlpf_, size_t stage, bool, size_t rate_, double alpha_,
+// ---------------------------------------------------------------- stage != 0: LSP -> MGLSA coefficients
+// Generalized::gnorm / ignorm (generalized.rs:6-38); gamma != 0 on this path (stage.rs:30)
+static std::vector<double> gnorm(const std::vector<double>& c, double gamma) {
+  std::vector<double> t(c);
+  if (gamma != 0.0) {
+    double k = 1.0 + gamma * c[0];
+    t[0] = std::pow(k, 1.0 / gamma);
+    for (size_t i = 1; i < c.size(); ++i) t[i] = c[i] / k;
+  } else {
+    t[0] = std::exp(c[0]);
+  }
+  return t;
+}
+static std::vector<double> ignorm(const std::vector<double>& c, double gamma) {
+  std::vector<double> t(c);
+  if (gamma != 0.0) {
+    double k = std::pow(c[0], gamma);
+    t[0] = (k - 1.0) / gamma;
+    for (size_t i = 1; i < c.size(); ++i) t[i] = c[i] * k;
+  } else {
+    t[0] = std::log(c[0]);
+  }
+  return t;
+}
+
+// MelGeneralizedCepstrum::gc2gc (cepstrum.rs:68-92): g1 = gamma of the input, g2 = of the output
+static std::vector<double> gc2gc(const std::vector<double>& c1, double g1, size_t m2, double g2) {
+  std::vector<double> c2(m2 + 1, 0.0);
+  c2[0] = c1[0];
+  for (size_t i = 1; i <= m2; ++i) {
+    double ss1 = 0.0, ss2 = 0.0;
+    size_t kmax = c1.size() < i ? c1.size() : i;
+    for (size_t k = 1; k < kmax; ++k) {
+      size_t mk = i - k;
+      double cc = c1[k] * c2[mk];
+      ss1 += (double)mk * cc;
+      ss2 += (double)k * cc;
+    }
+    if (i < c1.size()) c2[i] = c1[i] + (g2 * ss2 - g1 * ss1) / (double)i;
+    else c2[i] = (g2 * ss2 - g1 * ss1) / (double)i;
+  }
+  return c2;
+}
+
+// MelGeneralizedCepstrum::mgc2mgc (cepstrum.rs:94-101)
+static std::vector<double> mgc2mgc(const std::vector<double>& c, double a1, double g1, size_t m2, double a2,
+                                   double g2) {
+  if (a1 == a2) return ignorm(gc2gc(gnorm(c, g1), g1, m2, g2), g2);
+  double a = (a2 - a1) / (1.0 - a1 * a2);
+  return ignorm(gc2gc(gnorm(freqt(c, m2, a), g1), g1, m2, g2), g2);
+}
+
+// LineSpectralPairs::lsp2lpc (lsp.rs:27-88). As in the reference, the whole vector (gain slot
+// included) is read as m = len line spectral frequencies; the result has m + 1 entries.
+static std::vector<double> lsp2lpc(const std::vector<double>& lsp) {
+  const size_t m = lsp.size();
+  const size_t mh1 = m % 2 == 0 ? m / 2 : (m + 1) / 2, mh2 = m % 2 == 0 ? m / 2 : (m - 1) / 2;
+  std::vector<double> p, q;
+  for (size_t i = 0; i < m; i += 2) p.push_back(-2.0 * std::cos(lsp[i]));
+  for (size_t i = 1; i < m; i += 2) q.push_back(-2.0 * std::cos(lsp[i]));
+  std::vector<double> a0(mh1 + 1, 0.0), a1(mh1 + 1, 0.0), a2(mh1 + 1, 0.0);
+  std::vector<double> b0(mh2 + 1, 0.0), b1(mh2 + 1, 0.0), b2(mh2 + 1, 0.0);
+  double xff = 0.0, xf = 0.0;
+  std::vector<double> c(m + 1, 0.0);
+  for (size_t k = 0; k <= m; ++k) {
+    double xx = k == 0 ? 1.0 : 0.0;
+    if (m % 2 == 1) {
+      a0[0] = xx;
+      b0[0] = xx - xff;
+      xff = xf;
+      xf = xx;
+    } else {
+      a0[0] = xx + xf;
+      b0[0] = xx - xf;
+      xf = xx;
+    }
+    for (size_t i = 0; i < mh1; ++i) {
+      a0[i + 1] = a0[i] + p[i] * a1[i] + a2[i];
+      a2[i] = a1[i];
+      a1[i] = a0[i];
+    }
+    for (size_t i = 0; i < mh2; ++i) {
+      b0[i + 1] = b0[i] + q[i] * b1[i] + b2[i];
+      b2[i] = b1[i];
+      b1[i] = b0[i];
+    }
+    if (k > 0) c[k - 1] = -0.5 * (a0[mh1] + b0[mh2]);
+  }
+  for (size_t i = m; i-- > 0;) c[i + 1] = -c[i];
+  c[0] = 1.0;
+  return c;
+}
+
+// LineSpectralPairs::lsp2mgc (lsp.rs:90-102)
+static std::vector<double> lsp2mgc(const std::vector<double>& lsp, double alpha, bool use_log_gain, size_t stage,
+                                   double gamma) {
+  std::vector<double> lpc = lsp2lpc(lsp);
+  lpc[0] = use_log_gain ? std::exp(lsp[0]) : lsp[0];
+  lpc = ignorm(lpc, gamma);
+  for (size_t i = 1; i < lpc.size(); ++i) lpc[i] *= -(double)stage;
+  return mgc2mgc(lpc, alpha, gamma, lsp.size() - 1, alpha, gamma);
+}
+
+// LineSpectralPairs::postfilter_lsp (lsp.rs:108-137)
+static void postfilter_lsp(std::vector<double>* l, double alpha, bool use_log_gain, size_t stage, double gamma,
+                           double beta) {
+  std::vector<double>& s = *l;
+  const size_t n = s.size();
+  if (!(beta > 0.0) || n <= 2) return;
+  auto en = [&]() {
+    double e = 0.0;
+    for (double x : lsp2mgc(s, alpha, use_log_gain, stage, gamma)) e += x * x;
+    return e;
+  };
+  std::vector<double> buf(n, 0.0);
+  const double en1 = en();
+  for (size_t i = 0; i < n; ++i) {
+    if (i > 1 && i < n - 1) {
+      double d1 = beta * (s[i + 1] - s[i]);
+      double d2 = beta * (s[i] - s[i - 1]);
+      buf[i] = s[i - 1] + d2 + (d2 * d2 * ((s[i + 1] - s[i - 1]) - (d1 + d2))) / ((d2 * d2) + (d1 * d1));
+    } else {
+      buf[i] = s[i];
+    }
+  }
+  s = buf;
+  const double en2 = en();
+  if (en1 != en2) {
+    if (use_log_gain) s[0] += 0.5 * std::log(en1 / en2);
+    else s[0] *= std::sqrt(en1 / en2);
+  }
+}
+
+// LineSpectralPairs::check_lsp_stability (lsp.rs:139-165)
+static void check_lsp_stability(std::vector<double>* l) {
+  std::vector<double>& s = *l;
+  const double pi = 3.14159265358979323846;
+  const double min = 0.25 * pi / (double)s.size();
+  const size_t last = s.size() - 1;
+  for (int it = 0; it < 4; ++it) {
+    bool find = false;
+    for (size_t j = 1; j < last; ++j) {
+      double tmp = s[j + 1] - s[j];
+      if (tmp < min) {
+        s[j] -= 0.5 * (min - tmp);
+        s[j + 1] += 0.5 * (min - tmp);
+        find = true;
+      }
+    }
+    if (s[1] < min) {
+      s[1] = min;
+      find = true;
+    }
+    if (s[last] > pi - min) {
+      s[last] = pi - min;
+      find = true;
+    }
+    if (!find) break;
+  }
+}
+
+// The Stage::NonZero frame transform of Vocoder::synthesize (mod.rs:92-107 for the first frame,
+// :148-155 for every frame): LSP frame -> filter coefficients.
+std::vector<double> lsp_frame_coefficients(const double* spectrum, size_t n, double alpha, bool use_log_gain,
+                                           size_t stage, double beta, bool filtered) {
+  const double gamma = -1.0 / (double)stage;
+  std::vector<double> lsp(spectrum, spectrum + n);
+  if (filtered) {
+    postfilter_lsp(&lsp, alpha, use_log_gain, stage, gamma, beta);
+    check_lsp_stability(&lsp);
+  }
+  std::vector<double> mgc = lsp2mgc(lsp, alpha, use_log_gain, stage, gamma);
+  std::vector<double> cc = gnorm(mc2b(mgc.data(), mgc.size(), alpha), gamma);
+  for (size_t i = 1; i < cc.size(); ++i) cc[i] *= gamma;
+  return cc;
+}
+
+// MelGeneralizedLogSpectrumApproximation::dff (mglsa.rs:21-41)
+static void mglsa_dff(std::vector<double>& d, double* x, double alpha, const std::vector<double>& c) {
+  const double aa = 1.0 - alpha * alpha;
+  double y = d[0] * c[1];
+  for (size_t i = 1; i + 1 < c.size(); ++i) {
+    d[i] += alpha * (d[i + 1] - d[i - 1]);
+    y += d[i] * c[i + 1];
+  }
+  *x -= y;
+  for (size_t i = c.size() - 1; i >= 1; --i) d[i] = d[i - 1];
+  d[0] = alpha * d[0] + aa * *x;
+}
+
+Vocoder::Vocoder(size_t nmcp_, size_t nlpf_, size_t stage_, bool use_log_gain_, size_t rate_, double alpha_,
                  double beta_, double volume_, size_t fperiod_, bool fma_fir_)
     : nmcp(nmcp_), nlpf(nlpf_), rate(rate_), fperiod(fperiod_), alpha(alpha_), beta(beta_),
-      volume(volume_), fma_fir(fma_fir_) {
-  if (stage != 0) throw std::runtime_error("oracle: stage != 0 (MGLSA/LSP) is outside the built scope");
+      volume(volume_), fma_fir(fma_fir_), stage(stage_), use_log_gain(use_log_gain_) {
   for (auto& v : d21) v.assign(nmcp, 0.0);
+  mglsa_d.assign(stage, std::vector<double>(nmcp, 0.0));  // mglsa.rs:9-13
   ring.assign(nlpf, 0.0);
 }
 
@@ -183,12 +373,17 @@ void Vocoder::synthesize(double lf0, const double* spectrum, const double* lpf, 
   }
   if (is_first) {  // mod.rs:79-109
     is_first = false;
-    coefficients = mc2b(spectrum, nmcp, alpha);
+    coefficients = stage == 0 ? mc2b(spectrum, nmcp, alpha)
+                              : lsp_frame_coefficients(spectrum, nmcp, alpha, use_log_gain, stage, beta, false);
   }
-  // Stage::Zero arm, mod.rs:112-141
-  std::vector<double> cep(spectrum, spectrum + nmcp);
-  postfilter_mcp(&cep, alpha, beta);
-  std::vector<double> cc = mc2b(cep.data(), nmcp, alpha);
+  std::vector<double> cc;
+  if (stage == 0) {  // Stage::Zero arm, mod.rs:112-141
+    std::vector<double> cep(spectrum, spectrum + nmcp);
+    postfilter_mcp(&cep, alpha, beta);
+    cc = mc2b(cep.data(), nmcp, alpha);
+  } else {  // Stage::NonZero arm, mod.rs:142-176
+    cc = lsp_frame_coefficients(spectrum, nmcp, alpha, use_log_gain, stage, beta, true);
+  }
   std::vector<double> cinc(nmcp);
   for (size_t k = 0; k < nmcp; ++k) cinc[k] = (cc[k] - coefficients[k]) / (double)fperiod;
 
@@ -247,6 +442,14 @@ void Vocoder::synthesize(double lf0, const double* spectrum, const double* lpf, 
 
     if (pulse_tap) pulse_tap->push_back(tap_pulse);
 
+    if (stage != 0) {  // mod.rs:161-168
+      x *= coefficients[0];
+      if (gained_tap) gained_tap->push_back(x);
+      for (auto& dd : mglsa_d) mglsa_dff(dd, &x, alpha, coefficients);  // mglsa.rs:15-19
+      for (size_t k = 0; k < nmcp; ++k) coefficients[k] += cinc[k];
+      rawdata[i] = x * volume;
+      continue;
+    }
     if (x != 0.0) x *= std::exp(coefficients[0]);  // mod.rs:129-131
     if (gained_tap) gained_tap->push_back(x);
 

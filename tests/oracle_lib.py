@@ -108,6 +108,34 @@ def vocoder(mcp, lf0, lpf, rate=48000, fperiod=240, alpha=0.55, beta=0.0, volume
     return (out, exc) if tap else out
 
 
+def vocoder_ex(spectrum, lf0, lpf, stage=0, use_log_gain=False, rate=48000, fperiod=240, alpha=0.55, beta=0.0,
+               volume=1.0, fma=False, tap=False):
+    """Vocoder::new(nmcp, nlpf, stage, use_log_gain, ...) + SpeechGenerator::generate_all; stage > 0 takes
+    LSP frames (gain in column 0). lpf with zero columns = a voice without LPF stream (excitation.rs:87-99)."""
+    spectrum = np.ascontiguousarray(spectrum, dtype=np.float64)
+    lf0 = np.ascontiguousarray(lf0, dtype=np.float64)
+    lpf = np.ascontiguousarray(lpf, dtype=np.float64)
+    T = spectrum.shape[0]
+    nlpf = lpf.shape[1] if lpf.ndim == 2 else 0
+    out = np.zeros(T * fperiod)
+    exc = np.zeros(T * fperiod) if tap else None
+    _ck(_L.orc_vocoder_ex(C.c_size_t(T), C.c_size_t(spectrum.shape[1]), C.c_size_t(nlpf), C.c_size_t(stage),
+                          int(use_log_gain), spectrum.ctypes.data_as(D), lf0.ctypes.data_as(D),
+                          lpf.ctypes.data_as(D) if nlpf else None, C.c_size_t(rate), C.c_size_t(fperiod),
+                          C.c_double(alpha), C.c_double(beta), C.c_double(volume), int(fma),
+                          out.ctypes.data_as(D), exc.ctypes.data_as(D) if tap else None))
+    return (out, exc) if tap else out
+
+
+def lsp_coefficients(frame, stage, alpha=0.55, use_log_gain=False, beta=0.0, filtered=True):
+    """Stage::NonZero frame transform (vocoder/mod.rs:92-107 / 148-155): LSP frame -> filter coefficients."""
+    v = np.ascontiguousarray(frame, dtype=np.float64)
+    out = np.zeros(len(v))
+    _ck(_L.orc_lsp_coefficients(v.ctypes.data_as(D), C.c_size_t(len(v)), C.c_double(alpha), int(use_log_gain),
+                                C.c_size_t(stage), C.c_double(beta), int(filtered), out.ctypes.data_as(D)))
+    return out
+
+
 def postfilter(c, alpha=0.55, beta=0.3):
     """MelCepstrum::postfilter_mcp (cepstrum.rs:23-37) -> (c', energy before, energy after)."""
     v = np.array(c, dtype=np.float64)

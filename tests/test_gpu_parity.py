@@ -204,9 +204,14 @@ def test_postfilter_streaming_and_tohoku():
 
 def test_unsupported_is_loud():
     e = jb.Engine.load([NITECH])
-    e.set("stage", 2)
+    e.set("stage", 9)  # MGLSA filters of more than 8 sections are not built
     with pytest.raises(jb.JbError) as ei:
         e.synthesize(SAMPLE_SENTENCE_1)
+    assert ei.value.kind == "Unsupported"
+    e.set("stage", 2)  # streaming with stage != 0 is not built either
+    with pytest.raises(jb.JbError) as ei:
+        g = e.generator([SAMPLE_SENTENCE_1])
+        g.generate_step(1)
     assert ei.value.kind == "Unsupported"
 
 

@@ -114,3 +114,79 @@ def test_postfilter_properties():
         assert np.isfinite(b2[0]) and abs(b2[0] - b[0]) > 1e-6 and e_before > 0 and e_after > 0
         same, _, _ = ol.postfilter(row, a, 0.0)
         assert np.array_equal(same, row)
+
+
+# ---- stage != 0 arm (LSP -> MGLSA): no reference golden exists; these pin the restatement's algebra
+def _lsp(M, seed=0):
+    rng = np.random.default_rng(seed)
+    x = np.sort(np.linspace(0.12, 3.0, M) + rng.uniform(-0.02, 0.02, M))
+    x[0] = 0.06
+    return x
+
+
+def test_lsp_coefficients_structure():
+    import oracle_lib as O
+    f = _lsp(25)
+    for stage in (1, 2, 3):
+        c_log = O.lsp_coefficients(f, stage, 0.42, True, filtered=False)
+        assert np.isfinite(c_log).all() and c_log[0] > 0
+        # a well separated frame passes check_lsp_stability untouched and beta = 0 skips the post-filter
+        assert np.array_equal(O.lsp_coefficients(f, stage, 0.42, True, 0.0, True), c_log)
+        # frequencies closer than pi / (4 m) are pushed apart (lsp.rs:139-165), beta > 0 moves them (lsp.rs:108-137)
+        g = f.copy()
+        g[7] = g[6] + 1e-4
+        assert not np.array_equal(O.lsp_coefficients(g, stage, 0.42, True, 0.0, True),
+                                  O.lsp_coefficients(g, stage, 0.42, True, 0.0, False))
+        assert not np.array_equal(O.lsp_coefficients(f, stage, 0.42, True, 0.3, True), c_log)
+        # with the linear gain convention the gain slot is used as it is (lsp.rs:92-96): a larger gain, a larger c[0]
+        lin = O.lsp_coefficients(f, stage, 0.42, False, filtered=False)
+        assert lin[0] < c_log[0] and np.allclose(lin[1:], c_log[1:], rtol=1e-6, atol=1e-9)
+
+
+def test_lsp_transform_conditioning():
+    """How far a 1-ulp change of the input moves the rows: the bound the GPU's device-side transform
+    (CUDA cos/exp/pow, within 2 ulp of glibc) is held to in test_gpu_vocoder_seam.py."""
+    import oracle_lib as O
+    worst = {}
+    for M in (13, 25, 35):
+        f = _lsp(M, 1)
+        c0 = O.lsp_coefficients(f, 2, 0.42, True)
+        w = 0.0
+        for k in range(16):
+            sgn = np.where(np.random.default_rng(k).random(M) < 0.5, -1.0, 1.0)
+            c1 = O.lsp_coefficients(np.nextafter(f, f + sgn), 2, 0.42, True)
+            w = max(w, np.abs(c1 - c0).max() / np.abs(c0).max())
+        worst[M] = w
+    assert worst[13] < 1e-12 and worst[25] < 1e-9 and 1e-11 < worst[35] < 2e-7
+
+
+def test_mglsa_matches_a_direct_restatement():
+    """Vocoder stage 2 against a few lines of numpy that follow mglsa.rs:21-41 and vocoder/mod.rs:156-175."""
+    import oracle_lib as O
+    T, M, fp, stage, alpha = 6, 13, 16, 2, 0.42
+    spec = np.stack([_lsp(M, 10 + t) for t in range(T)])
+    lf0 = np.full(T, -1e10)
+    w, exc = O.vocoder_ex(spec, lf0, np.zeros((T, 0)), stage=stage, use_log_gain=True, alpha=alpha, fperiod=fp, tap=True)
+    rows = [O.lsp_coefficients(f, stage, alpha, True) for f in spec]
+    c = O.lsp_coefficients(spec[0], stage, alpha, True, filtered=False).copy()
+    d = np.zeros((stage, M))
+    aa = 1.0 - alpha * alpha
+    out = []
+    n = 0
+    for t in range(T):
+        cinc = (rows[t] - c) / fp
+        for _ in range(fp):
+            x = exc[n] * c[0]
+            for s in range(stage):
+                y = d[s, 0] * c[1]
+                for i in range(1, M - 1):
+                    d[s, i] += alpha * (d[s, i + 1] - d[s, i - 1])
+                    y += d[s, i] * c[i + 1]
+                x -= y
+                d[s, 1:] = d[s, :-1].copy()
+                d[s, 0] = alpha * d[s, 0] + aa * x
+            c = c + cinc
+            out.append(x)
+            n += 1
+        c = rows[t].copy()
+    assert np.array_equal(np.array(out), w)
