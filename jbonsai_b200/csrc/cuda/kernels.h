@@ -181,9 +181,11 @@ int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDe
 // After every wave has run: the largest state mismatch over all cuts -> *worst (device), for the
 // host to compare with its tolerance.
 // `host_mirror` (pinned, device-visible, or nullptr): also stored there by the device, no copy engine.
-// `stride` / `count`: doubles per (segment, side) slot and how many of them are compared.
+// `stride` / `count`: doubles per (segment, side) slot and how many of them are compared. `relative`:
+// every cut's mismatch is divided by max(1, largest |state value| at that cut) (MGLSA: the output scale
+// of an LSP voice is not known in advance).
 int launch_mlsa_seg_check(const MlsaSegments& sg, double* worst, double* host_mirror, cudaStream_t stream,
-                          int stride = kMlsaSegStateDoubles, int count = 5 * 37);
+                          int stride = kMlsaSegStateDoubles, int count = 5 * 37, bool relative = false);
 
 // Stage != 0 (mglsa.cu). launch_lsp_prep: rows of d.b = filter coefficients of every LSP frame of d.mcp
 // (postfilter_lsp(beta), check_lsp_stability, lsp2mgc, mc2b, gnorm, [1..] *= gamma; vocoder/mod.rs:148-155)
@@ -200,8 +202,11 @@ int launch_row_increments(const BatchLayout& b, const VocoderParams& p, const Vo
 constexpr int kMglsaMaxOrder = 36;
 constexpr int kMglsaMaxStage = 8;
 constexpr int mglsa_state_doubles(int stage) { return stage * kMglsaMaxOrder; }
+// `literal`: the tap update as the reference writes it, d[i] += alpha * (d[i+1] - d[i-1]) with separate
+// multiplies and adds (bit-identical to the oracle given the same rows, three dependent operations per tap);
+// otherwise (d[i] + alpha d[i+1]) - alpha d'[i-1] with fused multiply-adds, one operation on the serial path.
 int launch_mglsa(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, const MlsaSegments& sg,
-                 int seg_first, int seg_count, cudaStream_t stream);
+                 int seg_first, int seg_count, bool literal, cudaStream_t stream);
 
 // Streaming: copy frames [frame_begin, frame_begin+frame_count) of every utterance into
 // chunk[n_utt][frame_count*fperiod] (zero padded past the end of an utterance).

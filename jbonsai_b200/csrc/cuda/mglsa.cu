@@ -18,9 +18,13 @@
 //               of one segment form a pipeline one sample apart (section s filters sample n - s at
 //               step n and hands its output to the next lane by shuffle), every lane keeps the
 //               delay line d[0..M) of its section and its own copy of the interpolated coefficients
-//               in registers (their per-sample increments sit in shared memory). The arithmetic is the reference's, operation for operation (separate
-//               multiplies and adds, mglsa.rs:30-40), so a segment without warm-up reproduces the
-//               oracle's filter bit for bit given the same coefficient rows.
+//               in registers (their per-sample increments sit in shared memory). Two flavours of the
+//               tap update: LITERAL follows mglsa.rs:30-34 operation for operation (separate multiplies
+//               and adds; with the oracle's coefficient rows and no warm-up it reproduces the oracle bit
+//               for bit) and costs three dependent FP64 operations per tap; the default computes the same
+//               quantity as (d[i] + alpha d[i+1]) - alpha d'[i-1] with fused multiply-adds, one operation
+//               per tap on the serial path (the filter is a feedback loop: the chain over the taps is
+//               what bounds a warp). The two differ by rounding only, ~1e-13 relative on the output.
 #include "kernels.h"
 
 namespace jbk {
@@ -31,6 +35,12 @@ constexpr int kMaxM = 64;   // k_lsp_prep: largest vector length
 constexpr int kMG = kMglsaMaxOrder;  // k_mglsa: largest vector length held in registers (36)
 constexpr int kCH = 16;     // samples per staged chunk
 constexpr int kWPB = 4;
+
+__device__ __forceinline__ void cp_async8(double* smem_dst, const double* gmem_src) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(sa), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
 
 // Generalized::gnorm / ignorm in place (generalized.rs:6-38), gamma != 0
 __device__ void gnorm_dev(double* c, int n, double gamma) {
@@ -226,7 +236,9 @@ struct WarpShared {
   SlotInfo info[kSlots];
 };
 
-template <int STAGE>
+// MT > 0: the vector length is the compile-time constant MT (the tap loop is straight-line code);
+// MT == 0: any length up to kMG, decided at run time (a branch per tap).
+template <int STAGE, bool LITERAL, int MT>
 __global__ void __launch_bounds__(32 * kWPB, 2)
 k_mglsa(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg_first, int seg_end, int state_stride,
         const double* __restrict__ binc) {
@@ -237,7 +249,7 @@ k_mglsa(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg_f
   const int warp = blockIdx.x * kWPB + (threadIdx.x >> 5);
   if (seg_first + warp * kSlots >= seg_end) return;  // whole warp; warps of a block never sync with each other
   SlotInfo* const info = S.info;
-  const int fp = p.fperiod, M = p.nmcp;
+  const int fp = p.fperiod, M = MT > 0 ? MT : p.nmcp;
 
   for (int k = lane; k < kSlots; k += 32) {
     SlotInfo si;
@@ -265,7 +277,7 @@ k_mglsa(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg_f
   const bool live = lane < kSlots * STAGE;  // 32 % STAGE lanes at the top have no section to run
   const int g = live ? lane / STAGE : kSlots - 1, s = live ? lane - g * STAGE : 0;
   const bool tail = live && s == STAGE - 1;
-  const double a = p.alpha, aa = 1.0 - a * a;
+  const double a = p.alpha, ma = -a, aa = 1.0 - a * a;
   const SlotInfo me = info[g];
   int nfr_max = me.nfr;
 #pragma unroll
@@ -313,11 +325,14 @@ k_mglsa(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg_f
       const int gg = k / kCH, i = k - gg * kCH;
       const SlotInfo& si = info[gg];
       const int n = chunk * kCH + i;
-      S.In[((chunk & 1) * kCH + i) * kSlots + gg] = n < si.nfr * fp ? d.wave[si.in_base + n] : 0.0;
+      double* dst = S.In + ((chunk & 1) * kCH + i) * kSlots + gg;
+      if (n < si.nfr * fp) cp_async8(dst, d.wave + si.in_base + n);  // lands while the next chunk is filtered
+      else *dst = 0.0;
     }
   };
   fill_chunk(0);
   fill_chunk(1);
+  cp_async_wait_all();
   __syncwarp();
 
   const bool my_cut = me.prev >= 0 && live && me.seg >= 0 && sg.state != nullptr;
@@ -348,8 +363,14 @@ k_mglsa(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg_f
         if (i <= M - 2) {
           const double cur_old = old_next;
           old_next = dl[i + 1 < kMG ? i + 1 : i];
-          const double nw = __dadd_rn(cur_old, __dmul_rn(a, __dadd_rn(old_next, -prev_new)));
-          y = __dadd_rn(y, __dmul_rn(nw, c[i]));
+          double nw;
+          if (LITERAL) {  // d[i] += alpha * (d[i+1] - d[i-1]); y += d[i] * c[i+1]   (mglsa.rs:31-34)
+            nw = __dadd_rn(cur_old, __dmul_rn(a, __dadd_rn(old_next, -prev_new)));
+            y = __dadd_rn(y, __dmul_rn(nw, c[i]));
+          } else {  // the same value as (d[i] + alpha d[i+1]) - alpha d'[i-1]: one fused operation on the serial path
+            nw = __fma_rn(ma, prev_new, __fma_rn(a, old_next, cur_old));
+            y = __fma_rn(nw, c[i], y);
+          }
           c[i] = __dadd_rn(c[i], cinc[i * 32]);  // coefficient of the next sample (mod.rs:169-171)
           dl[i] = prev_new;
           prev_new = nw;
@@ -368,6 +389,7 @@ k_mglsa(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg_f
       }
       ++ks;
     }
+    cp_async_wait_all();  // chunk i0 / kCH + 1 has landed
     __syncwarp();
     {  // flush the samples whose last section has run; refill the half of the ring just consumed
       const int chunk = i0 / kCH;
@@ -385,17 +407,25 @@ k_mglsa(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg_f
   if (ks == dump1) dump_state(1);  // one section: the last step of the loop is the last sample
 }
 
-template <int STAGE>
+template <int STAGE, bool LITERAL, int MT>
 int launch_one(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, const MlsaSegments& sg,
                int seg_first, int seg_count, cudaStream_t stream) {
   constexpr int kSlots = 32 / STAGE;
   const int warps = (seg_count + kSlots - 1) / kSlots;
   const size_t smem = sizeof(WarpShared<STAGE>) * kWPB;
-  cudaError_t e = cudaFuncSetAttribute(k_mglsa<STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e =
+      cudaFuncSetAttribute(k_mglsa<STAGE, LITERAL, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return (int)e;
-  k_mglsa<STAGE><<<(warps + kWPB - 1) / kWPB, 32 * kWPB, smem, stream>>>(b, p, d, sg, seg_first, seg_first + seg_count,
-                                                                         mglsa_state_doubles(p.stage), d.binc);
+  k_mglsa<STAGE, LITERAL, MT><<<(warps + kWPB - 1) / kWPB, 32 * kWPB, smem, stream>>>(
+      b, p, d, sg, seg_first, seg_first + seg_count, mglsa_state_doubles(p.stage), d.binc);
   return (int)cudaGetLastError();
+}
+template <int STAGE>
+int launch_either(bool literal, const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,
+                  const MlsaSegments& sg, int seg_first, int seg_count, cudaStream_t stream) {
+  if (literal) return launch_one<STAGE, true, 0>(b, p, d, sg, seg_first, seg_count, stream);
+  if (p.nmcp == 35) return launch_one<STAGE, false, 35>(b, p, d, sg, seg_first, seg_count, stream);  // the shipped order
+  return launch_one<STAGE, false, 0>(b, p, d, sg, seg_first, seg_count, stream);
 }
 
 }  // namespace
@@ -419,20 +449,20 @@ int launch_row_increments(const BatchLayout& b, const VocoderParams& p, const Vo
 }
 
 int launch_mglsa(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, const MlsaSegments& sg,
-                 int seg_first, int seg_count, cudaStream_t stream) {
+                 int seg_first, int seg_count, bool literal, cudaStream_t stream) {
   if (seg_count <= 0) return 0;
   if (p.nmcp < 3 || p.nmcp > kMG || p.fperiod % kCH != 0 || d.out == nullptr || d.out == d.wave ||
       d.b_first == nullptr || d.binc == nullptr || seg_first < 0 || seg_first + seg_count > sg.n_seg)
     return (int)cudaErrorInvalidValue;
   switch (p.stage) {
-    case 1: return launch_one<1>(b, p, d, sg, seg_first, seg_count, stream);
-    case 2: return launch_one<2>(b, p, d, sg, seg_first, seg_count, stream);
-    case 3: return launch_one<3>(b, p, d, sg, seg_first, seg_count, stream);
-    case 4: return launch_one<4>(b, p, d, sg, seg_first, seg_count, stream);
-    case 5: return launch_one<5>(b, p, d, sg, seg_first, seg_count, stream);
-    case 6: return launch_one<6>(b, p, d, sg, seg_first, seg_count, stream);
-    case 7: return launch_one<7>(b, p, d, sg, seg_first, seg_count, stream);
-    case 8: return launch_one<8>(b, p, d, sg, seg_first, seg_count, stream);
+    case 1: return launch_either<1>(literal, b, p, d, sg, seg_first, seg_count, stream);
+    case 2: return launch_either<2>(literal, b, p, d, sg, seg_first, seg_count, stream);
+    case 3: return launch_either<3>(literal, b, p, d, sg, seg_first, seg_count, stream);
+    case 4: return launch_either<4>(literal, b, p, d, sg, seg_first, seg_count, stream);
+    case 5: return launch_either<5>(literal, b, p, d, sg, seg_first, seg_count, stream);
+    case 6: return launch_either<6>(literal, b, p, d, sg, seg_first, seg_count, stream);
+    case 7: return launch_either<7>(literal, b, p, d, sg, seg_first, seg_count, stream);
+    case 8: return launch_either<8>(literal, b, p, d, sg, seg_first, seg_count, stream);
     default: return (int)cudaErrorInvalidValue;
   }
 }

@@ -282,19 +282,26 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
 
 // Compares the two sides of every cut: state of segment g at the top of its own range (after its
 // warm-up from zero) against the end state of the segment before it. max |difference| -> *worst.
-__global__ void k_mlsa_seg_check(MlsaSegments sg, double* worst, int stride, int count) {
+// `relative` (one warp per block): the mismatch is divided by max(1, largest |state| of the true side).
+__global__ void k_mlsa_seg_check(MlsaSegments sg, double* worst, int stride, int count, int relative) {
   const int sid = blockIdx.x;
   const MlsaSegment s = sg.seg[sid];
   if (s.prev < 0) return;
   const double* A = sg.state + ((long long)sid * 2 + 0) * stride;
   const double* B = sg.state + ((long long)s.prev * 2 + 1) * stride;
-  double m = 0.0;
+  double m = 0.0, scale = 1.0;
   for (int i = threadIdx.x; i < count; i += blockDim.x) {
     const double dd = fabs(A[i] - B[i]);
     m = (dd > m || dd != dd) ? (dd != dd ? __longlong_as_double(0x7ff0000000000000ll) : dd) : m;
+    if (relative) scale = fmax(scale, fabs(B[i]));
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if (relative) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) scale = fmax(scale, __shfl_xor_sync(0xffffffffu, scale, o));
+    m = m / scale;  // inf / inf = NaN is caught by the host's !(w <= tol)
+  }
   if ((threadIdx.x & 31) == 0 && m > 0.0)
     atomicMax(reinterpret_cast<unsigned long long*>(worst), (unsigned long long)__double_as_longlong(m));
 }
@@ -325,11 +332,11 @@ int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDe
 }
 
 int launch_mlsa_seg_check(const MlsaSegments& sg, double* worst, double* host_mirror, cudaStream_t stream,
-                          int stride, int count) {
+                          int stride, int count, bool relative) {
   if (sg.n_seg == 0 || worst == nullptr || sg.state == nullptr) return 0;
   cudaError_t e = cudaMemsetAsync(worst, 0, sizeof(double), stream);
   if (e != cudaSuccess) return (int)e;
-  k_mlsa_seg_check<<<sg.n_seg, 64, 0, stream>>>(sg, worst, stride, count);
+  k_mlsa_seg_check<<<sg.n_seg, relative ? 32 : 64, 0, stream>>>(sg, worst, stride, count, relative ? 1 : 0);
   if (host_mirror) k_publish<<<1, 1, 0, stream>>>(worst, host_mirror);
   return (int)cudaGetLastError();
 }

@@ -106,19 +106,32 @@ def test_mglsa_filter_is_bit_exact_on_the_oracles_rows(eng, stage, log_gain):
     lf0 = [lf0_track(T, 50 + i) if i % 2 else np.full(T, -1e10) for i, T in enumerate(lens)]
     lpf = [lpf_track(T) for T in lens]
     rf = [oracle_rows(s, stage, 0.42, log_gain) for s in spec]
-    r = eng.prepare_tracks([x[0] for x in rf], lf0, lpf, stage=stage, use_log_gain=log_gain, alpha=0.42,
-                           first_rows=np.stack([x[1] for x in rf]))
-    tm = r.run()
-    w, off = r.fetch()
-    r.close()
-    assert tm["mlsa_segments"] == len(lens)
-    for i, (s, a, b) in enumerate(zip(spec, lf0, lpf)):
-        ref = O.vocoder_ex(s, a, b, stage=stage, use_log_gain=log_gain, alpha=0.42)
+    refs = [O.vocoder_ex(s, a, b, stage=stage, use_log_gain=log_gain, alpha=0.42) for s, a, b in zip(spec, lf0, lpf)]
+    # variant 0: whole utterances, the reference's operation order (launch_mglsa literal = true)
+    eng.set_mlsa_variant(0)
+    try:
+        r = eng.prepare_tracks([x[0] for x in rf], lf0, lpf, stage=stage, use_log_gain=log_gain, alpha=0.42,
+                               first_rows=np.stack([x[1] for x in rf]))
+        r.run()
+        w, off = r.fetch()
+        r.close()
+    finally:
+        eng.set_mlsa_variant(-1)
+    for i, ref in enumerate(refs):
         assert np.isfinite(ref).all() and np.abs(ref).max() > 1e-3
         if i % 2 == 0:
             assert np.array_equal(w[off[i]:off[i + 1]], ref)
         else:
             assert rel_diff(w[off[i]:off[i + 1]], ref) <= 1e-12
+    # default: time segments (one per utterance here) and the fused tap update: rounding differences only
+    r = eng.prepare_tracks([x[0] for x in rf], lf0, lpf, stage=stage, use_log_gain=log_gain, alpha=0.42,
+                           first_rows=np.stack([x[1] for x in rf]))
+    tm = r.run()
+    w, off = r.fetch()
+    r.close()
+    assert tm["mlsa_segments"] == len(lens) and tm["mlsa_fallback"] == 0
+    for i, ref in enumerate(refs):
+        assert rel_diff(w[off[i]:off[i + 1]], ref) <= 1e-11
 
 
 # Device-side LSP transform. lsp2lpc expands a product of m second-order sections: at m = 35 a 1-ulp
@@ -210,12 +223,11 @@ def test_mglsa_long_utterances_are_cut_and_checked(eng, stage):
     w, off = r.fetch()
     r.close()
     assert tm["mlsa_segments"] > len(lens) and tm["mlsa_fallback"] == 0
-    assert tm["mlsa_cut_worst"] <= 1e-7
+    assert tm["mlsa_cut_worst"] <= 1e-9  # relative to the state's scale for this filter
     for i, (s, a, b) in enumerate(zip(spec, lf0, lpf)):
         ref = O.vocoder_ex(s, a, b, stage=stage, use_log_gain=True, alpha=0.42)
-        assert rel_diff(w[off[i]:off[i + 1]], ref) <= 1e-12
-    # a warm-up too short for this filter is caught by the cut check and repeated on whole utterances,
-    # which is the bit-exact schedule
+        assert rel_diff(w[off[i]:off[i + 1]], ref) <= 1e-10
+    # a warm-up too short for this filter is caught by the cut check and repeated on whole utterances
     eng.set_mlsa_segmenting(5, 1e-7)
     try:
         r = eng.prepare_tracks([x[0] for x in rf], lf0, lpf, **kw)
@@ -227,9 +239,7 @@ def test_mglsa_long_utterances_are_cut_and_checked(eng, stage):
     assert tm["mlsa_fallback"] == 1
     for i, (s, a, b) in enumerate(zip(spec, lf0, lpf)):
         ref = O.vocoder_ex(s, a, b, stage=stage, use_log_gain=True, alpha=0.42)
-        assert rel_diff(w2[off[i]:off[i + 1]], ref) <= 1e-12
-        if i == 1:
-            assert np.array_equal(w2[off[i]:off[i + 1]], ref)
+        assert rel_diff(w2[off[i]:off[i + 1]], ref) <= 1e-10
 
 
 @pytest.mark.parametrize("stage", [0, 2])
