@@ -216,7 +216,8 @@ __global__ void k_row_increments(BatchLayout b, VocoderParams p, VocoderDev d, i
     const int mid = (lo + hi) >> 1;
     if (b.frame_off[mid] <= gf) lo = mid; else hi = mid;
   }
-  const double prev = gf == b.frame_off[lo] ? d.b_first[(int64_t)lo * M + k] : d.b[i - M];
+  // without b_first (stage 0, beta == 0) the first frame starts from its own row: no increment
+  const double prev = gf == b.frame_off[lo] ? (d.b_first ? d.b_first[(int64_t)lo * M + k] : d.b[i]) : d.b[i - M];
   d.binc[i] = (d.b[i] - prev) / (double)p.fperiod;
 }
 
@@ -442,7 +443,7 @@ int launch_lsp_prep(const BatchLayout& b, const VocoderParams& p, const VocoderD
 int launch_row_increments(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, int64_t total_frames,
                           cudaStream_t stream) {
   if (total_frames == 0) return 0;
-  if (d.binc == nullptr || d.b_first == nullptr) return (int)cudaErrorInvalidValue;
+  if (d.binc == nullptr) return (int)cudaErrorInvalidValue;
   const int64_t n = total_frames * p.nmcp;
   k_row_increments<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(b, p, d, total_frames);
   return (int)cudaGetLastError();

@@ -37,6 +37,14 @@
 // exactly the growth in FP64 instructions.
 #include <type_traits>
 
+// 1: read the per-frame coefficient increments from VocoderDev::binc (launch_row_increments) instead of
+// dividing at every frame boundary. Measured on B200: the kernel shrinks from ~2500 to ~900 instructions but
+// runs 5 % slower (32.6 vs 31.0 ms per step; ptxas lands on 255 registers with a spill in the sample loop),
+// so the divisions stay. The MGLSA kernel (mglsa.cu), with fewer live registers, does use the increments.
+#ifndef JB_V3_BINC
+#define JB_V3_BINC 0
+#endif
+
 #include "kernels.h"
 
 namespace jbk {
@@ -148,11 +156,20 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
     // un-filtered first frame
     const double* r0 = (me.warm == 0 && d.b_first != nullptr) ? d.b_first + (long long)info[g].utt * kNM + 1
                                                               : frame_row(-1);
-    const double* r1 = frame_row(0);
+    if (JB_V3_BINC) {
+      const double* ri = d.binc + me.b_base + 1 + (long long)me.warm * kNM;
 #pragma unroll
-    for (int k = 0; k < kTaps; ++k) {
-      c[k] = r0[k];
-      cinc[k] = (r1[k] - c[k]) / fper;
+      for (int k = 0; k < kTaps; ++k) {
+        c[k] = r0[k];
+        cinc[k] = ri[k];
+      }
+    } else {
+      const double* r1 = frame_row(0);
+#pragma unroll
+      for (int k = 0; k < kTaps; ++k) {
+        c[k] = r0[k];
+        cinc[k] = (r1[k] - c[k]) / fper;
+      }
     }
   }
 
@@ -225,12 +242,24 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
     if (--left == 0) {
       left = fp;
       const double* r0 = frame_row(frames_done);
-      const double* r1 = frame_row(frames_done + 1);
       ++frames_done;
+      if (JB_V3_BINC) {  // (cc - coefficients) / fperiod precomputed per frame (launch_row_increments)
+        int f = me.warm + frames_done;
+        const bool past = f > me.last_frame;  // beyond the utterance the coefficients stand still
+        f = past ? me.last_frame : f;
+        const double* ri = d.binc + me.b_base + 1 + (long long)f * kNM;
 #pragma unroll
-      for (int k = 0; k < kTaps; ++k) {
-        c[k] = r0[k];
-        cinc[k] = (r1[k] - c[k]) / fper;
+        for (int k = 0; k < kTaps; ++k) {
+          c[k] = r0[k];
+          cinc[k] = past ? 0.0 : ri[k];
+        }
+      } else {
+        const double* r1 = frame_row(frames_done);
+#pragma unroll
+        for (int k = 0; k < kTaps; ++k) {
+          c[k] = r0[k];
+          cinc[k] = (r1[k] - c[k]) / fper;
+        }
       }
     }
     // ---------------- phase B: Pade combine of df1 then df2 (mlsa.rs:54-79), next stage inputs
@@ -320,6 +349,7 @@ int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDe
                    int seg_first, int seg_count, cudaStream_t stream) {
   if (seg_count <= 0) return 0;
   if (p.nmcp != kNM || p.fperiod % kCH != 0 || d.out == nullptr || d.out == d.wave || seg_first < 0 ||
+      (JB_V3_BINC && d.binc == nullptr) ||
       seg_first + seg_count > sg.n_seg)
     return (int)cudaErrorInvalidValue;
   const int warps = (seg_count + kSlots - 1) / kSlots;

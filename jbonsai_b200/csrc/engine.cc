@@ -421,9 +421,10 @@ struct Engine::Resident {
   // excitation, MLSA (+ cut check for variant 3)
   int launches() const {
     if (from_tracks)
-      return 2 + (rows_given ? 0 : 1) + (vp.stage != 0 ? 1 : 0) + 2 + (segs.n_seg > 0 ? (int)wave_seg_first.size() : 1) +
+      return 2 + (rows_given ? 0 : 1) + (vd.binc ? 1 : 0) + 2 + (segs.n_seg > 0 ? (int)wave_seg_first.size() : 1) +
              (beta > 0.0 ? 2 : 0);
-    int n = 1 + 3 + 2 + 4 + (segs.n_seg > 0 ? (int)wave_seg_first.size() - 1 : 0) + (beta > 0.0 ? 2 : 0);
+    int n = 1 + 3 + 2 + 4 + (segs.n_seg > 0 ? (int)wave_seg_first.size() - 1 : 0) + (beta > 0.0 ? 2 : 0) +
+            (vd.binc ? 1 : 0);
     for (int i = 0; i < 3; ++i) n += gathered[i] ? 1 : 0;
     for (int i = 0; i < streams.n; ++i) n += streams.s[i].has_gv ? 1 : 0;
     // the 1-3-3 window shape runs as k_state_ivar + k_band_build + k_ldl instead of one solve kernel
@@ -750,7 +751,9 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   const bool postfilter = cond.stage == 0 && cond.beta > 0.0 && dim[0] > 2;  // cepstrum.rs:24
   const bool first_rows = postfilter || cond.stage != 0;  // rows the first frame starts from (mod.rs:79-109)
   const size_t w_bfirst = first_rows ? wk.take(n_utt * (size_t)dim[0] * 8) : 0;
-  const size_t w_binc = cond.stage != 0 ? wk.take((size_t)TF * dim[0] * 8) : 0;
+  const bool need_binc = cond.stage != 0;  // the MGLSA kernel reads per-frame increments (MLSA variant 3 was
+                                           // 5 % slower with them: mlsa_seg.cu, JB_V3_BINC)
+  const size_t w_binc = need_binc ? wk.take((size_t)TF * dim[0] * 8) : 0;
   r->d_work = ctx->dalloc(wk.off, &r->work_cap);
   uint8_t* di = (uint8_t*)r->d_in;
   uint8_t* dw = (uint8_t*)r->d_work;
@@ -819,7 +822,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   r->vd.lpf = r->streams.s[2].par;
   r->vd.b = (double*)(dw + w_b);
   r->vd.b_first = first_rows ? (const double*)(dw + w_bfirst) : nullptr;
-  r->vd.binc = cond.stage != 0 ? (double*)(dw + w_binc) : nullptr;
+  r->vd.binc = need_binc ? (double*)(dw + w_binc) : nullptr;
   r->beta = postfilter ? cond.beta : 0.0;
   r->vd.pitch = (double*)(dw + w_pitch);
   r->vd.pulse = (double*)(dw + w_pulse);
@@ -866,6 +869,7 @@ static void launch_spectrum_prep(Engine::Resident* r, cudaStream_t st) {
   if (r->beta > 0.0)  // MelCepstrum::postfilter_mcp (cepstrum.rs:23-37): rewrites vd.b in place
     JB_LAUNCH(jbk::launch_postfilter(r->layout, r->vp, r->vd, r->beta, const_cast<double*>(r->vd.b_first),
                                      r->total_frames, st));
+  if (r->vd.binc) JB_LAUNCH(jbk::launch_row_increments(r->layout, r->vp, r->vd, r->total_frames, st));
 }
 
 // MLPG for the three streams + the per-frame vocoder inputs. The LF0 chain (solve, GV, pitch
@@ -1090,7 +1094,8 @@ Engine::Resident* Engine::prepare_tracks(const VocoderConfig& cfg, size_t n_utt,
   const bool first_rows = postfilter || cfg.stage != 0 || cfg.coefficient_rows;
   r->rows_given = cfg.coefficient_rows;
   const size_t w_bfirst = first_rows ? wk.take(n_utt * M * 8) : 0;
-  const size_t w_binc = cfg.stage != 0 ? wk.take((size_t)TF * M * 8) : 0;
+  const bool need_binc = cfg.stage != 0;
+  const size_t w_binc = need_binc ? wk.take((size_t)TF * M * 8) : 0;
   r->d_work = ctx->dalloc(wk.off, &r->work_cap);
   uint8_t* di = (uint8_t*)r->d_in;
   uint8_t* dw = (uint8_t*)r->d_work;
@@ -1114,7 +1119,7 @@ Engine::Resident* Engine::prepare_tracks(const VocoderConfig& cfg, size_t n_utt,
   r->vd.lpf = (const double*)(di + o_lpf);
   r->vd.b = (double*)(dw + w_b);
   r->vd.b_first = first_rows ? (const double*)(dw + w_bfirst) : nullptr;
-  r->vd.binc = cfg.stage != 0 ? (double*)(dw + w_binc) : nullptr;
+  r->vd.binc = need_binc ? (double*)(dw + w_binc) : nullptr;
   r->vd.pitch = (double*)(dw + w_pitch);
   r->vd.pulse = (double*)(dw + w_pulse);
   r->vd.runs = (int32_t*)(dw + w_runs);
@@ -1158,7 +1163,7 @@ double Engine::run_resident(Resident* r, BatchTimings* tm) const {
       JB_CUDA(cudaMemcpyAsync(r->vd.b, r->vd.mcp, rows, cudaMemcpyDeviceToDevice, c->stream));
       JB_CUDA(cudaMemcpyAsync(const_cast<double*>(r->vd.b_first), (const uint8_t*)r->vd.mcp + rows,
                               (size_t)r->n_utt * r->vp.nmcp * 8, cudaMemcpyDeviceToDevice, c->stream));
-      if (r->vp.stage != 0) JB_LAUNCH(jbk::launch_row_increments(r->layout, r->vp, r->vd, r->total_frames, c->stream));
+      if (r->vd.binc) JB_LAUNCH(jbk::launch_row_increments(r->layout, r->vp, r->vd, r->total_frames, c->stream));
     } else {
       launch_spectrum_prep(r, c->stream);
     }

@@ -15,3 +15,6 @@ timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_ml
   python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline > $O/${TAG}_ncu_full.log 2>&1; echo "ncu full rc=$?"
 tail -3 $O/${TAG}_pytest_gpu.log; cat $O/${TAG}_smoke.log | tail -2; cat $O/${TAG}_bench.json | cut -c1-1500
 timeout 900 python tools/bench_configs.py > $O/${TAG}_configs.jsonl 2> $O/${TAG}_configs.err; echo "configs rc=$?"
+timeout 600 python tools/bench_mglsa.py > $O/${TAG}_mglsa.jsonl 2> $O/${TAG}_mglsa.err; echo "mglsa rc=$?"
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $O/${TAG}_mglsa_launches.csv \
+  python tools/bench_mglsa.py --utts 256 --stages 2 --reps 1 > $O/${TAG}_mglsa_ncu.log 2>&1; echo "ncu mglsa rc=$?"
