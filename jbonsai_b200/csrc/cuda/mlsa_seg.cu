@@ -41,6 +41,13 @@
 // dividing at every frame boundary. Measured on B200: the kernel shrinks from ~2500 to ~900 instructions but
 // runs 5 % slower (32.6 vs 31.0 ms per step; ptxas lands on 255 registers with a spill in the sample loop),
 // so the divisions stay. The MGLSA kernel (mglsa.cu), with fewer live registers, does use the increments.
+// 1: keep the per-sample coefficient increments in shared memory ([tap][lane], conflict-free) instead of 68
+// registers, and build for three blocks per SM. Measured on B200: 240 registers and two warps per scheduler:
+// MLSA 25.4 instead of 21.4 ms (34 more 64-bit shared loads per sample, two wavefronts each); 168 registers and
+// three warps per scheduler (engine.cc kSegWarpsPerSmsp = 3): 116 B of spills, 37 % warm-up, 47 ms per step.
+#ifndef JB_V3_CINC_SMEM
+#define JB_V3_CINC_SMEM 0
+#endif
 #ifndef JB_V3_BINC
 #define JB_V3_BINC 0
 #endif
@@ -88,13 +95,21 @@ struct WarpShared {
   double In[2 * kCH * 8];     // excitation ring: [sample mod 32][slot]
   double Out[kCH * 8];        // output tile: [sample mod 16][slot]
   SlotInfo info[kSlots];
+#if JB_V3_CINC_SMEM
+  double cinc[kTaps * 32];    // per-sample coefficient increments of every lane, [tap][lane]
+#endif
 };
 
 template <int WPB>
-__global__ void __launch_bounds__(32 * WPB, 2)
+__global__ void __launch_bounds__(32 * WPB, JB_V3_CINC_SMEM ? 3 : 2)
 k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg_first, int seg_end,
           const double iaa) {
+#if JB_V3_CINC_SMEM
+  extern __shared__ __align__(16) unsigned char v3_smem[];
+  WarpShared* const sh = reinterpret_cast<WarpShared*>(v3_smem);
+#else
   __shared__ __align__(16) WarpShared sh[WPB];
+#endif
 
   const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int warp = blockIdx.x * WPB + wib;
@@ -150,7 +165,14 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
     f = f < 0 ? 0 : (f > me.last_frame ? me.last_frame : f);
     return brow + (long long)f * kNM;
   };
+#if JB_V3_CINC_SMEM
+  double c[kTaps];
+  double* const cincs = S.cinc + lane;
+#define CINC(k) cincs[(k) * 32]
+#else
   double c[kTaps], cinc[kTaps];
+#define CINC(k) cinc[k]
+#endif
   {
     // the frame before the first is frame 0 itself (mod.rs:79-109); with beta > 0 it is mc2b of the
     // un-filtered first frame
@@ -161,14 +183,14 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
 #pragma unroll
       for (int k = 0; k < kTaps; ++k) {
         c[k] = r0[k];
-        cinc[k] = ri[k];
+        CINC(k) = ri[k];
       }
     } else {
       const double* r1 = frame_row(0);
 #pragma unroll
       for (int k = 0; k < kTaps; ++k) {
         c[k] = r0[k];
-        cinc[k] = (r1[k] - c[k]) / fper;
+        CINC(k) = (r1[k] - c[k]) / fper;
       }
     }
   }
@@ -238,7 +260,7 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
     __syncwarp();
     // coefficients of the next sample (mod.rs:133-135; :140 at a frame end)
 #pragma unroll
-    for (int k = 0; k < kTaps; ++k) c[k] += cinc[k];
+    for (int k = 0; k < kTaps; ++k) c[k] += CINC(k);
     if (--left == 0) {
       left = fp;
       const double* r0 = frame_row(frames_done);
@@ -251,14 +273,14 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
 #pragma unroll
         for (int k = 0; k < kTaps; ++k) {
           c[k] = r0[k];
-          cinc[k] = past ? 0.0 : ri[k];
+          CINC(k) = past ? 0.0 : ri[k];
         }
       } else {
         const double* r1 = frame_row(frames_done);
 #pragma unroll
         for (int k = 0; k < kTaps; ++k) {
           c[k] = r0[k];
-          cinc[k] = (r1[k] - c[k]) / fper;
+          CINC(k) = (r1[k] - c[k]) / fper;
         }
       }
     }
@@ -356,7 +378,13 @@ int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDe
   // 1 - alpha^2 as a parameter: derived in the kernel it was re-computed from the constant bank at the
   // top of every sample (254 registers leave no room to keep it): a load and two dependent FP64
   // operations on the serial path of the filter
-  k_mlsa_v3<kWPB><<<(warps + kWPB - 1) / kWPB, 32 * kWPB, 0, stream>>>(b, p, d, sg, seg_first,
+  size_t smem = 0;
+#if JB_V3_CINC_SMEM
+  smem = sizeof(WarpShared) * kWPB;
+  cudaError_t e = cudaFuncSetAttribute(k_mlsa_v3<kWPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return (int)e;
+#endif
+  k_mlsa_v3<kWPB><<<(warps + kWPB - 1) / kWPB, 32 * kWPB, smem, stream>>>(b, p, d, sg, seg_first,
                                                                         seg_first + seg_count, 1.0 - p.alpha * p.alpha);
   return (int)cudaGetLastError();
 }
