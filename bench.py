@@ -259,10 +259,17 @@ def run_b200(args, rank, world, local):
         barrier()
         n_e2e = max(2, min(args.steps, 5))
         t0 = time.perf_counter()
+        per_step = []
         for _ in range(n_e2e):
+            t1 = time.perf_counter()
             out, _, tm = eng.synthesize_batch_raw(flat)
             jb.lib.jb_free(out)
+            per_step.append(round((time.perf_counter() - t1) * 1e3, 2))
         e2e_ms = (time.perf_counter() - t0) / n_e2e * 1e3
+        print(f"[rank {rank}] e2e ms per step {per_step}; last call: " +
+              ", ".join(f"{k}={tm[k]:.4g}" for k in ("host_frontend_ms", "pack_ms", "h2d_ms", "kernels_ms", "d2h_ms", "mlsa_segments",
+                                                     "mlsa_cut_worst", "mlsa_fallback", "mlsa_repaired")),
+              file=sys.stderr, flush=True)
         e2e_ms = max_over_ranks(e2e_ms)
         e2e = {"value": total_samples / RATE / (e2e_ms * 1e-3), "unit": UNIT,
                "h2d_bytes_per_step": int(sum_over_ranks(tm["h2d_bytes"])),
@@ -307,6 +314,7 @@ def run_b200(args, rank, world, local):
         "segments": int(t.get("mlsa_segments", 0)),
         "warmup_overhead": (t.get("mlsa_seg_frames", 0) / frames - 1.0) if frames else None,
         "cut_check_worst": t.get("mlsa_cut_worst"), "sequential_fallback": int(t.get("mlsa_fallback", 0)),
+        "repaired_segments": int(t.get("mlsa_repaired", 0)),
         "peak_source": "measured live: DFMA micro-kernel (jb_device_measure_peaks); "
                        "MEASURED_PEAKS.json has no FP64 figure",
         "flops_per_sample": MLSA_FLOP_PER_SAMPLE, "msamples_per_s": samples / mlsa_s / 1e6,

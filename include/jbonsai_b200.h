@@ -104,7 +104,9 @@ int jb_engine_synthesize(const jb_engine* e, const char* const* lines, size_t n_
  * [0] host front-end ms [1] pack ms [2] H2D ms [3] kernels ms [4] D2H ms [5] MLPG ms
  * [6] excitation ms [7] MLSA ms [8] H2D bytes [9] D2H bytes [10] frames [11] samples
  * [12] voiced samples [13] kernel launches [14] MLSA time segments [15] frames filtered including
- * warm-up [16] largest state mismatch at a cut [17] 1 if the sequential kernel redid the batch. */
+ * warm-up [16] largest state mismatch at a cut (after a repair pass: of the repaired cuts) [17] passes
+ * redone without cuts by the sequential kernel [18] segments re-filtered with a longer warm-up after
+ * their cut check failed. */
 int jb_engine_synthesize_batch(const jb_engine* e, const char* const* lines, const size_t* line_off,
                                size_t n_utt, double** out, size_t* out_off, double* timings);
 /* The same synthesis delivered as 16-bit PCM: every f64 sample x becomes

@@ -131,7 +131,7 @@ def _take(ptr, n: int) -> np.ndarray:
 TIMING_KEYS = ["host_frontend_ms", "pack_ms", "h2d_ms", "kernels_ms", "d2h_ms", "mlpg_ms",
                "excitation_ms", "mlsa_ms", "h2d_bytes", "d2h_bytes", "frames", "samples",
                "voiced_samples", "launches", "mlsa_segments", "mlsa_seg_frames", "mlsa_cut_worst",
-               "mlsa_fallback"]
+               "mlsa_fallback", "mlsa_repaired"]
 
 
 class Engine:

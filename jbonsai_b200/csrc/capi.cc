@@ -67,7 +67,7 @@ void fill_timings(const jb::BatchTimings& t, double* out) {
                         t.excitation_ms, t.mlsa_ms, (double)t.h2d_bytes, (double)t.d2h_bytes,
                         (double)t.total_frames, (double)t.total_samples, (double)t.voiced_samples,
                         (double)t.launches, (double)t.mlsa_segments, (double)t.mlsa_seg_frames,
-                        t.mlsa_cut_worst, (double)t.mlsa_fallback, 0, 0};
+                        t.mlsa_cut_worst, (double)t.mlsa_fallback, (double)t.mlsa_repaired, 0};
   memcpy(out, v, sizeof v);
 }
 

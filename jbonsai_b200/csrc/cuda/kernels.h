@@ -174,6 +174,7 @@ struct MlsaSegments {
   int n_seg;
   const MlsaSegment* seg;  // [n_seg], six consecutive segments share a warp (host sorts by length)
   double* state;           // [n_seg][2][kMlsaSegStateDoubles] cut-check taps, or nullptr
+  double* mismatch;        // [n_seg] or nullptr: mismatch of every segment's cut (out of launch_mlsa_seg_check)
 };
 // Filters segments [seg_first, seg_first + seg_count) of d.wave into d.out (one launch = one wave).
 int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, const MlsaSegments& sg,
@@ -183,9 +184,11 @@ int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDe
 // `host_mirror` (pinned, device-visible, or nullptr): also stored there by the device, no copy engine.
 // `stride` / `count`: doubles per (segment, side) slot and how many of them are compared. `relative`:
 // every cut's mismatch is divided by max(1, largest |state value| at that cut) (MGLSA: the output scale
-// of an LSP voice is not known in advance).
+// of an LSP voice is not known in advance). `prev_state`: the state array the `prev` ids of `sg` index when it is
+// not sg.state (a repair pass over a few segments, compared with the end states of the original pass).
 int launch_mlsa_seg_check(const MlsaSegments& sg, double* worst, double* host_mirror, cudaStream_t stream,
-                          int stride = kMlsaSegStateDoubles, int count = 5 * 37, bool relative = false);
+                          int stride = kMlsaSegStateDoubles, int count = 5 * 37, bool relative = false,
+                          const double* prev_state = nullptr);
 
 // Stage != 0 (mglsa.cu). launch_lsp_prep: rows of d.b = filter coefficients of every LSP frame of d.mcp
 // (postfilter_lsp(beta), check_lsp_stability, lsp2mgc, mc2b, gnorm, [1..] *= gamma; vocoder/mod.rs:148-155)

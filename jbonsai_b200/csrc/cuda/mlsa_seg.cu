@@ -334,12 +334,16 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
 // Compares the two sides of every cut: state of segment g at the top of its own range (after its
 // warm-up from zero) against the end state of the segment before it. max |difference| -> *worst.
 // `relative` (one warp per block): the mismatch is divided by max(1, largest |state| of the true side).
-__global__ void k_mlsa_seg_check(MlsaSegments sg, double* worst, int stride, int count, int relative) {
+// `prev_state`: the state array the `prev` ids index (nullptr: sg.state itself; a repair pass keeps its own
+// states but is compared with the end states of the original pass). sg.mismatch[sid], when present,
+// receives the mismatch of this segment's cut.
+__global__ void k_mlsa_seg_check(MlsaSegments sg, const double* prev_state, double* worst, int stride, int count,
+                                 int relative) {
   const int sid = blockIdx.x;
   const MlsaSegment s = sg.seg[sid];
   if (s.prev < 0) return;
   const double* A = sg.state + ((long long)sid * 2 + 0) * stride;
-  const double* B = sg.state + ((long long)s.prev * 2 + 1) * stride;
+  const double* B = (prev_state ? prev_state : sg.state) + ((long long)s.prev * 2 + 1) * stride;
   double m = 0.0, scale = 1.0;
   for (int i = threadIdx.x; i < count; i += blockDim.x) {
     const double dd = fabs(A[i] - B[i]);
@@ -353,8 +357,11 @@ __global__ void k_mlsa_seg_check(MlsaSegments sg, double* worst, int stride, int
     for (int o = 16; o > 0; o >>= 1) scale = fmax(scale, __shfl_xor_sync(0xffffffffu, scale, o));
     m = m / scale;  // inf / inf = NaN is caught by the host's !(w <= tol)
   }
-  if ((threadIdx.x & 31) == 0 && m > 0.0)
+  if ((threadIdx.x & 31) == 0 && m > 0.0) {
     atomicMax(reinterpret_cast<unsigned long long*>(worst), (unsigned long long)__double_as_longlong(m));
+    if (sg.mismatch)
+      atomicMax(reinterpret_cast<unsigned long long*>(sg.mismatch + sid), (unsigned long long)__double_as_longlong(m));
+  }
 }
 
 // The result goes to pinned host memory by a plain store from the device: a cudaMemcpy on this
@@ -390,11 +397,12 @@ int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDe
 }
 
 int launch_mlsa_seg_check(const MlsaSegments& sg, double* worst, double* host_mirror, cudaStream_t stream,
-                          int stride, int count, bool relative) {
+                          int stride, int count, bool relative, const double* prev_state) {
   if (sg.n_seg == 0 || worst == nullptr || sg.state == nullptr) return 0;
   cudaError_t e = cudaMemsetAsync(worst, 0, sizeof(double), stream);
+  if (e == cudaSuccess && sg.mismatch) e = cudaMemsetAsync(sg.mismatch, 0, (size_t)sg.n_seg * sizeof(double), stream);
   if (e != cudaSuccess) return (int)e;
-  k_mlsa_seg_check<<<sg.n_seg, relative ? 32 : 64, 0, stream>>>(sg, worst, stride, count, relative ? 1 : 0);
+  k_mlsa_seg_check<<<sg.n_seg, relative ? 32 : 64, 0, stream>>>(sg, prev_state, worst, stride, count, relative ? 1 : 0);
   if (host_mirror) k_publish<<<1, 1, 0, stream>>>(worst, host_mirror);
   return (int)cudaGetLastError();
 }

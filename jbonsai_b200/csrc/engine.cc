@@ -413,6 +413,9 @@ struct Engine::Resident {
   std::vector<int32_t> wave_utt_first;  // [waves+1] utterance range whose output that launch completes
   double beta = 0.0;               // > 0: post-filter kernels run after frame_prep
   bool used_fallback = false;      // the last pass re-ran the sequential kernel
+  int repaired_segments = 0;       // the last pass re-filtered this many segments with a longer warm-up
+  std::vector<jbk::MlsaSegment> seg_table;  // host copy of segs.seg (for the repair pass)
+  int warm_frames = 0;             // warm-up the segments were cut with
   bool copied_by_waves = false;    // the last pass already queued its device-to-host copies
   cudaEvent_t kernels_end = nullptr;  // recorded after the last kernel of the last pass (variant 3)
   double* h_worst = nullptr;          // pinned word the last pass copies its cut-check result to
@@ -748,6 +751,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
       cond.stage != 0 ? (size_t)jbk::mglsa_state_doubles((int)cond.stage) : (size_t)jbk::kMlsaSegStateDoubles;
   const size_t w_segstate = segs.empty() ? 0 : wk.take(segs.size() * 2 * seg_state_doubles * 8);
   const size_t w_worst = wk.take(8);
+  const size_t w_segmis = segs.empty() ? 0 : wk.take(segs.size() * 8);
   const bool postfilter = cond.stage == 0 && cond.beta > 0.0 && dim[0] > 2;  // cepstrum.rs:24
   const bool first_rows = postfilter || cond.stage != 0;  // rows the first frame starts from (mod.rs:79-109)
   const size_t w_bfirst = first_rows ? wk.take(n_utt * (size_t)dim[0] * 8) : 0;
@@ -833,6 +837,9 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   r->segs.n_seg = (int)segs.size();
   r->segs.seg = (const jbk::MlsaSegment*)(di + o_segs);
   r->segs.state = segs.empty() ? nullptr : (double*)(dw + w_segstate);
+  r->segs.mismatch = segs.empty() ? nullptr : (double*)(dw + w_segmis);
+  r->seg_table = segs;
+  r->warm_frames = (int)(e.mlsa_warm_frames * (cond.stage != 0 ? kMglsaWarmFactor : 1));
   r->whole.n_seg = (int)whole.size();
   r->whole.seg = (const jbk::MlsaSegment*)(di + o_whole);
   r->whole.state = nullptr;
@@ -912,6 +919,7 @@ static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_exc
   if (after_exc) JB_CUDA(cudaEventRecord(after_exc, st));
   r->result = r->vd.wave;
   r->used_fallback = false;
+  r->repaired_segments = 0;
   r->copied_by_waves = false;
   r->kernels_end = nullptr;
   if (stop_after_excitation) return;
@@ -979,6 +987,67 @@ static bool mlsa_cut_check_failed(Engine::Resident* r, double tol) {
   const double w = r->h_worst ? *r->h_worst : 0.0;
   return !(w <= tol);  // NaN counts as a failed cut
 }
+// A failed cut check, first resort: the segments whose cut disagrees are filtered again with four times the
+// warm-up and checked against the same end states; the rest of the batch stands. `touched` receives the
+// utterances whose output changed. Returns false when that is not possible or not enough (many failing
+// cuts, or a repaired cut still off): the caller then redoes the whole batch without cuts.
+static bool mlsa_repair_segments(Engine::Resident* r, double tol, std::vector<int32_t>* touched) {
+  DeviceCtx* c = r->ctx;
+  cudaStream_t st = c->stream;
+  const int n = r->segs.n_seg;
+  if (n == 0 || r->segs.mismatch == nullptr || (int)r->seg_table.size() != n || r->h_worst == nullptr) return false;
+  if (r->vp.stage != 0) tol = std::min(tol, kMglsaCutRelTolerance);
+  std::vector<double> mis((size_t)n);
+  JB_CUDA(cudaMemcpy(mis.data(), r->segs.mismatch, (size_t)n * 8, cudaMemcpyDeviceToHost));
+  std::vector<jbk::MlsaSegment> fix;
+  for (int i = 0; i < n; ++i)
+    if (r->seg_table[(size_t)i].prev >= 0 && !(mis[(size_t)i] <= tol)) {
+      jbk::MlsaSegment s = r->seg_table[(size_t)i];  // `prev` keeps indexing the original pass's states
+      s.warm = std::max<int32_t>(0, s.begin - 4 * std::max(1, r->warm_frames));
+      fix.push_back(s);
+    }
+  if (fix.empty() || (int)fix.size() > std::max(16, n / 16)) return false;
+  std::stable_sort(fix.begin(), fix.end(), [](const jbk::MlsaSegment& a, const jbk::MlsaSegment& b) {
+    return a.end - a.warm > b.end - b.warm;
+  });
+  const bool mg = r->vp.stage != 0;
+  const size_t stride = mg ? (size_t)jbk::mglsa_state_doubles(r->vp.stage) : (size_t)jbk::kMlsaSegStateDoubles;
+  Carver wk;
+  const size_t o_tab = wk.take(fix.size() * sizeof(jbk::MlsaSegment));
+  const size_t o_state = wk.take(fix.size() * 2 * stride * 8);
+  size_t cap = 0;
+  uint8_t* d = (uint8_t*)c->dalloc(wk.off, &cap);
+  bool ok = false;
+  try {
+    JB_CUDA(cudaMemcpyAsync(d + o_tab, fix.data(), fix.size() * sizeof(jbk::MlsaSegment), cudaMemcpyHostToDevice, st));
+    jbk::MlsaSegments sg{};
+    sg.n_seg = (int)fix.size();
+    sg.seg = (const jbk::MlsaSegment*)(d + o_tab);
+    sg.state = (double*)(d + o_state);
+    sg.mismatch = nullptr;
+    if (mg) JB_LAUNCH(jbk::launch_mglsa(r->layout, r->vp, r->vd, sg, 0, sg.n_seg, false, st));
+    else JB_LAUNCH(jbk::launch_mlsa_v3(r->layout, r->vp, r->vd, sg, 0, sg.n_seg, st));
+    const int cnt = mg ? (int)stride : 5 * 37;
+    JB_LAUNCH(jbk::launch_mlsa_seg_check(sg, r->d_worst, r->h_worst, st, (int)stride, cnt, mg, r->segs.state));
+    JB_CUDA(cudaStreamSynchronize(st));  // `fix` and the scratch stay alive until here
+    ok = *r->h_worst <= tol;
+  } catch (...) {
+    cudaStreamSynchronize(st);
+    c->dfree(d, cap);
+    throw;
+  }
+  c->dfree(d, cap);
+  if (!ok) return false;
+  r->repaired_segments = (int)fix.size();
+  if (touched) {
+    touched->clear();
+    for (const jbk::MlsaSegment& s : fix) touched->push_back(s.utt);
+    std::sort(touched->begin(), touched->end());
+    touched->erase(std::unique(touched->begin(), touched->end()), touched->end());
+  }
+  return true;
+}
+
 static void mlsa_sequential_rerun(Engine::Resident* r) {
   cudaStream_t st = r->ctx->stream;
   if (r->vp.stage != 0) {
@@ -1090,6 +1159,7 @@ Engine::Resident* Engine::prepare_tracks(const VocoderConfig& cfg, size_t n_utt,
       cfg.stage != 0 ? (size_t)jbk::mglsa_state_doubles((int)cfg.stage) : (size_t)jbk::kMlsaSegStateDoubles;
   const size_t w_segstate = wk.take(plan.segs.size() * 2 * seg_state_doubles * 8);
   const size_t w_worst = wk.take(8);
+  const size_t w_segmis = wk.take(plan.segs.size() * 8);
   const bool postfilter = cfg.stage == 0 && cfg.beta > 0.0 && M > 2;
   const bool first_rows = postfilter || cfg.stage != 0 || cfg.coefficient_rows;
   r->rows_given = cfg.coefficient_rows;
@@ -1131,6 +1201,9 @@ Engine::Resident* Engine::prepare_tracks(const VocoderConfig& cfg, size_t n_utt,
   r->segs.n_seg = (int)plan.segs.size();
   r->segs.seg = (const jbk::MlsaSegment*)(di + o_segs);
   r->segs.state = plan.segs.empty() ? nullptr : (double*)(dw + w_segstate);
+  r->segs.mismatch = plan.segs.empty() ? nullptr : (double*)(dw + w_segmis);
+  r->seg_table = plan.segs;
+  r->warm_frames = (int)(mlsa_warm_frames * (cfg.stage != 0 ? kMglsaWarmFactor : 1));
   r->whole.n_seg = (int)whole.size();
   r->whole.seg = (const jbk::MlsaSegment*)(di + o_whole);
   r->d_worst = (double*)(dw + w_worst);
@@ -1175,7 +1248,7 @@ double Engine::run_resident(Resident* r, BatchTimings* tm) const {
   JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
   JB_CUDA(cudaEventSynchronize(c->ev[5]));
   if (mlsa_cut_check_failed(r, mlsa_cut_tolerance)) {  // timed too: ev[5] is recorded again
-    mlsa_sequential_rerun(r);
+    if (!mlsa_repair_segments(r, mlsa_cut_tolerance, nullptr)) mlsa_sequential_rerun(r);
     JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
     JB_CUDA(cudaEventSynchronize(c->ev[5]));
   }
@@ -1198,6 +1271,7 @@ double Engine::run_resident(Resident* r, BatchTimings* tm) const {
     tm->mlsa_seg_frames = r->seg_frames;
     tm->mlsa_cut_worst = (r->segs.n_seg > 0 && r->h_worst) ? *r->h_worst : 0.0;
     tm->mlsa_fallback = r->used_fallback ? 1 : 0;
+    tm->mlsa_repaired = r->repaired_segments;
   }
   return total;
 }
@@ -1391,6 +1465,21 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
         }
       };
 
+      auto copy_utterance = [&](Chunk& ch, size_t u) {  // utterance u of the chunk (chunk-relative index)
+        Resident* r = ch.r;
+        const int64_t n0 = r->frame_off[u] * r->vp.fperiod, n1 = r->frame_off[u + 1] * r->vp.fperiod;
+        if (n1 <= n0) return;
+        if (pcm16) {
+          int16_t* dev16 = reinterpret_cast<int16_t*>(r->vd.pulse);
+          JB_LAUNCH(jbk::launch_pcm16(r->result + n0, dev16 + n0, n1 - n0, c->stream));
+          JB_CUDA(cudaMemcpyAsync(host16 + (*out_off)[ch.u0] + n0, dev16 + n0, (size_t)(n1 - n0) * 2,
+                                  cudaMemcpyDeviceToHost, c->stream));
+        } else {
+          JB_CUDA(cudaMemcpyAsync(host + (*out_off)[ch.u0] + n0, r->result + n0, (size_t)(n1 - n0) * 8,
+                                  cudaMemcpyDeviceToHost, c->stream));
+        }
+      };
+
       for (size_t q = 0; q < nchunks; ++q) {
         Chunk ch;
         ch.u0 = ccut[q];
@@ -1461,10 +1550,17 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
         Resident* r = ch.r;
         c->use_slot(ch.slot);
         if (mlsa_cut_check_failed(r, mlsa_cut_tolerance)) {
-          // the copies above carried a waveform with a bad cut: redo the filter sequentially, copy again
-          mlsa_sequential_rerun(r);
-          JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
-          copy_result(ch);
+          // the copies above carried a waveform with a bad cut: re-filter the segments behind the failing
+          // cuts and copy their utterances again; if that does not settle it, the whole chunk without cuts
+          std::vector<int32_t> touched;
+          if (mlsa_repair_segments(r, mlsa_cut_tolerance, &touched)) {
+            JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
+            for (int32_t u : touched) copy_utterance(ch, (size_t)u);
+          } else {
+            mlsa_sequential_rerun(r);
+            JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
+            copy_result(ch);
+          }
           JB_CUDA(cudaEventRecord(c->ev[6], c->stream));
           JB_CUDA(cudaStreamSynchronize(c->stream));
         }
@@ -1473,8 +1569,9 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
         const double worst = r->segs.n_seg > 0 && r->h_worst && !(dbg && dbg->stop_after_excitation) ? *r->h_worst : 0.0;
         t.mlsa_cut_worst = std::max(t.mlsa_cut_worst, worst);
         t.mlsa_fallback += r->used_fallback ? 1 : 0;
+        t.mlsa_repaired += r->repaired_segments;
         float f = 0;
-        cudaEvent_t kend = (r->kernels_end && !r->used_fallback) ? r->kernels_end : c->ev[5];
+        cudaEvent_t kend = (r->kernels_end && !r->used_fallback && !r->repaired_segments) ? r->kernels_end : c->ev[5];
         JB_CUDA(cudaEventElapsedTime(&f, c->ev[0], c->ev[1])); t.h2d_ms += f;
         JB_CUDA(cudaEventElapsedTime(&f, c->ev[2], c->ev[3])); t.mlpg_ms += f;
         JB_CUDA(cudaEventElapsedTime(&f, c->ev[3], c->ev[4])); t.excitation_ms += f;
@@ -1493,7 +1590,7 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
         Chunk& z = chunks.back();
         cudaEvent_t* eva = c->evsets[a.slot];
         cudaEvent_t* evz = c->evsets[z.slot];
-        cudaEvent_t kend = (z.r->kernels_end && !z.r->used_fallback) ? z.r->kernels_end : evz[5];
+        cudaEvent_t kend = (z.r->kernels_end && !z.r->used_fallback && !z.r->repaired_segments) ? z.r->kernels_end : evz[5];
         float f = 0;
         JB_CUDA(cudaEventElapsedTime(&f, eva[2], kend)); t.kernels_ms = f;
         JB_CUDA(cudaEventElapsedTime(&f, kend, evz[6])); t.d2h_ms = f > 0 ? f : 0;
@@ -1540,6 +1637,7 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
       tm->mlsa_seg_frames += t.mlsa_seg_frames;
       tm->mlsa_cut_worst = std::max(tm->mlsa_cut_worst, t.mlsa_cut_worst);
       tm->mlsa_fallback += t.mlsa_fallback;
+      tm->mlsa_repaired += t.mlsa_repaired;
     }
   }
   *out = host_raw;

@@ -40,6 +40,7 @@ struct BatchTimings {
   int64_t mlsa_segments = 0, mlsa_seg_frames = 0;
   double mlsa_cut_worst = 0;
   int mlsa_fallback = 0;
+  int mlsa_repaired = 0;  // segments re-filtered with a longer warm-up after a failed cut check
 };
 
 class Engine {

@@ -353,6 +353,30 @@ def test_segmented_filter_tohoku_stays_segmented(genji_labels):
     assert np.abs(w - o.synthesize(labels, fma=True)).max() <= WAVE_ATOL
 
 
+def test_segmented_filter_repairs_a_few_bad_cuts(genji_labels, orc):
+    # 8 frames of warm-up leave the cuts of this utterance off by more than the tolerance; with only a
+    # handful of them the segments behind them are filtered again with 4 x the warm-up, checked again,
+    # and only their utterance is copied again: no sequential pass, same result
+    labels = genji_labels[:22]
+    e = jb.Engine.load([NITECH])
+    e.set_mlsa_segmenting(8, 1e-7)
+    ow = orc.synthesize(labels, fma=True)
+    short = orc.synthesize(SAMPLE_SENTENCE_1, fma=True)
+    tm = {}
+    w, off = e.synthesize_batch([SAMPLE_SENTENCE_1, labels], timings=tm)
+    assert tm["mlsa_repaired"] > 0 and tm["mlsa_fallback"] == 0 and tm["mlsa_cut_worst"] <= 1e-7
+    assert np.abs(w[off[1]:off[2]] - ow).max() <= WAVE_ATOL
+    assert np.abs(w[off[0]:off[1]] - short).max() <= WAVE_ATOL
+    p, poff = e.synthesize_batch_pcm16([SAMPLE_SENTENCE_1, labels])
+    assert np.array_equal(p, np.trunc(np.clip(w, -32768.0, 32767.0)).astype(np.int16))
+    r = e.prepare([SAMPLE_SENTENCE_1, labels])
+    t = r.run()
+    assert t["mlsa_repaired"] > 0 and t["mlsa_fallback"] == 0
+    w2, _ = r.fetch()
+    assert np.abs(w2 - w).max() <= SCHED_ATOL
+    r.close()
+
+
 def test_segmented_filter_short_warmup_falls_back(genji_labels, orc):
     # 2 frames of warm-up cannot converge: the cut check must see it and the sequential kernel
     # must redo the batch, so the result is still right
