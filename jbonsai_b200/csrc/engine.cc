@@ -30,6 +30,7 @@ namespace jb {
 namespace {
 
 constexpr int kSegWarpsPerSmsp = 2;  // resident warps per scheduler of k_mlsa_v3 (206 registers)
+constexpr int kRepairWarmFactor = 2;
 constexpr double kMglsaCutRelTolerance = 1e-9;
 constexpr int kMglsaWarmFactor = 2;  // stage != 0: the all-pole MGLSA filter of an LSP frame forgets more slowly than the
                                      // MLSA filter (synthetic tracks: 40 frames leave 1e0, 80 frames 1e-12 at the cuts)
@@ -987,8 +988,8 @@ static bool mlsa_cut_check_failed(Engine::Resident* r, double tol) {
   const double w = r->h_worst ? *r->h_worst : 0.0;
   return !(w <= tol);  // NaN counts as a failed cut
 }
-// A failed cut check, first resort: the segments whose cut disagrees are filtered again with four times the
-// warm-up and checked against the same end states; the rest of the batch stands. `touched` receives the
+// A failed cut check, first resort: the segments whose cut disagrees are filtered again with twice the
+// warm-up (a lone segment is a serial chain: every extra warm-up frame is 0.12 ms of latency) and checked against the same end states; the rest of the batch stands. `touched` receives the
 // utterances whose output changed. Returns false when that is not possible or not enough (many failing
 // cuts, or a repaired cut still off): the caller then redoes the whole batch without cuts.
 static bool mlsa_repair_segments(Engine::Resident* r, double tol, std::vector<int32_t>* touched) {
@@ -1003,7 +1004,7 @@ static bool mlsa_repair_segments(Engine::Resident* r, double tol, std::vector<in
   for (int i = 0; i < n; ++i)
     if (r->seg_table[(size_t)i].prev >= 0 && !(mis[(size_t)i] <= tol)) {
       jbk::MlsaSegment s = r->seg_table[(size_t)i];  // `prev` keeps indexing the original pass's states
-      s.warm = std::max<int32_t>(0, s.begin - 4 * std::max(1, r->warm_frames));
+      s.warm = std::max<int32_t>(0, s.begin - kRepairWarmFactor * std::max(1, r->warm_frames));
       fix.push_back(s);
     }
   if (fix.empty() || (int)fix.size() > std::max(16, n / 16)) return false;

@@ -355,7 +355,7 @@ def test_segmented_filter_tohoku_stays_segmented(genji_labels):
 
 def test_segmented_filter_repairs_a_few_bad_cuts(genji_labels, orc):
     # 8 frames of warm-up leave the cuts of this utterance off by more than the tolerance; with only a
-    # handful of them the segments behind them are filtered again with 4 x the warm-up, checked again,
+    # handful of them the segments behind them are filtered again with a longer warm-up, checked again,
     # and only their utterance is copied again: no sequential pass, same result
     labels = genji_labels[:22]
     e = jb.Engine.load([NITECH])
