@@ -177,8 +177,11 @@ struct MlsaSegments {
   double* mismatch;        // [n_seg] or nullptr: mismatch of every segment's cut (out of launch_mlsa_seg_check)
 };
 // Filters segments [seg_first, seg_first + seg_count) of d.wave into d.out (one launch = one wave).
+// `f64_tail`: how many warm-up frames in front of the own range run in double precision; the warm-up frames
+// before them run the same recurrence in FP32 (their output is discarded and their rounding error fades
+// below the cut tolerance over the tail; the cut check sees the result). < 0: all of the warm-up in FP64.
 int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, const MlsaSegments& sg,
-                   int seg_first, int seg_count, cudaStream_t stream);
+                   int seg_first, int seg_count, cudaStream_t stream, int f64_tail = -1);
 // After every wave has run: the largest state mismatch over all cuts -> *worst (device), for the
 // host to compare with its tolerance.
 // `host_mirror` (pinned, device-visible, or nullptr): also stored there by the device, no copy engine.

@@ -51,6 +51,31 @@
 #ifndef JB_V3_BINC
 #define JB_V3_BINC 0
 #endif
+// 1 (default): the mc2b rows a frame boundary needs are staged in shared memory by cp.async one frame ahead.
+// With 254 live registers ptxas cannot keep more than a few global loads in flight at the boundary, so the 68
+// row loads ran one after another at L2/HBM latency: ~15 % of the kernel's stall samples sat in that block
+// (ncu source page, r1e), for code that runs once per 240 samples.
+#ifndef JB_V3_ROWS_SMEM
+#define JB_V3_ROWS_SMEM 1
+#endif
+// 1: the first own0 - f64_tail warm-up frames of a warp run in FP32 (launch_mlsa_v3's f64_tail). Measured on
+// B200 (bench batch, W = 40): the FP32 head leaves ~0.6 absolute in the worst cut's taps (states reach 1e4;
+// rounding accumulates over the filter's memory) and the worst cut sheds only 0.19 decades per FP64 frame:
+// mismatch 1.2e-5 / 3.6e-4 / 5.5e-3 / 0.11 with 20 / 12 / 8 / 4 double-precision frames behind it, against a
+// tolerance of 1e-7 - it would take 36 of the 40 frames. Off.
+#ifndef JB_V3_F32_HEAD
+#define JB_V3_F32_HEAD 0
+#endif
+// How many of the 34 coefficient additions stay in front of the exchange loads (34: all, the first layout).
+// The additions do not depend on the exchange, so the ones behind the loads fill the loads' latency; each
+// load kept in flight across them costs two registers of a kernel that sits at the cap.
+// 1: the frame-end block sits inside the sample step (first layout); 0: after the chunk's sample loop.
+#ifndef JB_V3_BOUNDARY_IN_STEP
+#define JB_V3_BOUNDARY_IN_STEP 1
+#endif
+#ifndef JB_V3_CADD_FRONT
+#define JB_V3_CADD_FRONT 34
+#endif
 
 #include "kernels.h"
 
@@ -94,6 +119,9 @@ struct WarpShared {
   double F[2][32];            // df1 section outputs
   double In[2 * kCH * 8];     // excitation ring: [sample mod 32][slot]
   double Out[kCH * 8];        // output tile: [sample mod 16][slot]
+#if JB_V3_ROWS_SMEM
+  double R[2][kTaps * 8];     // mc2b rows of frames f and f + 1 of every slot, [frame parity][tap][slot]
+#endif
   SlotInfo info[kSlots];
 #if JB_V3_CINC_SMEM
   double cinc[kTaps * 32];    // per-sample coefficient increments of every lane, [tap][lane]
@@ -103,7 +131,7 @@ struct WarpShared {
 template <int WPB>
 __global__ void __launch_bounds__(32 * WPB, JB_V3_CINC_SMEM ? 3 : 2)
 k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg_first, int seg_end,
-          const double iaa) {
+          const double iaa, const int f64_tail) {
 #if JB_V3_CINC_SMEM
   extern __shared__ __align__(16) unsigned char v3_smem[];
   WarpShared* const sh = reinterpret_cast<WarpShared*>(v3_smem);
@@ -215,6 +243,24 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
       else *dst = 0.0;
     }
   };
+#if JB_V3_ROWS_SMEM
+  auto stage_row = [&](int frame_rel) {  // row `frame_rel` (relative to warm) of all six slots -> S.R[parity]
+    double* const dst = S.R[frame_rel & 1];
+#pragma unroll
+    for (int r = 0; r < (kSlots * kTaps + 31) / 32; ++r) {
+      const int idx = lane + 32 * r;
+      if (idx < kSlots * kTaps) {
+        const int gg = idx / kTaps, k = idx - kTaps * gg;
+        const SlotInfo& si = info[gg];
+        int f = si.warm + frame_rel;
+        f = f < 0 ? 0 : (f > si.last_frame ? si.last_frame : f);
+        cp_async8s(dst + k * 8 + gg, d.b + si.b_base + 1 + (long long)f * kNM + k);
+      }
+    }
+  };
+  stage_row(0);
+  stage_row(1);
+#endif
   fill_chunk(0);
   if (kCH < nsmp_max) fill_chunk(1);
   cp_async_wait_all_s();
@@ -231,7 +277,160 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
   };
 
   int left = fp, frames_done = 0;
+  int i0_start = 0;
   const double* inp = S.In + g;
+#if JB_V3_ROWS_SMEM && JB_V3_F32_HEAD
+  // ---- single-precision head of the warm-up. The output of the warm-up frames is discarded and what the
+  // state keeps of an early frame decays by >= 0.2 decades per frame, so the first own0 - f64_tail warm-up
+  // frames of a warp whose six segments all start at a cut run the same recurrence in FP32 (four times the
+  // issue rate, half the chain latency); the rounding error it leaves (~1e-6 relative) fades below the cut
+  // tolerance over the f64_tail double-precision frames that follow. Nothing is assumed here either: the cut
+  // check compares the state at the top of the own range with the true one as before.
+  int n32 = 0x7fffffff;
+  if (lane < 30 && me.seg >= 0 && me.nfr > 0) n32 = max(0, me.own0 - f64_tail);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) n32 = min(n32, __shfl_xor_sync(0xffffffffu, n32, o));
+  if (f64_tail < 0 || n32 == 0x7fffffff) n32 = 0;
+  if (n32 > 0) {
+    float t32[kTaps], c32[kTaps], ci32[kTaps];
+#pragma unroll
+    for (int k = 0; k < kTaps; ++k) {
+      t32[k] = 0.f;
+      c32[k] = (float)c[k];
+      ci32[k] = (float)CINC(k);
+    }
+    float d11s = 0.f, gins = 0.f, uins = 0.f;
+    const float af = (float)a, maf = -af, iaaf = (float)iaa;
+    const float q1 = (float)pp1, q2 = (float)pp2, q3 = (float)pp3, q4 = (float)pp4, q5 = (float)pp5;
+    auto step32 = [&](float* __restrict__ Y, float* __restrict__ F, int jin) {
+      float po = t32[0];
+      float pn = __fmaf_rn(af, po, iaaf * uins);
+      t32[0] = pn;
+      float y0 = 0.f, y1 = 0.f;
+#pragma unroll
+      for (int i = 1; i < kTaps; i += 2) {
+        float q = __fmaf_rn(af, t32[i], po);
+        po = t32[i];
+        pn = __fmaf_rn(maf, pn, q);
+        t32[i] = pn;
+        y0 = __fmaf_rn(c32[i], pn, y0);
+        if (i + 1 < kTaps) {
+          q = __fmaf_rn(af, t32[i + 1], po);
+          po = t32[i + 1];
+          pn = __fmaf_rn(maf, pn, q);
+          t32[i + 1] = pn;
+          y1 = __fmaf_rn(c32[i + 1], pn, y1);
+        }
+      }
+      d11s = __fmaf_rn(af, d11s, iaaf * gins);
+      Y[lane] = y0 + y1;
+      F[lane] = d11s * c32[0];
+      __syncwarp();
+#pragma unroll
+      for (int k = 0; k < kTaps; ++k) c32[k] += ci32[k];
+      const float y1v = Y[g5], y2v = Y[g5 + 1], y3v = Y[g5 + 2], y4v = Y[g5 + 3], y5v = Y[g5 + 4];
+      const float f1v = F[g5], f2v = F[g5 + 1], f3v = F[g5 + 2], f4v = F[g5 + 3], f5v = F[g5 + 4];
+      const float yprev = Y[prev_lane], fprev = F[prev_lane];
+      const float e = (float)inp[jin * 8];
+      const float Af = __fmaf_rn(q5, f5v, __fmaf_rn(q3, f3v, q1 * f1v));
+      const float Bf = __fmaf_rn(q4, f4v, q2 * f2v);
+      const float Ay = __fmaf_rn(q5, y5v, __fmaf_rn(q3, y3v, q1 * y1v));
+      const float By = __fmaf_rn(q4, y4v, q2 * y2v);
+      const float d120 = (e + Af) - Bf;
+      const float x1 = __fmaf_rn(2.f, Af, e);
+      const float d220 = (x1 + Ay) - By;
+      gins = s == 0 ? d120 : fprev;
+      uins = s == 0 ? d220 : yprev;
+    };
+    float* const Y32 = reinterpret_cast<float*>(&S.Y[0][0]);  // [2][32] floats in the space of S.Y[0]
+    float* const F32 = reinterpret_cast<float*>(&S.F[0][0]);
+    const int n32_smp = n32 * fp;
+    for (int i0 = 0; i0 < n32_smp; i0 += kCH) {
+      const int ring = (i0 & kCH);
+#pragma unroll 1
+      for (int j = 0; j < kCH; j += 2) {
+        step32(Y32, F32, ring + j);
+        step32(Y32 + 32, F32 + 32, ring + j + 1);
+      }
+      left -= kCH;
+      bool restage = false;
+      if (left == 0) {  // frame end: rows from shared memory as in the double-precision part
+        left = fp;
+        if (frames_done + 1 < n32) {
+          const double* r0 = S.R[frames_done & 1] + g;
+          const double* r1 = S.R[(frames_done + 1) & 1] + g;
+#pragma unroll
+          for (int k = 0; k < kTaps; ++k) {
+            const double cc = r0[k * 8];
+            c32[k] = (float)cc;
+            ci32[k] = (float)((r1[k * 8] - cc) / fper);
+          }
+          restage = true;
+        }  // the last frame end hands over to double precision below, outside this loop
+        ++frames_done;
+      }
+      cp_async_wait_all_s();
+      __syncwarp();
+      if ((i0 / kCH + 2) * kCH < nsmp_max) fill_chunk(i0 / kCH + 2);
+      if (restage) stage_row(frames_done + 1);
+      __syncwarp();
+    }
+    {  // hand-over: double-precision coefficients of the first FP64 frame (the frame end skipped above)
+      const double* r0 = S.R[(n32 - 1) & 1] + g;
+      const double* r1 = S.R[n32 & 1] + g;
+#pragma unroll
+      for (int k = 0; k < kTaps; ++k) {
+        c[k] = r0[k * 8];
+        CINC(k) = (r1[k * 8] - c[k]) / fper;
+      }
+      __syncwarp();
+      stage_row(n32 + 1);  // waited for at the end of the next chunk
+    }
+#pragma unroll
+    for (int k = 0; k < kTaps; ++k) t[k] = (double)t32[k];
+    d11 = (double)d11s;
+    gin = (double)gins;
+    uin = (double)uins;
+    i0_start = n32_smp;
+  }
+#endif
+
+  bool staged = false;
+  auto frame_end = [&]() {  // mod.rs:140: the coefficients restart from mc2b of the frame just filtered
+    left = fp;
+#if JB_V3_ROWS_SMEM
+    const double* r0 = S.R[frames_done & 1] + g;
+    const double* r1 = S.R[(frames_done + 1) & 1] + g;
+    ++frames_done;
+#pragma unroll
+    for (int k = 0; k < kTaps; ++k) {
+      c[k] = r0[k * 8];
+      CINC(k) = (r1[k * 8] - c[k]) / fper;
+    }
+    staged = true;
+#else
+    const double* r0 = frame_row(frames_done);
+    ++frames_done;
+    if (JB_V3_BINC) {  // (cc - coefficients) / fperiod precomputed per frame (launch_row_increments)
+      int f = me.warm + frames_done;
+      const bool past = f > me.last_frame;  // beyond the utterance the coefficients stand still
+      f = past ? me.last_frame : f;
+      const double* ri = d.binc + me.b_base + 1 + (long long)f * kNM;
+#pragma unroll
+      for (int k = 0; k < kTaps; ++k) {
+        c[k] = r0[k];
+        CINC(k) = past ? 0.0 : ri[k];
+      }
+    } else {
+      const double* r1 = frame_row(frames_done);
+#pragma unroll
+      for (int k = 0; k < kTaps; ++k) {
+        c[k] = r0[k];
+        CINC(k) = (r1[k] - c[k]) / fper;
+      }
+    }
+#endif
+  };
 
   auto step = [&](double* __restrict__ Y, double* __restrict__ F, int jin, int jout) {
     // ---------------- phase A: fir of this lane's stage (mlsa.rs:128-163) and its df1 section
@@ -258,37 +457,19 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
     Y[lane] = y0 + y1;
     F[lane] = d11 * c[0];
     __syncwarp();
-    // coefficients of the next sample (mod.rs:133-135; :140 at a frame end)
+    // coefficients of the next sample (mod.rs:133-135); independent of the exchange
 #pragma unroll
-    for (int k = 0; k < kTaps; ++k) c[k] += CINC(k);
-    if (--left == 0) {
-      left = fp;
-      const double* r0 = frame_row(frames_done);
-      ++frames_done;
-      if (JB_V3_BINC) {  // (cc - coefficients) / fperiod precomputed per frame (launch_row_increments)
-        int f = me.warm + frames_done;
-        const bool past = f > me.last_frame;  // beyond the utterance the coefficients stand still
-        f = past ? me.last_frame : f;
-        const double* ri = d.binc + me.b_base + 1 + (long long)f * kNM;
-#pragma unroll
-        for (int k = 0; k < kTaps; ++k) {
-          c[k] = r0[k];
-          CINC(k) = past ? 0.0 : ri[k];
-        }
-      } else {
-        const double* r1 = frame_row(frames_done);
-#pragma unroll
-        for (int k = 0; k < kTaps; ++k) {
-          c[k] = r0[k];
-          CINC(k) = (r1[k] - c[k]) / fper;
-        }
-      }
-    }
+    for (int k = 0; k < JB_V3_CADD_FRONT; ++k) c[k] += CINC(k);
+#if JB_V3_BOUNDARY_IN_STEP
+    if (--left == 0) frame_end();
+#endif
     // ---------------- phase B: Pade combine of df1 then df2 (mlsa.rs:54-79), next stage inputs
     const double y1v = Y[g5], y2v = Y[g5 + 1], y3v = Y[g5 + 2], y4v = Y[g5 + 3], y5v = Y[g5 + 4];
     const double f1v = F[g5], f2v = F[g5 + 1], f3v = F[g5 + 2], f4v = F[g5 + 3], f5v = F[g5 + 4];
     const double yprev = Y[prev_lane], fprev = F[prev_lane];
     const double e = inp[jin * 8];
+#pragma unroll
+    for (int k = JB_V3_CADD_FRONT; k < kTaps; ++k) c[k] += CINC(k);  // these fill the latency of the loads
     const double Af = __fma_rn(pp5, f5v, __fma_rn(pp3, f3v, pp1 * f1v));
     const double Bf = __fma_rn(pp4, f4v, pp2 * f2v);
     const double Ay = __fma_rn(pp5, y5v, __fma_rn(pp3, y3v, pp1 * y1v));
@@ -302,7 +483,7 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
     if (head) S.Out[jout * 8 + g] = outv;
   };
 
-  for (int i0 = 0; i0 < nsmp_max; i0 += kCH) {
+  for (int i0 = i0_start; i0 < nsmp_max; i0 += kCH) {
     if (left == fp) {  // top of a frame (fp % kCH == 0): state taps for the cut check
       if (frames_done == me.own0 && my_cut) dump_state(0);
     }
@@ -312,6 +493,10 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
       step(S.Y[0], S.F[0], ring + j, j);
       step(S.Y[1], S.F[1], ring + j + 1, j + 1);
     }
+#if !JB_V3_BOUNDARY_IN_STEP
+    left -= kCH;  // fperiod % kCH == 0: a frame ends with a chunk
+    if (left == 0) frame_end();
+#endif
     if (left == fp && frames_done == me.nfr) dump_state(1);
     cp_async_wait_all_s();  // chunk i0/kCH + 1 has landed
     __syncwarp();
@@ -326,6 +511,12 @@ k_mlsa_v3(BatchLayout b, VocoderParams p, VocoderDev d, MlsaSegments sg, int seg
         if (n >= si.own0 * fp && n < si.nfr * fp) d.out[si.in_base + n] = S.Out[i * 8 + gg] * p.volume;
       }
       if ((chunk + 2) * kCH < nsmp_max) fill_chunk(chunk + 2);
+#if JB_V3_ROWS_SMEM
+      if (staged) {
+        staged = false;
+        stage_row(frames_done + 1);
+      }  // over the row just consumed (the __syncwarp above orders the reads)
+#endif
     }
     __syncwarp();
   }
@@ -375,7 +566,7 @@ __global__ void k_publish(const double* src, double* host_dst) {
 }  // namespace
 
 int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, const MlsaSegments& sg,
-                   int seg_first, int seg_count, cudaStream_t stream) {
+                   int seg_first, int seg_count, cudaStream_t stream, int f64_tail) {
   if (seg_count <= 0) return 0;
   if (p.nmcp != kNM || p.fperiod % kCH != 0 || d.out == nullptr || d.out == d.wave || seg_first < 0 ||
       (JB_V3_BINC && d.binc == nullptr) ||
@@ -392,7 +583,7 @@ int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDe
   if (e != cudaSuccess) return (int)e;
 #endif
   k_mlsa_v3<kWPB><<<(warps + kWPB - 1) / kWPB, 32 * kWPB, smem, stream>>>(b, p, d, sg, seg_first,
-                                                                        seg_first + seg_count, 1.0 - p.alpha * p.alpha);
+                                                                        seg_first + seg_count, 1.0 - p.alpha * p.alpha, f64_tail);
   return (int)cudaGetLastError();
 }
 

@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <thread>
 
@@ -417,6 +418,7 @@ struct Engine::Resident {
   int repaired_segments = 0;       // the last pass re-filtered this many segments with a longer warm-up
   std::vector<jbk::MlsaSegment> seg_table;  // host copy of segs.seg (for the repair pass)
   int warm_frames = 0;             // warm-up the segments were cut with
+  int f64_tail = -1;               // double-precision tail of the warm-up (launch_mlsa_v3), < 0: all of it
   bool copied_by_waves = false;    // the last pass already queued its device-to-host copies
   cudaEvent_t kernels_end = nullptr;  // recorded after the last kernel of the last pass (variant 3)
   double* h_worst = nullptr;          // pinned word the last pass copies its cut-check result to
@@ -452,6 +454,12 @@ static jbk::WindowSet make_windows(const Windows& w) {
 }
 
 // Time segments of the filter kernels (MLSA variant 3, MGLSA): what make_resident uploads.
+// JB_MLSA_F64_TAIL in the environment overrides the engine's setting (sweeps; -1 = whole warm-up in FP64)
+static int mlsa_f64_tail_setting(int engine_value) {
+  static const char* env = getenv("JB_MLSA_F64_TAIL");
+  return env ? atoi(env) : engine_value;
+}
+
 struct SegmentPlan {
   std::vector<jbk::MlsaSegment> segs;
   std::vector<int32_t> wave_seg_first, wave_utt_first;  // [waves + 1]
@@ -841,6 +849,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   r->segs.mismatch = segs.empty() ? nullptr : (double*)(dw + w_segmis);
   r->seg_table = segs;
   r->warm_frames = (int)(e.mlsa_warm_frames * (cond.stage != 0 ? kMglsaWarmFactor : 1));
+  r->f64_tail = mlsa_f64_tail_setting(e.mlsa_f64_tail);
   r->whole.n_seg = (int)whole.size();
   r->whole.seg = (const jbk::MlsaSegment*)(di + o_whole);
   r->whole.state = nullptr;
@@ -938,7 +947,7 @@ static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_exc
     for (int w = 0; w < waves; ++w) {
       const int s0 = r->wave_seg_first[w], s1 = r->wave_seg_first[w + 1];
       if (mg) JB_LAUNCH(jbk::launch_mglsa(r->layout, r->vp, vd, r->segs, s0, s1 - s0, false, st));
-      else JB_LAUNCH(jbk::launch_mlsa_v3(r->layout, r->vp, vd, r->segs, s0, s1 - s0, st));
+      else JB_LAUNCH(jbk::launch_mlsa_v3(r->layout, r->vp, vd, r->segs, s0, s1 - s0, st, r->f64_tail));
       if (wc && !direct) {
         const int64_t f0 = r->frame_off[(size_t)r->wave_utt_first[w]];
         const int64_t f1 = r->frame_off[(size_t)r->wave_utt_first[w + 1]];
@@ -1027,7 +1036,7 @@ static bool mlsa_repair_segments(Engine::Resident* r, double tol, std::vector<in
     sg.state = (double*)(d + o_state);
     sg.mismatch = nullptr;
     if (mg) JB_LAUNCH(jbk::launch_mglsa(r->layout, r->vp, r->vd, sg, 0, sg.n_seg, false, st));
-    else JB_LAUNCH(jbk::launch_mlsa_v3(r->layout, r->vp, r->vd, sg, 0, sg.n_seg, st));
+    else JB_LAUNCH(jbk::launch_mlsa_v3(r->layout, r->vp, r->vd, sg, 0, sg.n_seg, st, r->f64_tail));
     const int cnt = mg ? (int)stride : 5 * 37;
     JB_LAUNCH(jbk::launch_mlsa_seg_check(sg, r->d_worst, r->h_worst, st, (int)stride, cnt, mg, r->segs.state));
     JB_CUDA(cudaStreamSynchronize(st));  // `fix` and the scratch stay alive until here
@@ -1205,6 +1214,7 @@ Engine::Resident* Engine::prepare_tracks(const VocoderConfig& cfg, size_t n_utt,
   r->segs.mismatch = plan.segs.empty() ? nullptr : (double*)(dw + w_segmis);
   r->seg_table = plan.segs;
   r->warm_frames = (int)(mlsa_warm_frames * (cfg.stage != 0 ? kMglsaWarmFactor : 1));
+  r->f64_tail = mlsa_f64_tail_setting(mlsa_f64_tail);
   r->whole.n_seg = (int)whole.size();
   r->whole.seg = (const jbk::MlsaSegment*)(di + o_whole);
   r->d_worst = (double*)(dw + w_worst);

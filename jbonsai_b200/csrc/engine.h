@@ -62,6 +62,10 @@ class Engine {
   // row indices and k_gather_states interpolates. false = the host packs interpolated vectors.
   bool device_gather = true;
   int mlsa_warm_frames = 40;
+  // Of those, how many (the ones next to the own range) run in double precision; the ones before them run in
+  // FP32 (k_mlsa_v3 built with JB_V3_F32_HEAD=1; measured: the FP32 error does not fade in time, see
+  // mlsa_seg.cu). < 0 (default): the whole warm-up in double precision.
+  int mlsa_f64_tail = -1;
   // Largest accepted state mismatch across a cut. Two correct trajectories with different rounding
   // histories already differ by up to ~3e-8 in the delay-line taps (measured floor: nitech 4e-9,
   // tohoku-f01 3e-8, independent of the warm-up length beyond the knee), while a short warm-up
