@@ -127,7 +127,13 @@ __global__ void __launch_bounds__(256) k_pulse_list(BatchLayout b, VocoderDev d,
   d.runs[1 + slot] = (int32_t)gf;
 }
 
-constexpr int kRunLanes = 4;
+// Walks per warp. Measured inside the MLPG phase (the walks share the chip with k_mlpg_gv of the MCP stream):
+// 4 -> 6.29 ms, 8 -> 6.11 ms, 16 -> 6.45 ms for the phase; ncu: with 4, 1.66 threads are active per warp
+// instruction on average and the kernel issues 458 M warp instructions.
+#ifndef JB_RUN_LANES
+#define JB_RUN_LANES 8
+#endif
+constexpr int kRunLanes = JB_RUN_LANES;
 __global__ void __launch_bounds__(128) k_pulse_runs(BatchLayout b, VocoderParams p, VocoderDev d,
                                                     int64_t total_frames) {
   // kRunLanes walks per warp: a walk leaves the 8-sample fast path about once in 30 blocks, and a
