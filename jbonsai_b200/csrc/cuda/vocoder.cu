@@ -294,13 +294,20 @@ __global__ void __launch_bounds__(256) k_excitation(BatchLayout b, VocoderParams
 // own (the block-per-frame kernel above reads two operands per tap and is shared-memory bound).
 // Same operands, same order of additions per sample. The staging arrays skip one slot in nine so
 // that lanes reading with a stride of eight doubles fall into different banks.
-constexpr int kExWarps = 4;
+#ifndef JB_EX_WARPS
+#define JB_EX_WARPS 4
+#endif
+constexpr int kExWarps = JB_EX_WARPS;
 // Frames one warp handles in a row. coefficients[0] of every sample is a chain of fperiod dependent additions
 // (mod.rs:133-135: the rounding sequence of the reference); run by one lane per frame it cost 240 warp-wide
 // DADDs and 2000 cycles of latency for every frame. Here lane q runs the chain of frame q of the group and
 // keeps every eighth value; the lane that owns samples 8 L .. 8 L + 7 of a frame restarts from the exact value
-// at 8 L: 240 / 16 + 7 additions per frame instead of 240, same bits.
-constexpr int kExGroup = 16;
+// at 8 L: 240 / G + 7 additions per frame instead of 240, same bits. Measured (B200, bench batch): one frame
+// per warp 3.24 ms; G = 16: 2.40, 8: 2.09, 4: 2.05 ms (a larger group costs shared memory, i.e. resident warps).
+#ifndef JB_EX_GROUP
+#define JB_EX_GROUP 8
+#endif
+constexpr int kExGroup = JB_EX_GROUP;
 template <int NL>
 __global__ void __launch_bounds__(32 * kExWarps) k_excitation_w(BatchLayout b, VocoderParams p, VocoderDev d,
                                                                 int64_t total_frames) {
