@@ -319,34 +319,51 @@ __global__ void __launch_bounds__(32 * kExWarps) k_excitation_w(BatchLayout b, V
   __shared__ double s_c8[kExWarps][kExGroup][33];  // coefficients[0] at samples 0, 8, 16, ... of every frame
   __shared__ double s_cinc[kExWarps][kExGroup];
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int64_t gf0 = ((int64_t)blockIdx.x * kExWarps + w) * kExGroup;
-  if (gf0 >= total_frames) return;  // whole warp; warps never sync with each other
+  // Work items: every frame of the batch, or (chunked synthesis: d.frame_count >= 0) only frames
+  // [frame_begin, frame_begin + frame_count) of every utterance, numbered utterance-major.
+  const bool chunked = d.frame_count >= 0;
+  const int64_t n_items = chunked ? (int64_t)b.n_utt * d.frame_count : total_frames;
+  const int64_t v0 = ((int64_t)blockIdx.x * kExWarps + w) * kExGroup;
+  if (v0 >= n_items) return;  // whole warp; warps never sync with each other
   const int fp = p.fperiod;
   auto pad = [](int j) { return j + (j >> 3); };
+  auto locate = [&](int64_t v, int& u, int& f, int64_t& gf) -> bool {
+    if (v >= n_items) return false;
+    if (chunked) {
+      u = (int)(v / d.frame_count);
+      f = d.frame_begin + (int)(v - (int64_t)u * d.frame_count);
+      gf = b.frame_off[u] + f;
+      return gf < b.frame_off[u + 1];
+    }
+    gf = v;
+    u = find_utt(b.frame_off, b.n_utt, gf);
+    f = (int)(gf - b.frame_off[u]);
+    return f >= d.frame_begin;
+  };
 
-  if (lane < kExGroup && gf0 + lane < total_frames) {  // the chain of frame gf0 + lane (mod.rs:133-135)
-    const int64_t gf = gf0 + lane;
-    const int u = find_utt(b.frame_off, b.n_utt, gf);
-    const int f = (int)(gf - b.frame_off[u]);
-    const double cc = d.b[gf * p.nmcp];
-    double c = f > 0 ? d.b[(gf - 1) * p.nmcp] : (d.b_first ? d.b_first[(int64_t)u * p.nmcp] : cc);
-    const double cinc = (cc - c) / (double)fp;
-    s_cinc[w][lane] = cinc;
-    for (int i = 0; i < fp; i += R) {
-      s_c8[w][lane][i / R] = c;
+  if (lane < kExGroup) {  // the chain of item v0 + lane (mod.rs:133-135)
+    int u, f;
+    int64_t gf;
+    if (locate(v0 + lane, u, f, gf)) {
+      const double cc = d.b[gf * p.nmcp];
+      double c = f > 0 ? d.b[(gf - 1) * p.nmcp] : (d.b_first ? d.b_first[(int64_t)u * p.nmcp] : cc);
+      const double cinc = (cc - c) / (double)fp;
+      s_cinc[w][lane] = cinc;
+      for (int i = 0; i < fp; i += R) {
+        s_c8[w][lane][i / R] = c;
 #pragma unroll
-      for (int r = 0; r < R; ++r) c += cinc;
+        for (int r = 0; r < R; ++r) c += cinc;
+      }
     }
   }
   __syncwarp();
 
   for (int q = 0; q < kExGroup; ++q) {
-    const int64_t gf = gf0 + q;
-    if (gf >= total_frames) break;  // uniform
-    const int u = find_utt(b.frame_off, b.n_utt, gf);
+    if (v0 + q >= n_items) break;  // uniform
+    int u, f;
+    int64_t gf;
+    if (!locate(v0 + q, u, f, gf)) continue;  // uniform
     const int64_t foff = b.frame_off[u];
-    const int f = (int)(gf - foff);
-    if (f < d.frame_begin || (d.frame_count >= 0 && f - d.frame_begin >= d.frame_count)) continue;  // uniform
     const int64_t n0 = (int64_t)f * fp;
     const bool voiced_cur = d.pitch[gf] != 0.0;
     const bool voiced_prev = f > 0 && d.pitch[gf - 1] != 0.0;
@@ -889,9 +906,12 @@ int launch_excitation(const BatchLayout& b, const VocoderParams& p, const Vocode
   if (total_frames == 0) return 0;
   if (p.nlpf > kMaxLpf || p.fperiod > kMaxFperiod) return (int)cudaErrorInvalidValue;
   if (p.nlpf == 31 && p.fperiod % 8 == 0 && p.fperiod <= 256)
-    k_excitation_w<31><<<(unsigned)((total_frames + kExWarps * kExGroup - 1) / (kExWarps * kExGroup)), 32 * kExWarps, 0,
-                         stream>>>(
-        b, p, d, total_frames);
+  {
+    const int64_t items = d.frame_count >= 0 ? (int64_t)b.n_utt * d.frame_count : total_frames;
+    if (items == 0) return 0;
+    k_excitation_w<31><<<(unsigned)((items + kExWarps * kExGroup - 1) / (kExWarps * kExGroup)), 32 * kExWarps, 0,
+                         stream>>>(b, p, d, total_frames);
+  }
   else
     k_excitation<<<(unsigned)total_frames, 256, 0, stream>>>(b, p, d, total_frames);
   return (int)cudaGetLastError();
