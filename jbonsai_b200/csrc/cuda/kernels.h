@@ -132,8 +132,8 @@ struct VocoderDev {
   const double* b_first;  // [n_utt][nmcp] or nullptr. beta > 0 only: mc2b of the un-filtered first frame, the
                           // coefficients the reference starts from (is_first, vocoder/mod.rs:79-88); nullptr =
                           // row 0 of `b` (identical when beta == 0)
-  double* binc;         // stage != 0 only: [total_frames][nmcp] per-sample coefficient increments of every frame
-                        // (launch_row_increments), else nullptr
+  double* binc;         // [total_frames][nmcp] per-sample coefficient increments of every frame
+                        // (launch_row_increments): read by the segmented filters (MLSA variant 3, MGLSA); else nullptr
   double* pitch;        // [total_frames]        p per frame (out of frame_prep)
   double* pulse;        // [total_samples]       pulse amplitude or 0 (out of pitch kernel)
   int32_t* runs;        // [1 + total_frames]    work: number of voiced runs, then their first frames
@@ -175,13 +175,22 @@ struct MlsaSegments {
   const MlsaSegment* seg;  // [n_seg], six consecutive segments share a warp (host sorts by length)
   double* state;           // [n_seg][2][kMlsaSegStateDoubles] cut-check taps, or nullptr
   double* mismatch;        // [n_seg] or nullptr: mismatch of every segment's cut (out of launch_mlsa_seg_check)
+  // Repair pass (launch_mlsa_v3 only): a segment with warm == begin and prev >= 0 starts from the end state of
+  // segment `prev` in this array (the state array of the original pass) instead of a warm-up from zero.
+  const double* init_state = nullptr;
+  // Cuts that failed the check, compacted on the device: ids into `seg`, count (may exceed fail_cap: then the
+  // list is incomplete and the caller falls back), and a pinned host word the count is published to.
+  int* fail_count = nullptr;
+  int* fail_list = nullptr;
+  int fail_cap = 0;
+  int* host_fail_count = nullptr;
 };
 // Filters segments [seg_first, seg_first + seg_count) of d.wave into d.out (one launch = one wave).
-// `f64_tail`: how many warm-up frames in front of the own range run in double precision; the warm-up frames
-// before them run the same recurrence in FP32 (their output is discarded and their rounding error fades
-// below the cut tolerance over the tail; the cut check sees the result). < 0: all of the warm-up in FP64.
+// Needs d.binc (launch_row_increments), nmcp for which mlsa_v3_supports() is true, an even fperiod.
+bool mlsa_v3_supports(int nmcp);
+int mlsa_v3_chunk(int fperiod);  // samples per staged chunk; 0 = fperiod not supported (odd)
 int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, const MlsaSegments& sg,
-                   int seg_first, int seg_count, cudaStream_t stream, int f64_tail = -1);
+                   int seg_first, int seg_count, cudaStream_t stream);
 // After every wave has run: the largest state mismatch over all cuts -> *worst (device), for the
 // host to compare with its tolerance.
 // `host_mirror` (pinned, device-visible, or nullptr): also stored there by the device, no copy engine.
@@ -189,9 +198,22 @@ int launch_mlsa_v3(const BatchLayout& b, const VocoderParams& p, const VocoderDe
 // every cut's mismatch is divided by max(1, largest |state value| at that cut) (MGLSA: the output scale
 // of an LSP voice is not known in advance). `prev_state`: the state array the `prev` ids of `sg` index when it is
 // not sg.state (a repair pass over a few segments, compared with the end states of the original pass).
+// `gain` (MLSA): the mismatch of a cut is scaled to a bound on the waveform error, mismatch * max(1, sum_k |c_k|
+// of the coefficient rows at the cut) * |volume|, and compared with gain->tol on the device (sg.fail_*).
+struct SegCheckGain {
+  const BatchLayout* layout;
+  const double* rows;  // VocoderDev::b
+  int nm;
+  double volume, tol;
+};
 int launch_mlsa_seg_check(const MlsaSegments& sg, double* worst, double* host_mirror, cudaStream_t stream,
                           int stride = kMlsaSegStateDoubles, int count = 5 * 37, bool relative = false,
-                          const double* prev_state = nullptr);
+                          const double* prev_state = nullptr, const SegCheckGain* gain = nullptr);
+// Repair pass epilogue: segment i of fix[n_fix] (device) re-filtered frames [begin, end) from the exact state
+// into `scratch` (indexed like `out`); where the last re-filtered frame agrees with `out` to `tol` the new
+// samples replace the old ones and ok[i] = 1, else ok[i] = 0 and `out` stands.
+int launch_mlsa_repair_merge(const BatchLayout& b, const MlsaSegment* fix, int n_fix, const double* scratch, double* out,
+                             int fperiod, double tol, int* ok, cudaStream_t stream);
 
 // Stage != 0 (mglsa.cu). launch_lsp_prep: rows of d.b = filter coefficients of every LSP frame of d.mcp
 // (postfilter_lsp(beta), check_lsp_stability, lsp2mgc, mc2b, gnorm, [1..] *= gamma; vocoder/mod.rs:148-155)

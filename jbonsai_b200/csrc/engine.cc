@@ -30,7 +30,8 @@ namespace jb {
 
 namespace {
 
-constexpr int kSegWarpsPerSmsp = 2;  // resident warps per scheduler of k_mlsa_v3 (206 registers)
+// resident warps per scheduler of k_mlsa_v3 (255 registers: two fit)
+static const int kSegWarpsPerSmsp = getenv("JB_X_WPS") ? atoi(getenv("JB_X_WPS")) : 2;
 constexpr int kRepairWarmFactor = 2;
 constexpr double kMglsaCutRelTolerance = 1e-9;
 constexpr int kMglsaWarmFactor = 2;  // stage != 0: the all-pole MGLSA filter of an LSP frame forgets more slowly than the
@@ -160,11 +161,14 @@ class DeviceCtx {
   void use_slot(int i) {
     ev = evsets[i];
     h_worst = h_worst_base + i;
+    h_fail = h_fail_base + i;
   }
   std::multimap<size_t, void*> cached;  // freed device blocks
   int sm_count = 148;
   double* h_worst_base = nullptr;
   double* h_worst = nullptr;  // pinned: MLSA variant 3 cut-check result (of the current slot)
+  int* h_fail_base = nullptr;
+  int* h_fail = nullptr;      // pinned: number of cuts that failed the check (of the current slot)
   // leaf pdf tables of the engine's voices, resident for the life of the context (device gather)
   double* d_tab_mean[3] = {nullptr, nullptr, nullptr};
   double* d_tab_vari[3] = {nullptr, nullptr, nullptr};
@@ -212,7 +216,9 @@ class DeviceCtx {
       for (auto& x : set) JB_CUDA(cudaEventCreate(&x));
     JB_CUDA(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
     JB_CUDA(cudaMallocHost((void**)&h_worst_base, kMaxChunks * sizeof(double)));
+    JB_CUDA(cudaMallocHost((void**)&h_fail_base, kMaxChunks * sizeof(int)));
     for (int i = 0; i < kMaxChunks; ++i) h_worst_base[i] = 0.0;
+    for (int i = 0; i < kMaxChunks; ++i) h_fail_base[i] = 0;
     use_slot(0);
   }
   ~DeviceCtx() {
@@ -225,6 +231,7 @@ class DeviceCtx {
       if (d_tab_msd[s]) cudaFree(d_tab_msd[s]);
     }
     if (h_worst_base) cudaFreeHost(h_worst_base);
+    if (h_fail_base) cudaFreeHost(h_fail_base);
     for (auto& set : evsets)
       for (auto& x : set) cudaEventDestroy(x);
     for (auto& x : evx) cudaEventDestroy(x);
@@ -418,10 +425,12 @@ struct Engine::Resident {
   int repaired_segments = 0;       // the last pass re-filtered this many segments with a longer warm-up
   std::vector<jbk::MlsaSegment> seg_table;  // host copy of segs.seg (for the repair pass)
   int warm_frames = 0;             // warm-up the segments were cut with
-  int f64_tail = -1;               // double-precision tail of the warm-up (launch_mlsa_v3), < 0: all of it
   bool copied_by_waves = false;    // the last pass already queued its device-to-host copies
   cudaEvent_t kernels_end = nullptr;  // recorded after the last kernel of the last pass (variant 3)
   double* h_worst = nullptr;          // pinned word the last pass copies its cut-check result to
+  int* h_fail = nullptr;              // pinned word: cuts of the last pass that failed the check
+  double* out_direct = nullptr;       // output mode 2: the pinned host buffer the last pass stored into
+  double cut_tol = 0.0;               // waveform-error bound the last pass checked its cuts against
   const double* result = nullptr;  // device waveform of the last pass
   // kernels per pass: expand, 3 solves (+ GV kernels), 2 frame preps, pulse (memset excluded),
   // excitation, MLSA (+ cut check for variant 3)
@@ -454,12 +463,6 @@ static jbk::WindowSet make_windows(const Windows& w) {
 }
 
 // Time segments of the filter kernels (MLSA variant 3, MGLSA): what make_resident uploads.
-// JB_MLSA_F64_TAIL in the environment overrides the engine's setting (sweeps; -1 = whole warm-up in FP64)
-static int mlsa_f64_tail_setting(int engine_value) {
-  static const char* env = getenv("JB_MLSA_F64_TAIL");
-  return env ? atoi(env) : engine_value;
-}
-
 struct SegmentPlan {
   std::vector<jbk::MlsaSegment> segs;
   std::vector<int32_t> wave_seg_first, wave_utt_first;  // [waves + 1]
@@ -543,6 +546,13 @@ static SegmentPlan cut_segments(const std::vector<int64_t>& frame_off, size_t n_
       std::stable_sort(perm.begin(), perm.end(), [&](int32_t x, int32_t y) {
         return ws[x].end - ws[x].warm > ws[y].end - ws[y].warm;
       });
+      // Two blocks (of 4 warps x 6 segments) are resident per SM and block b shares its SM with block
+      // b + #SMs: the second round of blocks takes the segments in ascending order, so that the longest
+      // warps sit beside the shortest ones and every scheduler gets about the same number of frames.
+      {
+        const size_t first_round = (size_t)(target / std::max(1, kSegWarpsPerSmsp));  // #SMs x 24 segments
+        if (kSegWarpsPerSmsp == 2 && perm.size() > first_round) std::reverse(perm.begin() + first_round, perm.end());
+      }
       for (size_t i = 0; i < perm.size(); ++i) where[perm[i]] = (int32_t)i;
       const int32_t base = (int32_t)segs.size();
       if (wv > 0) {
@@ -761,11 +771,13 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   const size_t w_segstate = segs.empty() ? 0 : wk.take(segs.size() * 2 * seg_state_doubles * 8);
   const size_t w_worst = wk.take(8);
   const size_t w_segmis = segs.empty() ? 0 : wk.take(segs.size() * 8);
+  const size_t w_failcnt = wk.take(8);
+  const size_t fail_cap = std::max<size_t>(64, segs.size() / 16);
+  const size_t w_faillist = segs.empty() ? 0 : wk.take(fail_cap * 4);
   const bool postfilter = cond.stage == 0 && cond.beta > 0.0 && dim[0] > 2;  // cepstrum.rs:24
   const bool first_rows = postfilter || cond.stage != 0;  // rows the first frame starts from (mod.rs:79-109)
   const size_t w_bfirst = first_rows ? wk.take(n_utt * (size_t)dim[0] * 8) : 0;
-  const bool need_binc = cond.stage != 0;  // the MGLSA kernel reads per-frame increments (MLSA variant 3 was
-                                           // 5 % slower with them: mlsa_seg.cu, JB_V3_BINC)
+  const bool need_binc = cond.stage != 0 || !segs.empty();  // the segmented filters read per-frame increments
   const size_t w_binc = need_binc ? wk.take((size_t)TF * dim[0] * 8) : 0;
   r->d_work = ctx->dalloc(wk.off, &r->work_cap);
   uint8_t* di = (uint8_t*)r->d_in;
@@ -847,9 +859,11 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   r->segs.seg = (const jbk::MlsaSegment*)(di + o_segs);
   r->segs.state = segs.empty() ? nullptr : (double*)(dw + w_segstate);
   r->segs.mismatch = segs.empty() ? nullptr : (double*)(dw + w_segmis);
+  r->segs.fail_count = segs.empty() ? nullptr : (int*)(dw + w_failcnt);
+  r->segs.fail_list = segs.empty() ? nullptr : (int*)(dw + w_faillist);
+  r->segs.fail_cap = segs.empty() ? 0 : (int)fail_cap;
   r->seg_table = segs;
   r->warm_frames = (int)(e.mlsa_warm_frames * (cond.stage != 0 ? kMglsaWarmFactor : 1));
-  r->f64_tail = mlsa_f64_tail_setting(e.mlsa_f64_tail);
   r->whole.n_seg = (int)whole.size();
   r->whole.seg = (const jbk::MlsaSegment*)(di + o_whole);
   r->whole.state = nullptr;
@@ -922,8 +936,11 @@ struct WaveCopy {
 };
 
 static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_excitation,
-                           cudaEvent_t after_exc, bool pulse_done, const WaveCopy* wc = nullptr) {
+                           cudaEvent_t after_exc, bool pulse_done, double cut_tol, const WaveCopy* wc = nullptr) {
   cudaStream_t st = r->ctx->stream;
+  // the noise table of the device may have been re-allocated (grown) by a batch prepared after this one:
+  // take the pointer now, under the device mutex, not the one cached at prepare time
+  r->vd.noise = r->ctx->d_noise;
   if (!pulse_done) JB_LAUNCH(jbk::launch_pulse(r->layout, r->vp, r->vd, r->total_samples, st));
   JB_LAUNCH(jbk::launch_excitation(r->layout, r->vp, r->vd, r->total_frames, st));
   if (after_exc) JB_CUDA(cudaEventRecord(after_exc, st));
@@ -932,22 +949,27 @@ static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_exc
   r->repaired_segments = 0;
   r->copied_by_waves = false;
   r->kernels_end = nullptr;
+  r->out_direct = nullptr;
+  r->cut_tol = cut_tol;
   if (stop_after_excitation) return;
   const bool mg = r->vp.stage != 0;  // MGLSA (mglsa.cu): segmented unless the sequential variant is forced
   if (mg && (r->vd.out == nullptr || r->vp.fperiod % 16 != 0))
     throw Error(kErrUnsupported, "stage != 0: streaming synthesis / fperiod not a multiple of 16 are not built");
   const bool v3 = mg ? (variant < 0 || variant == 3) && r->segs.n_seg > 0
-                     : (variant < 0 || variant == 3) && r->segs.n_seg > 0 && r->vp.nmcp == 35 &&
-                           r->vp.fperiod % 16 == 0 && r->vd.frame_begin == 0 && r->vd.frame_count < 0;
+                     : (variant < 0 || variant == 3) && r->segs.n_seg > 0 && jbk::mlsa_v3_supports(r->vp.nmcp) &&
+                           jbk::mlsa_v3_chunk(r->vp.fperiod) > 0 && r->vd.frame_begin == 0 && r->vd.frame_count < 0;
   if (v3) {
     const int waves = (int)r->wave_seg_first.size() - 1;
     const bool direct = wc && wc->direct && !wc->host16;
     jbk::VocoderDev vd = r->vd;
-    if (direct) vd.out = wc->host;  // zero-copy: output stores cross PCIe while the filter runs
+    if (direct) {  // zero-copy: output stores cross PCIe while the filter runs
+      vd.out = wc->host;
+      r->out_direct = wc->host;
+    }
     for (int w = 0; w < waves; ++w) {
       const int s0 = r->wave_seg_first[w], s1 = r->wave_seg_first[w + 1];
       if (mg) JB_LAUNCH(jbk::launch_mglsa(r->layout, r->vp, vd, r->segs, s0, s1 - s0, false, st));
-      else JB_LAUNCH(jbk::launch_mlsa_v3(r->layout, r->vp, vd, r->segs, s0, s1 - s0, st, r->f64_tail));
+      else JB_LAUNCH(jbk::launch_mlsa_v3(r->layout, r->vp, vd, r->segs, s0, s1 - s0, st));
       if (wc && !direct) {
         const int64_t f0 = r->frame_off[(size_t)r->wave_utt_first[w]];
         const int64_t f1 = r->frame_off[(size_t)r->wave_utt_first[w + 1]];
@@ -964,11 +986,16 @@ static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_exc
       }
     }
     r->h_worst = r->ctx->h_worst;
+    r->h_fail = r->ctx->h_fail;
+    r->segs.host_fail_count = r->h_fail;
     if (mg) {
       const int n = jbk::mglsa_state_doubles(r->vp.stage);
       JB_LAUNCH(jbk::launch_mlsa_seg_check(r->segs, r->d_worst, r->h_worst, st, n, n, true));
     } else {
-      JB_LAUNCH(jbk::launch_mlsa_seg_check(r->segs, r->d_worst, r->h_worst, st));
+      // the mismatch of every cut is scaled to a bound on the waveform error (kernels.h) and compared with cut_tol
+      const jbk::SegCheckGain gain{&r->layout, r->vd.b, r->vp.nmcp, r->vp.volume, cut_tol};
+      JB_LAUNCH(jbk::launch_mlsa_seg_check(r->segs, r->d_worst, r->h_worst, st, jbk::kMlsaSegStateDoubles, 5 * 37, false,
+                                           nullptr, &gain));
     }
     JB_CUDA(cudaEventRecord(r->ctx->ev[7], st));
     r->kernels_end = r->ctx->ev[7];
@@ -991,22 +1018,103 @@ static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_exc
 // Returns true when it did; the caller then repeats whatever it had queued behind the filter.
 static bool mlsa_cut_check_failed(Engine::Resident* r, double tol) {
   if (r->result != r->vd.out || r->vd.out == nullptr || r->kernels_end == nullptr) return false;
+  static const bool off = getenv("JB_X_NOCHECK") != nullptr;  // timing experiments with deliberately wrong kernels
+  if (off) return false;
   // MGLSA: the mismatch is relative to the state's scale (launch_mlsa_seg_check); held to 1e-9, an order
   // below what the LSP transform's conditioning leaves of the coefficient rows themselves
   if (r->vp.stage != 0) tol = std::min(tol, kMglsaCutRelTolerance);
+  else if (r->h_fail && *r->h_fail > 0) return true;  // the device compared every cut's bound with cut_tol
   const double w = r->h_worst ? *r->h_worst : 0.0;
   return !(w <= tol);  // NaN counts as a failed cut
 }
-// A failed cut check, first resort: the segments whose cut disagrees are filtered again with twice the
-// warm-up (a lone segment is a serial chain: every extra warm-up frame is 0.12 ms of latency) and checked against the same end states; the rest of the batch stands. `touched` receives the
-// utterances whose output changed. Returns false when that is not possible or not enough (many failing
-// cuts, or a repaired cut still off): the caller then redoes the whole batch without cuts.
-static bool mlsa_repair_segments(Engine::Resident* r, double tol, std::vector<int32_t>* touched) {
+// A failed cut check, first resort (MLSA): the head of every segment behind a failing cut is filtered again from
+// the exact state - the end state of the segment before it, which the original pass stored for the check - over
+// `repair_frames` frames, into a scratch buffer (the pulse train's, consumed by now). Where the last re-filtered
+// frame agrees with the original pass the two trajectories have merged: the new samples replace the old ones and
+// the rest of the segment stands. The failing cuts come compacted from the device (MlsaSegments::fail_list).
+// `ranges` receives (utterance, first sample, one past the last sample) of what changed, relative to the
+// utterance. Returns false when that is not possible or not enough (many failing cuts, or a trajectory that has
+// not merged): the caller then redoes the whole batch without cuts.
+struct RepairRange {
+  int32_t utt;
+  int64_t n0, n1;
+};
+static bool mglsa_repair_segments(Engine::Resident* r, double tol, std::vector<RepairRange>* ranges);
+static bool mlsa_repair_segments(Engine::Resident* r, double tol, std::vector<RepairRange>* ranges) {
+  if (r->vp.stage != 0) return mglsa_repair_segments(r, tol, ranges);
+  DeviceCtx* c = r->ctx;
+  cudaStream_t st = c->stream;
+  const int n = r->segs.n_seg;
+  if (n == 0 || r->segs.fail_list == nullptr || (int)r->seg_table.size() != n || r->h_fail == nullptr) return false;
+  const int nfail = *r->h_fail;
+  if (nfail <= 0 || nfail > r->segs.fail_cap || nfail > std::max(16, n / 16)) return false;
+  std::vector<int32_t> ids((size_t)nfail);
+  JB_CUDA(cudaMemcpyAsync(ids.data(), r->segs.fail_list, (size_t)nfail * 4, cudaMemcpyDeviceToHost, st));
+  JB_CUDA(cudaStreamSynchronize(st));
+  std::sort(ids.begin(), ids.end());
+  const int repair_frames = std::max(32, r->warm_frames);  // the mismatch left by the warm-up has this long to fade
+  std::vector<jbk::MlsaSegment> fix;
+  for (int32_t id : ids) {
+    if (id < 0 || id >= n) return false;
+    jbk::MlsaSegment s = r->seg_table[(size_t)id];  // `prev` keeps indexing the original pass's states
+    if (s.prev < 0) return false;
+    s.warm = s.begin;  // no warm-up: the kernel loads the end state of `prev`
+    s.end = std::min<int32_t>(s.end, s.begin + repair_frames);
+    fix.push_back(s);
+  }
+  std::stable_sort(fix.begin(), fix.end(), [](const jbk::MlsaSegment& a, const jbk::MlsaSegment& b) {
+    return a.end - a.warm > b.end - b.warm;
+  });
+  Carver wk;
+  const size_t o_tab = wk.take(fix.size() * sizeof(jbk::MlsaSegment));
+  const size_t o_ok = wk.take(fix.size() * 4);
+  size_t cap = 0;
+  uint8_t* d = (uint8_t*)c->dalloc(wk.off, &cap);
+  std::vector<int32_t> ok(fix.size(), 0);
+  bool all_ok = false;
+  try {
+    JB_CUDA(cudaMemcpyAsync(d + o_tab, fix.data(), fix.size() * sizeof(jbk::MlsaSegment), cudaMemcpyHostToDevice, st));
+    jbk::MlsaSegments sg{};
+    sg.n_seg = (int)fix.size();
+    sg.seg = (const jbk::MlsaSegment*)(d + o_tab);
+    sg.init_state = r->segs.state;
+    jbk::VocoderDev vd = r->vd;
+    vd.out = r->vd.pulse;  // scratch, indexed like the output
+    JB_LAUNCH(jbk::launch_mlsa_v3(r->layout, r->vp, vd, sg, 0, sg.n_seg, st));
+    double* out = r->out_direct ? r->out_direct : r->vd.out;
+    // merged when the last re-filtered frame agrees to a fifth of the waveform bound
+    JB_LAUNCH(jbk::launch_mlsa_repair_merge(r->layout, sg.seg, sg.n_seg, vd.out, out, r->vp.fperiod, 0.2 * tol,
+                                            (int*)(d + o_ok), st));
+    JB_CUDA(cudaMemcpyAsync(ok.data(), d + o_ok, fix.size() * 4, cudaMemcpyDeviceToHost, st));
+    JB_CUDA(cudaStreamSynchronize(st));  // `fix` and the scratch stay alive until here
+    all_ok = true;
+    for (int32_t x : ok) all_ok = all_ok && x == 1;
+  } catch (...) {
+    cudaStreamSynchronize(st);
+    c->dfree(d, cap);
+    throw;
+  }
+  c->dfree(d, cap);
+  if (!all_ok) return false;
+  r->repaired_segments = (int)fix.size();
+  if (ranges) {
+    ranges->clear();
+    if (!r->out_direct)  // zero-copy output: the merge kernel has already stored into the host buffer
+      for (const jbk::MlsaSegment& s : fix)
+        ranges->push_back(RepairRange{s.utt, (int64_t)s.begin * r->vp.fperiod, (int64_t)s.end * r->vp.fperiod});
+  }
+  return true;
+}
+
+// Stage != 0 (MGLSA): the segments whose cut disagrees are filtered again with twice the warm-up and checked
+// against the same end states; the rest of the batch stands.
+static bool mglsa_repair_segments(Engine::Resident* r, double tol, std::vector<RepairRange>* ranges) {
   DeviceCtx* c = r->ctx;
   cudaStream_t st = c->stream;
   const int n = r->segs.n_seg;
   if (n == 0 || r->segs.mismatch == nullptr || (int)r->seg_table.size() != n || r->h_worst == nullptr) return false;
-  if (r->vp.stage != 0) tol = std::min(tol, kMglsaCutRelTolerance);
+  if (r->out_direct) return false;
+  tol = std::min(tol, kMglsaCutRelTolerance);
   std::vector<double> mis((size_t)n);
   JB_CUDA(cudaMemcpy(mis.data(), r->segs.mismatch, (size_t)n * 8, cudaMemcpyDeviceToHost));
   std::vector<jbk::MlsaSegment> fix;
@@ -1020,8 +1128,7 @@ static bool mlsa_repair_segments(Engine::Resident* r, double tol, std::vector<in
   std::stable_sort(fix.begin(), fix.end(), [](const jbk::MlsaSegment& a, const jbk::MlsaSegment& b) {
     return a.end - a.warm > b.end - b.warm;
   });
-  const bool mg = r->vp.stage != 0;
-  const size_t stride = mg ? (size_t)jbk::mglsa_state_doubles(r->vp.stage) : (size_t)jbk::kMlsaSegStateDoubles;
+  const size_t stride = (size_t)jbk::mglsa_state_doubles(r->vp.stage);
   Carver wk;
   const size_t o_tab = wk.take(fix.size() * sizeof(jbk::MlsaSegment));
   const size_t o_state = wk.take(fix.size() * 2 * stride * 8);
@@ -1035,10 +1142,8 @@ static bool mlsa_repair_segments(Engine::Resident* r, double tol, std::vector<in
     sg.seg = (const jbk::MlsaSegment*)(d + o_tab);
     sg.state = (double*)(d + o_state);
     sg.mismatch = nullptr;
-    if (mg) JB_LAUNCH(jbk::launch_mglsa(r->layout, r->vp, r->vd, sg, 0, sg.n_seg, false, st));
-    else JB_LAUNCH(jbk::launch_mlsa_v3(r->layout, r->vp, r->vd, sg, 0, sg.n_seg, st, r->f64_tail));
-    const int cnt = mg ? (int)stride : 5 * 37;
-    JB_LAUNCH(jbk::launch_mlsa_seg_check(sg, r->d_worst, r->h_worst, st, (int)stride, cnt, mg, r->segs.state));
+    JB_LAUNCH(jbk::launch_mglsa(r->layout, r->vp, r->vd, sg, 0, sg.n_seg, false, st));
+    JB_LAUNCH(jbk::launch_mlsa_seg_check(sg, r->d_worst, r->h_worst, st, (int)stride, (int)stride, true, r->segs.state));
     JB_CUDA(cudaStreamSynchronize(st));  // `fix` and the scratch stay alive until here
     ok = *r->h_worst <= tol;
   } catch (...) {
@@ -1049,11 +1154,10 @@ static bool mlsa_repair_segments(Engine::Resident* r, double tol, std::vector<in
   c->dfree(d, cap);
   if (!ok) return false;
   r->repaired_segments = (int)fix.size();
-  if (touched) {
-    touched->clear();
-    for (const jbk::MlsaSegment& s : fix) touched->push_back(s.utt);
-    std::sort(touched->begin(), touched->end());
-    touched->erase(std::unique(touched->begin(), touched->end()), touched->end());
+  if (ranges) {
+    ranges->clear();
+    for (const jbk::MlsaSegment& s : fix)
+      ranges->push_back(RepairRange{s.utt, (int64_t)s.begin * r->vp.fperiod, (int64_t)s.end * r->vp.fperiod});
   }
   return true;
 }
@@ -1170,11 +1274,14 @@ Engine::Resident* Engine::prepare_tracks(const VocoderConfig& cfg, size_t n_utt,
   const size_t w_segstate = wk.take(plan.segs.size() * 2 * seg_state_doubles * 8);
   const size_t w_worst = wk.take(8);
   const size_t w_segmis = wk.take(plan.segs.size() * 8);
+  const size_t w_failcnt = wk.take(8);
+  const size_t fail_cap = std::max<size_t>(64, plan.segs.size() / 16);
+  const size_t w_faillist = wk.take(fail_cap * 4);
   const bool postfilter = cfg.stage == 0 && cfg.beta > 0.0 && M > 2;
   const bool first_rows = postfilter || cfg.stage != 0 || cfg.coefficient_rows;
   r->rows_given = cfg.coefficient_rows;
   const size_t w_bfirst = first_rows ? wk.take(n_utt * M * 8) : 0;
-  const bool need_binc = cfg.stage != 0;
+  const bool need_binc = cfg.stage != 0 || !plan.segs.empty();
   const size_t w_binc = need_binc ? wk.take((size_t)TF * M * 8) : 0;
   r->d_work = ctx->dalloc(wk.off, &r->work_cap);
   uint8_t* di = (uint8_t*)r->d_in;
@@ -1212,9 +1319,11 @@ Engine::Resident* Engine::prepare_tracks(const VocoderConfig& cfg, size_t n_utt,
   r->segs.seg = (const jbk::MlsaSegment*)(di + o_segs);
   r->segs.state = plan.segs.empty() ? nullptr : (double*)(dw + w_segstate);
   r->segs.mismatch = plan.segs.empty() ? nullptr : (double*)(dw + w_segmis);
+  r->segs.fail_count = plan.segs.empty() ? nullptr : (int*)(dw + w_failcnt);
+  r->segs.fail_list = plan.segs.empty() ? nullptr : (int*)(dw + w_faillist);
+  r->segs.fail_cap = plan.segs.empty() ? 0 : (int)fail_cap;
   r->seg_table = plan.segs;
   r->warm_frames = (int)(mlsa_warm_frames * (cfg.stage != 0 ? kMglsaWarmFactor : 1));
-  r->f64_tail = mlsa_f64_tail_setting(mlsa_f64_tail);
   r->whole.n_seg = (int)whole.size();
   r->whole.seg = (const jbk::MlsaSegment*)(di + o_whole);
   r->d_worst = (double*)(dw + w_worst);
@@ -1255,7 +1364,7 @@ double Engine::run_resident(Resident* r, BatchTimings* tm) const {
     launch_mlpg_all(r, true);
   }
   JB_CUDA(cudaEventRecord(c->ev[3], c->stream));
-  launch_vocoder(r, mlsa_variant, false, c->ev[4], true);
+  launch_vocoder(r, mlsa_variant, false, c->ev[4], true, mlsa_cut_tolerance);
   JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
   JB_CUDA(cudaEventSynchronize(c->ev[5]));
   if (mlsa_cut_check_failed(r, mlsa_cut_tolerance)) {  // timed too: ev[5] is recorded again
@@ -1476,9 +1585,14 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
         }
       };
 
-      auto copy_utterance = [&](Chunk& ch, size_t u) {  // utterance u of the chunk (chunk-relative index)
+      auto copy_range = [&](Chunk& ch, const RepairRange& rr) {  // samples [n0, n1) of utterance rr.utt of the chunk
         Resident* r = ch.r;
-        const int64_t n0 = r->frame_off[u] * r->vp.fperiod, n1 = r->frame_off[u + 1] * r->vp.fperiod;
+        const int64_t base = r->frame_off[(size_t)rr.utt] * r->vp.fperiod;
+        int64_t n0 = base + rr.n0, n1 = base + rr.n1;
+        if (pcm16) {  // launch_pcm16 works on groups of four samples
+          n0 = n0 / 4 * 4;
+          n1 = std::min<int64_t>((n1 + 3) / 4 * 4, r->total_samples);
+        }
         if (n1 <= n0) return;
         if (pcm16) {
           int16_t* dev16 = reinterpret_cast<int16_t*>(r->vd.pulse);
@@ -1528,7 +1642,7 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
         wc.copy_stream = c->stream_copy;
         wc.done = c->ev[6];
         wc.direct = output_mode == 2;
-        launch_vocoder(r, mlsa_variant, dbg && dbg->stop_after_excitation, c->ev[4], true,
+        launch_vocoder(r, mlsa_variant, dbg && dbg->stop_after_excitation, c->ev[4], true, mlsa_cut_tolerance,
                        (dbg || output_mode == 0) ? nullptr : &wc);
         JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
         if (!r->copied_by_waves) {
@@ -1563,10 +1677,10 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
         if (mlsa_cut_check_failed(r, mlsa_cut_tolerance)) {
           // the copies above carried a waveform with a bad cut: re-filter the segments behind the failing
           // cuts and copy their utterances again; if that does not settle it, the whole chunk without cuts
-          std::vector<int32_t> touched;
-          if (mlsa_repair_segments(r, mlsa_cut_tolerance, &touched)) {
+          std::vector<RepairRange> ranges;
+          if (mlsa_repair_segments(r, mlsa_cut_tolerance, &ranges)) {
             JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
-            for (int32_t u : touched) copy_utterance(ch, (size_t)u);
+            for (const RepairRange& rr : ranges) copy_range(ch, rr);
           } else {
             mlsa_sequential_rerun(r);
             JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
@@ -1687,7 +1801,7 @@ double Stream::step(size_t n_frames, double* out, size_t* written) {
   r_->vd.frame_begin = (int)next_;
   r_->vd.frame_count = (int)n_frames;
   JB_CUDA(cudaEventRecord(c->ev[2], c->stream));
-  launch_vocoder(r_, e_->mlsa_variant, false, nullptr, false);
+  launch_vocoder(r_, e_->mlsa_variant, false, nullptr, false, e_->mlsa_cut_tolerance);
   JB_LAUNCH(jbk::launch_gather_chunk(r_->layout, r_->vp, r_->vd, r_->d_chunk, c->stream));
   JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
   JB_CUDA(cudaMemcpyAsync(out, r_->d_chunk, n * chunk * 8, cudaMemcpyDeviceToHost, c->stream));

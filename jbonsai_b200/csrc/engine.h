@@ -56,22 +56,20 @@ class Engine {
   void set_devices(const std::vector<int>& devices);
   const std::vector<int>& devices() const { return devices_; }
   int mlsa_variant = -1;  // -1 = default kernel (3: time-segmented; streams use 2)
-  // Variant 3: frames a segment filters ahead of its own range (from a zero state), and the largest
-  // state mismatch tolerated at a cut before the sequential kernel redoes the batch.
   // Device-side parameter gather (default): leaf pdf tables stay resident in HBM, the host sends
   // row indices and k_gather_states interpolates. false = the host packs interpolated vectors.
   bool device_gather = true;
+  // Variant 3: frames a segment filters ahead of its own range (from a zero state).
   int mlsa_warm_frames = 40;
-  // Of those, how many (the ones next to the own range) run in double precision; the ones before them run in
-  // FP32 (k_mlsa_v3 built with JB_V3_F32_HEAD=1; measured: the FP32 error does not fade in time, see
-  // mlsa_seg.cu). < 0 (default): the whole warm-up in double precision.
-  int mlsa_f64_tail = -1;
-  // Largest accepted state mismatch across a cut. Two correct trajectories with different rounding
-  // histories already differ by up to ~3e-8 in the delay-line taps (measured floor: nitech 4e-9,
-  // tohoku-f01 3e-8, independent of the warm-up length beyond the knee), while a short warm-up
-  // decays by ~0.35 decades per frame; a tap error d moves the output by at most sum|c_k| d ~ 8 d,
-  // so 1e-7 keeps the waveform inside the 1e-6 bar.
-  double mlsa_cut_tolerance = 1e-7;
+  // Variant 3: bound on the waveform error a cut may cause. The device compares, for every cut, the state the
+  // segment reached after its warm-up with the true one (the end state of the segment before it) and scales
+  // the largest difference d to what it can do to the output: a tap error d moves a stage output by at most
+  // d * sum_k |c_k| (the coefficients of the frame at the cut) and the waveform by about as much, times the
+  // volume. A cut whose bound exceeds this value is repaired (Engine::mlsa_repair_segments); half the 1e-6 bar
+  // of the north star. Two correct trajectories with different rounding histories already differ by up to
+  // ~3e-8 in the delay-line taps (measured floor: nitech 4e-9, tohoku-f01 3e-8), i.e. ~2e-7 in this measure.
+  // Stage != 0 (MGLSA): the state mismatch relative to the state's scale is held to 1e-9 instead.
+  double mlsa_cut_tolerance = 5e-7;
   // How synthesize_batch brings the waveform to the host: 0 = one copy after the filter, 1 = several
   // filter waves (output_waves), each copied under the next one (default), 2 = the filter stores
   // straight into the pinned output buffer (zero-copy; measured slower: SM stores reach ~34 GB/s

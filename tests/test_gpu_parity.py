@@ -355,8 +355,9 @@ def test_segmented_filter_tohoku_stays_segmented(genji_labels):
 
 def test_segmented_filter_repairs_a_few_bad_cuts(genji_labels, orc):
     # 8 frames of warm-up leave the cuts of this utterance off by more than the tolerance; with only a
-    # handful of them the segments behind them are filtered again with a longer warm-up, checked again,
-    # and only their utterance is copied again: no sequential pass, same result
+    # handful of them the head of every segment behind a failing cut is filtered again from the exact state
+    # (the end state of the segment before it) until it has merged with the first pass, and only those sample
+    # ranges are copied again: no sequential pass, same result
     labels = genji_labels[:22]
     e = jb.Engine.load([NITECH])
     e.set_mlsa_segmenting(8, 1e-7)
@@ -364,7 +365,7 @@ def test_segmented_filter_repairs_a_few_bad_cuts(genji_labels, orc):
     short = orc.synthesize(SAMPLE_SENTENCE_1, fma=True)
     tm = {}
     w, off = e.synthesize_batch([SAMPLE_SENTENCE_1, labels], timings=tm)
-    assert tm["mlsa_repaired"] > 0 and tm["mlsa_fallback"] == 0 and tm["mlsa_cut_worst"] <= 1e-7
+    assert tm["mlsa_repaired"] > 0 and tm["mlsa_fallback"] == 0 and tm["mlsa_cut_worst"] > 1e-7
     assert np.abs(w[off[1]:off[2]] - ow).max() <= WAVE_ATOL
     assert np.abs(w[off[0]:off[1]] - short).max() <= WAVE_ATOL
     p, poff = e.synthesize_batch_pcm16([SAMPLE_SENTENCE_1, labels])
@@ -442,3 +443,54 @@ def test_device_gather_equals_host_pack(multi):
     wa, offa = make(True).synthesize_batch(utts)
     wb, offb = make(False).synthesize_batch(utts)
     assert list(offa) == list(offb) and np.array_equal(wa, wb)
+
+
+def test_repair_with_zero_copy_output(genji_labels, orc):
+    # output mode 2: the filter stores straight into the pinned host buffer, the device copy of the waveform is
+    # never written. A repair must then merge into the host buffer, not copy stale device memory over it.
+    labels = genji_labels[:22]
+    e = jb.Engine.load([NITECH])
+    e.set_mlsa_segmenting(8, 1e-7)
+    e.set_output_mode(2)
+    tm = {}
+    w, off = e.synthesize_batch([SAMPLE_SENTENCE_1, labels], timings=tm)
+    assert tm["mlsa_repaired"] > 0 and tm["mlsa_fallback"] == 0
+    assert np.abs(w[off[1]:off[2]] - orc.synthesize(labels, fma=True)).max() <= WAVE_ATOL
+    assert np.abs(w[off[0]:off[1]] - orc.synthesize(SAMPLE_SENTENCE_1, fma=True)).max() <= WAVE_ATOL
+
+
+def test_cut_tolerance_scales_with_volume(genji_labels, orc):
+    # the cut check bounds the WAVEFORM error: the state mismatch is scaled by sum |c_k| of the frame at the
+    # cut and by the volume, so +12 dB must not let a four times larger error through
+    labels = genji_labels[:120]
+    e, o = jb.Engine.load([NITECH]), Oracle([NITECH])
+    e.set("volume", 12.0)
+    o.set("volume", 12.0)
+    tm = {}
+    w, _ = e.synthesize_batch([labels], timings=tm)
+    ow = o.synthesize(labels, fma=True)
+    assert tm["mlsa_segments"] > 20 and tm["mlsa_fallback"] == 0
+    assert np.abs(w - ow).max() <= WAVE_ATOL
+    e0 = jb.Engine.load([NITECH])
+    tm0 = {}
+    e0.synthesize_batch([labels], timings=tm0)
+    # same cuts, same states: the reported bound is the plain one times the linear gain of +12 dB
+    assert tm["mlsa_cut_worst"] == pytest.approx(tm0["mlsa_cut_worst"] * 10 ** (12 / 20), rel=1e-6)
+
+
+def test_noise_table_regrowth_keeps_older_batches_valid(genji_labels, orc):
+    # the per-device noise table grows (is re-allocated) when a longer utterance arrives; a stream or resident
+    # batch opened before must keep reading valid memory (they take the table pointer at launch time)
+    e = jb.Engine.load([NITECH])
+    g = e.generator([SAMPLE_SENTENCE_1])
+    r = e.prepare([SAMPLE_SENTENCE_2])
+    long_labels = genji_labels[:300]  # several times longer than anything before: forces the re-allocation
+    wl_, _ = e.synthesize_batch([long_labels])
+    assert np.abs(wl_ - orc.synthesize(long_labels, fma=True)).max() <= WAVE_ATOL
+    parts = g.generate_all(9)
+    g.close()
+    assert np.abs(parts[0] - orc.synthesize(SAMPLE_SENTENCE_1, fma=True)).max() <= WAVE_ATOL
+    r.run()
+    w2, _ = r.fetch()
+    r.close()
+    assert np.abs(w2 - orc.synthesize(SAMPLE_SENTENCE_2, fma=True)).max() <= WAVE_ATOL
