@@ -280,6 +280,8 @@ def run_b200(args, rank, world, local):
     red = Reducer(world, "nccl" if world > 1 else None, local)
     barrier, max_over_ranks, sum_over_ranks = red.barrier, red.max, red.sum
 
+    if world > 1:  # several ranks share the host: cores / ranks front-end threads each
+        jb.set_host_threads(max(1, (os.cpu_count() or 1) // world))
     voice, utts = build_workload(args, rank, ngpu, ranks_here=here)
     eng = jb.Engine.load([voice])
     devs = list(range(ngpu)) if single else [local]

@@ -75,9 +75,10 @@ int jb_engine_set_mlsa_variant(jb_engine* e, int variant);
 int jb_engine_set_device_gather(jb_engine* e, int enabled);
 /* Variant 3 cuts utterances into time segments that are filtered concurrently; each segment first
  * filters `warm_frames` frames ahead of its own range from a zero state (default 40). The states on
- * both sides of every cut are compared on the device; when they differ by more than `cut_tolerance`
- * (default 1e-7, absolute: the rounding-noise floor of that comparison is ~3e-8 on the shipped voices, and a
- * tap error d moves the output by at most ~8 d) the batch is filtered again by the sequential kernel. */
+ * both sides of every cut are compared on the device and the largest difference d of a cut is scaled to a
+ * bound on the waveform error, d * max(1, sum_k |c_k| of the frame at the cut) * volume. A cut whose bound
+ * exceeds `cut_tolerance` (default 5e-7, half the 1e-6 bar) is repaired: the head of the segment behind it is
+ * filtered again from the exact state; if that does not settle it the sequential kernel redoes the batch. */
 int jb_engine_set_mlsa_segmenting(jb_engine* e, int warm_frames, double cut_tolerance);
 /* How jb_engine_synthesize_batch brings the waveform (8 B per sample, the Vec<f64> of
  * engine.rs:294) to the host. 1 (default): the batch is filtered in three launches, each part copied
@@ -104,9 +105,9 @@ int jb_engine_synthesize(const jb_engine* e, const char* const* lines, size_t n_
  * [0] host front-end ms [1] pack ms [2] H2D ms [3] kernels ms [4] D2H ms [5] MLPG ms
  * [6] excitation ms [7] MLSA ms [8] H2D bytes [9] D2H bytes [10] frames [11] samples
  * [12] voiced samples [13] kernel launches [14] MLSA time segments [15] frames filtered including
- * warm-up [16] largest state mismatch at a cut (after a repair pass: of the repaired cuts) [17] passes
- * redone without cuts by the sequential kernel [18] segments re-filtered with a longer warm-up after
- * their cut check failed. */
+ * warm-up [16] largest waveform-error bound of a cut in the first pass [17] passes redone without cuts
+ * by the sequential kernel [18] segments whose head was re-filtered from the exact state after their cut
+ * check failed. */
 int jb_engine_synthesize_batch(const jb_engine* e, const char* const* lines, const size_t* line_off,
                                size_t n_utt, double** out, size_t* out_off, double* timings);
 /* The same synthesis delivered as 16-bit PCM: every f64 sample x becomes
@@ -181,9 +182,26 @@ int jb_resident_rows(const jb_engine* e, jb_resident* r, double* out, size_t cap
 int jb_resident_run(const jb_engine* e, jb_resident* r, double* device_ms, double* timings);
 int jb_resident_fetch(const jb_engine* e, jb_resident* r, double** out, size_t* out_off);
 void jb_resident_free(const jb_engine* e, jb_resident* r);
+/* Device-resident delivery (the launcher seam a GPU-side consumer binds; no 8 B/sample D2H copy).
+ * jb_resident_device_output: the waveform of the last jb_resident_run as a DEVICE pointer, out_off[n_utt]
+ * doubles on CUDA device *device, valid until the next run / free of `r`; the producing stream is
+ * synchronised before the call returns, so any stream of the caller may read it.
+ * jb_engine_synthesize_batch_device: Engine::synthesize for a batch (engine.rs:294-296) whose Vec<f64> stays
+ * in HBM: prepare + run + device output in one call; release *keep with jb_resident_free when done. */
+int jb_resident_device_output(const jb_engine* e, jb_resident* r, const double** d_out, size_t* out_off, int* device);
+int jb_engine_synthesize_batch_device(const jb_engine* e, const char* const* lines, const size_t* line_off, size_t n_utt,
+                                      int device_index, jb_resident** keep, const double** d_out, size_t* out_off,
+                                      double* timings);
+/* Process-wide knobs (no reference equivalent). jb_set_host_threads: host threads the front-end and the
+ * batching layer use (0 = all cores; env JB_HOST_THREADS) - set it to cores / ranks when several processes
+ * share a box. jb_trim_pools: frees the cached pinned host buffers (up to 24 GB are kept for reuse);
+ * returns the bytes released. */
+int jb_set_host_threads(int n);
+size_t jb_trim_pools(void);
 
 /* Engine::generator + SpeechGenerator (src/engine.rs:301, src/speech.rs:25-96), batched:
  * MLPG runs at open; every step emits up to n_frames frames per utterance. */
+/* `device`: index into the engine's device list (jb_engine_set_devices), as for jb_resident_prepare. */
 int jb_stream_open(const jb_engine* e, const char* const* lines, const size_t* line_off,
                    size_t n_utt, int device, jb_stream** out);
 size_t jb_stream_fperiod(const jb_stream* s);            /* SpeechGenerator::fperiod */

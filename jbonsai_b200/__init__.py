@@ -29,7 +29,8 @@ C_ABI_SYMBOLS = [
     "jb_engine_stream_parameters", "jb_engine_duration_parameters", "jb_engine_gv_parameters",
     "jb_resident_prepare", "jb_resident_prepare_tracks", "jb_resident_rows", "jb_engine_vocoder_synthesize", "jb_resident_run", "jb_resident_fetch", "jb_resident_free",
     "jb_stream_open", "jb_stream_fperiod", "jb_stream_synthesized_frames", "jb_stream_step",
-    "jb_stream_close",
+    "jb_stream_close", "jb_resident_device_output", "jb_engine_synthesize_batch_device", "jb_set_host_threads",
+    "jb_trim_pools",
 ]
 
 STATUS_NAMES = {
@@ -100,6 +101,17 @@ def measure_peaks(device: int = 0):
     t, g = C.c_double(), C.c_double()
     _check(lib.jb_device_measure_peaks(int(device), C.byref(t), C.byref(g)))
     return t.value, g.value
+
+
+def set_host_threads(n: int) -> None:
+    """Host threads of the front-end / batching layer (0 = all cores): cores // ranks when ranks share a box."""
+    _check(lib.jb_set_host_threads(int(n)))
+
+
+def trim_pools() -> int:
+    """Frees the cached pinned host buffers of the library; returns the bytes released."""
+    lib.jb_trim_pools.restype = C.c_size_t
+    return int(lib.jb_trim_pools())
 
 
 def _lines(lines: Sequence[str]):
@@ -343,6 +355,16 @@ class Engine:
         _check(lib.jb_resident_prepare(self._h, arr, offs, C.c_size_t(n), int(device_index), C.byref(r)))
         return Resident(self, r, n)
 
+    def synthesize_batch_device(self, utts: Sequence[Sequence[str]], device_index: int = 0):
+        """Engine::synthesize for a batch whose Vec<f64> stays in HBM: (Resident to keep alive, device pointer,
+        out_off)."""
+        arr, offs, n = _flatten(utts)
+        r, ptr = C.c_void_p(), C.c_void_p()
+        out_off = (C.c_size_t * (n + 1))()
+        _check(lib.jb_engine_synthesize_batch_device(self._h, arr, offs, C.c_size_t(n), int(device_index), C.byref(r),
+                                                     C.byref(ptr), out_off, None))
+        return Resident(self, r, n), int(ptr.value or 0), np.array(list(out_off), dtype=np.int64)
+
     # -- the vocoder seam: Vocoder::new + SpeechGenerator::generate_all over parameter tracks
     @staticmethod
     def _tracks(spectrum, lf0, lpf, stage, use_log_gain, rate, alpha, beta, volume, fperiod, first_rows=None):
@@ -423,6 +445,14 @@ class Resident:
         buf = np.zeros((frames + self.n_utt) * nmcp)
         _check(lib.jb_resident_rows(self._e._h, self._h, buf.ctypes.data_as(C.POINTER(C.c_double)), C.c_size_t(buf.size)))
         return buf[:frames * nmcp].reshape(frames, nmcp), buf[frames * nmcp:].reshape(self.n_utt, nmcp)
+
+    def device_output(self):
+        """(device pointer, out_off, CUDA device) of the last run's waveform: it stays in HBM (no D2H copy)."""
+        ptr = C.c_void_p()
+        out_off = (C.c_size_t * (self.n_utt + 1))()
+        dev = C.c_int()
+        _check(lib.jb_resident_device_output(self._e._h, self._h, C.byref(ptr), out_off, C.byref(dev)))
+        return int(ptr.value or 0), np.array(list(out_off), dtype=np.int64), dev.value
 
     def fetch(self):
         out = C.POINTER(C.c_double)()

@@ -50,7 +50,7 @@ std::vector<std::vector<std::string>> to_utts(const char* const* lines, const si
     for (size_t u = a; u < b; ++u) utts[u].assign(lines + line_off[u], lines + line_off[u + 1]);
   };
   // ~40 label strings per utterance: for a big batch the copies are worth a few threads
-  const size_t nt = n_utt >= 256 ? std::min<size_t>(8, std::max(1u, std::thread::hardware_concurrency())) : 1;
+  const size_t nt = n_utt >= 256 ? std::min<size_t>(8, std::max(1u, std::thread::hardware_concurrency())) : 1;  // plain copies
   if (nt <= 1) {
     copy_range(0, n_utt);
   } else {
@@ -426,6 +426,41 @@ int jb_resident_fetch(const jb_engine* e, jb_resident* r, double** out, size_t* 
   memcpy(out_off, off.data(), off.size() * sizeof(size_t));
   JB_CATCH
 }
+
+int jb_resident_device_output(const jb_engine* e, jb_resident* r, const double** d_out, size_t* out_off, int* device) {
+  JB_TRY
+  std::vector<size_t> off;
+  r->e->resident_device_output(r->r, d_out, &off, device);
+  if (out_off) memcpy(out_off, off.data(), off.size() * sizeof(size_t));
+  JB_CATCH
+}
+
+int jb_engine_synthesize_batch_device(const jb_engine* e, const char* const* lines, const size_t* line_off, size_t n_utt,
+                                      int device_index, jb_resident** keep, const double** d_out, size_t* out_off,
+                                      double* timings) {
+  JB_TRY
+  jb::Engine::Resident* r = e->e->prepare(to_utts(lines, line_off, n_utt), device_index);
+  try {
+    jb::BatchTimings tm;
+    e->e->run_resident(r, &tm);
+    std::vector<size_t> off;
+    e->e->resident_device_output(r, d_out, &off, nullptr);
+    if (out_off) memcpy(out_off, off.data(), off.size() * sizeof(size_t));
+    fill_timings(tm, timings);
+  } catch (...) {
+    e->e->release(r);
+    throw;
+  }
+  *keep = new jb_resident{e->e, r};
+  JB_CATCH
+}
+
+int jb_set_host_threads(int n) {
+  jb::Engine::set_host_threads(n);
+  return JB_OK;
+}
+
+size_t jb_trim_pools(void) { return jb::Engine::trim_pools(); }
 
 void jb_resident_free(const jb_engine* e, jb_resident* r) {
   if (!r) return;

@@ -95,13 +95,39 @@ PinnedPool& pinned() {
   static PinnedPool* p = new PinnedPool();  // leaked on purpose: outlives static destructors
   return *p;
 }
+size_t pinned_trim() {  // frees every cached (not handed out) pinned block; returns the bytes released
+  PinnedPool& pp = pinned();
+  std::multimap<size_t, void*> drop;
+  size_t bytes = 0;
+  {
+    std::lock_guard<std::mutex> g(pp.mu);
+    drop.swap(pp.cached);
+    bytes = pp.cached_bytes;
+    pp.cached_bytes = 0;
+  }
+  for (auto& kv : drop) cudaFreeHost(kv.second);
+  return bytes;
+}
 
 size_t align_up(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+// Host threads the front-end and the batching layer may use: all cores by default; a process that shares the
+// box with others (one rank per GPU under torchrun) caps it with jb_set_host_threads / JB_HOST_THREADS, so that
+// eight ranks do not run eight times the core count.
+std::atomic<int> g_host_threads{0};
+size_t host_threads() {
+  int n = g_host_threads.load();
+  if (n <= 0) {
+    static const int env = getenv("JB_HOST_THREADS") ? atoi(getenv("JB_HOST_THREADS")) : 0;
+    n = env > 0 ? env : (int)std::max(1u, std::thread::hardware_concurrency());
+  }
+  return (size_t)n;
+}
 
 // Runs fn(0..n-1) on all host cores; rethrows the first jb::Error.
 template <class F>
 void parallel_for(size_t n, F fn) {
-  size_t nthreads = std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), n / 8 + 1);
+  size_t nthreads = std::min<size_t>(host_threads(), n / 8 + 1);
   if (nthreads <= 1) {
     for (size_t i = 0; i < n; ++i) fn(i);
     return;
@@ -298,6 +324,8 @@ DeviceCtx* Engine::ctx(int device) const {
 }
 
 void Engine::free_output(void* p) { pinned().release(p); }
+void Engine::set_host_threads(int n) { g_host_threads.store(n > 0 ? n : 0); }
+size_t Engine::trim_pools() { return pinned_trim(); }
 
 // Random::{nrandom, fill_queue} + rnd (src/vocoder/excitation.rs:197-237), run on the host so
 // that ln/sqrt come from the same libm the reference uses; extended lazily, 64 values a time.
@@ -358,7 +386,7 @@ std::vector<UtterancePack> Engine::build_packs(const std::vector<std::vector<std
     throw Error(kErrUnsupported, "voices without an LPF stream are not built yet");
   std::vector<UtterancePack> packs(utts.size());
   const std::vector<StreamTable>* tabs = device_gather ? &tables_ : nullptr;
-  size_t nthreads = std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), utts.size());
+  size_t nthreads = std::min<size_t>(host_threads(), utts.size());
   if (nthreads <= 1) {
     for (size_t u = 0; u < utts.size(); ++u) packs[u] = build_utterance(voices_, condition, utts[u], tabs);
     return packs;
@@ -1413,6 +1441,17 @@ void Engine::fetch_resident(Resident* r, double** out, std::vector<size_t>* out_
   *out = h;
 }
 
+void Engine::resident_device_output(Resident* r, const double** d_out, std::vector<size_t>* out_off, int* device) const {
+  DeviceCtx* c = r->ctx;
+  std::lock_guard<std::mutex> g(c->mu);
+  JB_CUDA(cudaSetDevice(c->device));
+  JB_CUDA(cudaStreamSynchronize(c->stream));
+  *d_out = r->result ? r->result : r->vd.wave;
+  if (device) *device = c->device;
+  out_off->assign((size_t)r->n_utt + 1, 0);
+  for (int u = 0; u <= r->n_utt; ++u) (*out_off)[(size_t)u] = (size_t)(r->frame_off[(size_t)u] * r->vp.fperiod);
+}
+
 std::vector<double> Engine::resident_rows(Resident* r) const {
   DeviceCtx* c = r->ctx;
   std::lock_guard<std::mutex> g(c->mu);
@@ -1459,6 +1498,8 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
   const double t0 = now_ms();
   const size_t n = utts.size();
   const int fperiod = (int)condition.fperiod;
+  if (pcm16 && fperiod % 4 != 0)
+    throw Error(kErrUnsupported, "16-bit PCM delivery needs fperiod % 4 == 0 (the quantiser packs four samples per store)");
   // touch the device even for an empty batch: there is no CPU path to fall back to
   std::vector<DeviceCtx*> ctxs;
   for (int d : devices_) ctxs.push_back(ctx(d));
@@ -1539,10 +1580,12 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
         }
       c->use_slot(0);
     };
+    // taken before the try block: the error path (free_chunks) touches the device context too
+    std::unique_lock<std::mutex> g(c->mu, std::defer_lock);
     try {
       const size_t u0 = cut[k], u1 = cut[k + 1];
       if (u1 <= u0) return;
-      std::lock_guard<std::mutex> g(c->mu);
+      g.lock();
       // chunks of this device: each is a complete pass (gather ... filter ... copy) of its own
       size_t nchunks = 1;
       if (pipelined) {
@@ -1772,14 +1815,25 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
 Stream::Stream(const Engine* e, const std::vector<std::vector<std::string>>& utts, int device)
     : e_(e), r_(nullptr) {
   std::vector<UtterancePack> packs = e->build_packs(utts);
-  DeviceCtx* c = e->ctx(device);
+  // `device` is an index into the engine's device list (jb_engine_set_devices), like everywhere in the C ABI
+  if (device < 0 || (size_t)device >= e->devices().size()) throw Error(kErrArgument, "device index out of range");
+  DeviceCtx* c = e->ctx(e->devices()[(size_t)device]);
   std::lock_guard<std::mutex> g(c->mu);
   r_ = Engine::make_resident(*e, c, packs.data(), packs.size(), true, e->condition, {});
-  // MLPG for the whole utterance up front, like Engine::generator (engine.rs:333-357)
-  launch_mlpg_all(r_, false);
-  if (r_->n_utt)
-    JB_CUDA(cudaMemsetAsync(r_->vd.state, 0, (size_t)r_->n_utt * jbk::kVocStateDoubles * 8, c->stream));
-  JB_CUDA(cudaStreamSynchronize(c->stream));
+  try {
+    // MLPG for the whole utterance up front, like Engine::generator (engine.rs:333-357)
+    launch_mlpg_all(r_, false);
+    if (r_->n_utt)
+      JB_CUDA(cudaMemsetAsync(r_->vd.state, 0, (size_t)r_->n_utt * jbk::kVocStateDoubles * 8, c->stream));
+    JB_CUDA(cudaStreamSynchronize(c->stream));
+  } catch (...) {
+    cudaStreamSynchronize(c->stream);
+    c->dfree(r_->d_in, r_->in_cap);
+    c->dfree(r_->d_work, r_->work_cap);
+    delete r_;
+    r_ = nullptr;
+    throw;
+  }
 }
 
 Stream::~Stream() { e_->release(r_); }

@@ -129,7 +129,15 @@ class Engine {
   void fetch_resident(Resident* r, double** out, std::vector<size_t>* out_off) const;
   void release(Resident* r) const;
 
+  // Device-resident delivery: the waveform of the last run_resident stays in HBM. *d_out: its device pointer
+  // (out_off[n_utt] doubles, on CUDA device *device), valid until the next run_resident / release of `r`.
+  void resident_device_output(Resident* r, const double** d_out, std::vector<size_t>* out_off, int* device) const;
+
   static void free_output(void* p);
+  // Host threads the front-end and the batching layer use (0 = all cores; also JB_HOST_THREADS).
+  static void set_host_threads(int n);
+  // Frees the cached pinned host buffers of the process-wide pool; returns the bytes released.
+  static size_t trim_pools();
 
   std::vector<double> noise_prefix(size_t n) const;  // first n Gaussians (host table)
 

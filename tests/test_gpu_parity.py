@@ -494,3 +494,21 @@ def test_noise_table_regrowth_keeps_older_batches_valid(genji_labels, orc):
     w2, _ = r.fetch()
     r.close()
     assert np.abs(w2 - orc.synthesize(SAMPLE_SENTENCE_2, fma=True)).max() <= WAVE_ATOL
+
+
+def test_device_resident_output_seam(eng, orc):
+    # jb_engine_synthesize_batch_device: the waveform stays in HBM for a GPU-side consumer (no 8 B/sample D2H);
+    # read back here through the CUDA runtime, independently of the library's own copy path
+    from cuda.bindings import runtime as cudart
+    utts = [SAMPLE_SENTENCE_1, SAMPLE_SENTENCE_2]
+    keep, dptr, off = eng.synthesize_batch_device(utts)
+    assert dptr != 0 and off[-1] == 66480 + 100800
+    host = np.empty(int(off[-1]), dtype=np.float64)
+    (err,) = cudart.cudaMemcpy(host.ctypes.data, dptr, host.nbytes, cudart.cudaMemcpyKind.cudaMemcpyDeviceToHost)
+    assert int(err) == 0
+    p2, off2, dev = keep.device_output()
+    assert p2 == dptr and list(off2) == list(off) and dev == 0
+    keep.close()
+    w, woff = eng.synthesize_batch(utts)
+    assert list(woff) == list(off) and np.array_equal(host, w)
+    assert np.abs(host[: off[1]] - orc.synthesize(SAMPLE_SENTENCE_1, fma=True)).max() <= WAVE_ATOL
