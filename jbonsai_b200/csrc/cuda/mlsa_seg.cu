@@ -437,11 +437,9 @@ static int launch_v3_t(const BatchLayout& b, const VocoderParams& p, const Vocod
   // 1 - alpha^2 as a parameter: derived in the kernel it was re-computed from the constant bank at the
   // top of every sample: a load and two dependent FP64 operations on the serial path of the filter
   const size_t smem = sizeof(WarpShared<NM>) * kWPB;
-  static bool configured = false;  // per instantiation
-  if (!configured) {
+  {  // per device (context), not per process: set it at every launch, it costs microseconds
     const cudaError_t e = cudaFuncSetAttribute(k_mlsa_v3<NM, kWPB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
-    configured = true;
   }
   k_mlsa_v3<NM, kWPB><<<(warps + kWPB - 1) / kWPB, 32 * kWPB, smem, stream>>>(
       b, p, d, sg, seg_first, seg_first + seg_count, 1.0 - p.alpha * p.alpha, mlsa_v3_chunk(p.fperiod));

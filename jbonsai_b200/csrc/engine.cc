@@ -1080,7 +1080,15 @@ static bool mlsa_repair_segments(Engine::Resident* r, double tol, std::vector<Re
   JB_CUDA(cudaMemcpyAsync(ids.data(), r->segs.fail_list, (size_t)nfail * 4, cudaMemcpyDeviceToHost, st));
   JB_CUDA(cudaStreamSynchronize(st));
   std::sort(ids.begin(), ids.end());
-  const int repair_frames = std::max(32, r->warm_frames);  // the mismatch left by the warm-up has this long to fade
+  // How long the mismatch left by the warm-up needs to fade below the merge tolerance: the slowest decay seen on
+  // the shipped voices is ~0.2 decades per frame; a lone warp filters a frame in ~80 us, so the
+  // range is kept as short as the worst bound of this pass allows. The merge check decides whether it was enough.
+  const double worst = r->h_worst ? *r->h_worst : 0.0;
+  int repair_frames = std::max(32, r->warm_frames);
+  if (worst > 0.0 && worst < 1e300 && tol > 0.0) {
+    const double decades = std::log10(std::max(worst / (0.2 * tol), 1.0));
+    repair_frames = std::min(repair_frames, std::max(8, (int)std::ceil(decades / 0.2) + 4));
+  }
   std::vector<jbk::MlsaSegment> fix;
   for (int32_t id : ids) {
     if (id < 0 || id >= n) return false;
@@ -1710,6 +1718,28 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
           dbg->frame_off = r->frame_off;
         }
       }
+      // All kernels done; the copies of the last waves are still crossing PCIe on the copy stream. A failed cut
+      // is repaired now, under that copy tail: the repair kernel runs on the main stream, and only the final
+      // copy of the repaired sample ranges waits for the bulk copies (same destination, so it must come last).
+      JB_CUDA(cudaStreamSynchronize(c->stream));
+      if (pcm16) JB_CUDA(cudaStreamSynchronize(c->stream_copy));  // the repair's scratch is the PCM staging buffer
+      for (Chunk& ch : chunks) {
+        Resident* r = ch.r;
+        c->use_slot(ch.slot);
+        if (!mlsa_cut_check_failed(r, mlsa_cut_tolerance)) continue;
+        std::vector<RepairRange> ranges;
+        if (mlsa_repair_segments(r, mlsa_cut_tolerance, &ranges)) {
+          JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
+          if (r->copied_by_waves) JB_CUDA(cudaStreamWaitEvent(c->stream, c->ev[6], 0));
+          for (const RepairRange& rr : ranges) copy_range(ch, rr);
+        } else {  // the whole chunk without cuts
+          mlsa_sequential_rerun(r);
+          JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
+          if (r->copied_by_waves) JB_CUDA(cudaStreamWaitEvent(c->stream, c->ev[6], 0));
+          copy_result(ch);
+        }
+        JB_CUDA(cudaEventRecord(c->ev[6], c->stream));
+      }
       JB_CUDA(cudaStreamSynchronize(c->stream));
       JB_CUDA(cudaStreamSynchronize(c->stream_copy));
 
@@ -1717,21 +1747,6 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
       for (Chunk& ch : chunks) {
         Resident* r = ch.r;
         c->use_slot(ch.slot);
-        if (mlsa_cut_check_failed(r, mlsa_cut_tolerance)) {
-          // the copies above carried a waveform with a bad cut: re-filter the segments behind the failing
-          // cuts and copy their utterances again; if that does not settle it, the whole chunk without cuts
-          std::vector<RepairRange> ranges;
-          if (mlsa_repair_segments(r, mlsa_cut_tolerance, &ranges)) {
-            JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
-            for (const RepairRange& rr : ranges) copy_range(ch, rr);
-          } else {
-            mlsa_sequential_rerun(r);
-            JB_CUDA(cudaEventRecord(c->ev[5], c->stream));
-            copy_result(ch);
-          }
-          JB_CUDA(cudaEventRecord(c->ev[6], c->stream));
-          JB_CUDA(cudaStreamSynchronize(c->stream));
-        }
         t.mlsa_segments += r->segs.n_seg;
         t.mlsa_seg_frames += r->seg_frames;
         const double worst = r->segs.n_seg > 0 && r->h_worst && !(dbg && dbg->stop_after_excitation) ? *r->h_worst : 0.0;

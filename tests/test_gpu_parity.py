@@ -307,6 +307,20 @@ def test_multi_gpu_sharding_matches_single(eng):
     e2.set_devices(list(range(jb.device_count())))
     w2, off2 = e2.synthesize_batch(utts)
     assert list(off) == list(off2) and np.abs(w - w2).max() <= SCHED_ATOL
+    # a batch large enough for every device to get a full, segmented shard: against the oracle
+    e3 = jb.Engine.load([TOHOKU_NEUTRAL])
+    e3.set_devices(list(range(jb.device_count())))
+    big = wl.timed_batch(e3, 32 * jb.device_count(), wl.SEED_TOHOKU)
+    tm = {}
+    w3, off3 = e3.synthesize_batch(big, tm)
+    ow, ooff = Oracle([TOHOKU_NEUTRAL]).synthesize_batch(big, fma=True, nthreads=16)
+    assert list(off3) == list(ooff) and tm["mlsa_fallback"] == 0
+    assert np.abs(w3 - ow).max() <= WAVE_ATOL
+    # streams and resident batches on the second device of the engine's list (device = index into that list)
+    g = e2.generator([SAMPLE_SENTENCE_1], device=1)
+    parts = g.generate_all(11)
+    g.close()
+    assert np.abs(parts[0] - eng.synthesize(SAMPLE_SENTENCE_1)).max() <= SCHED_ATOL
 
 
 @pytest.mark.parametrize("variant", [0, 1, 2, 3])
