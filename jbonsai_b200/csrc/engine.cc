@@ -50,7 +50,9 @@ struct PinnedPool {
   std::map<void*, size_t> live;                  // handed out
   std::multimap<size_t, void*> cached;           // free, by capacity
   size_t cached_bytes = 0;
-  static constexpr size_t kMaxCached = (size_t)24 << 30;
+  // Free blocks kept for reuse. One f64 batch of BASELINE config 4 (16384 utterances in ONE call) is 31.5 GB:
+  // pinning that afresh costs ~14 s per call, so the cap must sit above it (JB_PINNED_CACHE_GB overrides).
+  const size_t kMaxCached = (size_t)(getenv("JB_PINNED_CACHE_GB") ? atoi(getenv("JB_PINNED_CACHE_GB")) : 48) << 30;
   void* alloc(size_t bytes) {
     if (bytes == 0) bytes = 8;
     {
