@@ -824,10 +824,38 @@ __device__ __forceinline__ double block_sum(double v, double* red) {
   return t;
 }
 
+// Three sums in one pass over the block: one barrier per call (the staging area alternates between two halves,
+// so the values of the call before may still be read while this one writes).
+__device__ __forceinline__ void block_sum3(double& a, double& b, double& c, double* red /* [2][3][8] */, int& phase) {
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+    a += __shfl_xor_sync(0xffffffffu, a, o);
+    b += __shfl_xor_sync(0xffffffffu, b, o);
+    c += __shfl_xor_sync(0xffffffffu, c, o);
+  }
+  const int w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  double* r = red + phase * 24;
+  phase ^= 1;
+  if ((threadIdx.x & 31) == 0) {
+    r[w] = a;
+    r[8 + w] = b;
+    r[16 + w] = c;
+  }
+  __syncthreads();
+  a = 0.0; b = 0.0; c = 0.0;
+  for (int i = 0; i < nw; ++i) {
+    a += r[i];
+    b += r[8 + i];
+    c += r[16 + i];
+  }
+}
+
 template <int BW, bool sysmajor>
 __global__ void __launch_bounds__(256, 3) k_mlpg_gv(BatchLayout b, StreamDev s, int64_t plane, int smem_frames) {
   extern __shared__ double sm[];
   __shared__ double red[8];
+  __shared__ double red3[48];
+  int phase = 0;
   const int sys = blockIdx.x;
   const int u = sys / s.dim, d = sys - u * s.dim;
   const int64_t soff = b.state_off[u], foff = b.frame_off[u];
@@ -896,9 +924,11 @@ __global__ void __launch_bounds__(256, 3) k_mlpg_gv(BatchLayout b, StreamDev s, 
         }
       vari = block_sum(a, red) / n;
     };
+    double m0;  // shift of the one-pass variance below: the mean (conv_gv keeps it, to rounding)
     {  // conv_gv (mlpg.rs:191-199)
       double mean, vari;
       calc_gv(mean, vari);
+      m0 = mean;
       const double ratio = sqrt(gv_mean / vari);
       for (int k = tid; k < Tp; k += nt)
         if (sw(k)) PAR[k * st] = ratio * (PAR[k * st] - mean) + mean;
@@ -910,21 +940,30 @@ __global__ void __launch_bounds__(256, 3) k_mlpg_gv(BatchLayout b, StreamDev s, 
     const double lenm1 = (double)(Tp - 1);
     double step = 0.1, prevobj = 0.0;
     for (int it = 1; it <= 5; ++it) {
-      double mean, vari;
-      calc_gv(mean, vari);
-      const double gvobj = -0.5 * 1.0 * vari * gv_vari * (vari - 2.0 * gv_mean);
-      double h = 0.0;  // calc_hmmobj_derivative (mlpg.rs:200-226)
+      // One pass, one barrier: the sums of calc_gv (mlpg.rs:168-188; variance about the shift m0, which is the
+      // mean to rounding, so nothing cancels) and of calc_hmmobj_derivative (mlpg.rs:200-226) together.
+      double a1 = 0.0, a2 = 0.0, h = 0.0;
       for (int k = tid; k < Tp; k += nt) {
-        double g = O[0][k * st] * PAR[k * st];
+        const double p = PAR[k * st];
+        if (sw(k)) {
+          a1 += p - m0;
+          a2 += (p - m0) * (p - m0);
+        }
+        double g = O[0][k * st] * p;
 #pragma unroll
         for (int i = 1; i < BW; ++i) {
           if (k + i < Tp) g += O[i][k * st] * PAR[(k + i) * st];
           if (k + 1 > i) g += O[i][(k - i) * st] * PAR[(k - i) * st];
         }
         GRAD[k * st] = g;
-        h += 1.0 * wnorm * PAR[k * st] * (WUM[k * st] - 0.5 * g);
+        h += 1.0 * wnorm * p * (WUM[k * st] - 0.5 * g);
       }
-      const double hmmobj = block_sum(h, red);
+      block_sum3(a1, a2, h, red3, phase);
+      const double dm = a1 / n;
+      const double mean = m0 + dm, vari = a2 / n - dm * dm;
+      m0 = mean;
+      const double gvobj = -0.5 * 1.0 * vari * gv_vari * (vari - 2.0 * gv_mean);
+      const double hmmobj = h;
       const double obj = -(hmmobj + gvobj);
       if (it > 1) {
         if (obj > prevobj)

@@ -763,7 +763,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   Carver wk;
   const size_t w_fstate = wk.take((size_t)TF * 4);
   size_t w_left[3] = {0}, w_right[3] = {0}, w_vidx[3] = {0}, w_nv[3] = {0}, w_par[3];
-  size_t scratch_bytes = 0, scratch1_bytes = 0;  // streams 0/2 run one after the other; stream 1 beside them
+  size_t scratch_bytes = 0, scratch1_bytes = 0;  // streams 1/2 run one after the other on the side stream; stream 0 beside them
   for (size_t s = 0; s < nstream; ++s) {
     if (is_msd[s]) {
       w_left[s] = wk.take((size_t)TF * 4);
@@ -773,7 +773,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
     }
     w_par[s] = wk.take((size_t)TF * dim[s] * 8);
     jbk::WindowSet ws = make_windows(vs.stream_windows(s));
-    size_t& sb = (s == 1) ? scratch1_bytes : scratch_bytes;
+    size_t& sb = (s != 0) ? scratch1_bytes : scratch_bytes;
     sb = std::max(sb, (size_t)jbk::mlpg_scratch_planes(ws.band_width(), has_gv[s]) *
                                                 (size_t)TF * dim[s] * 8);
   }
@@ -860,7 +860,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
     sd.right = is_msd[s] ? (int32_t*)(dw + w_right[s]) : nullptr;
     sd.vidx = is_msd[s] ? (int32_t*)(dw + w_vidx[s]) : nullptr;
     sd.nvoiced = is_msd[s] ? (int32_t*)(dw + w_nv[s]) : nullptr;
-    sd.scratch = (double*)(dw + (s == 1 ? w_scratch1 : w_scratch));
+    sd.scratch = (double*)(dw + (s != 0 ? w_scratch1 : w_scratch));
     sd.par = (double*)(dw + w_par[s]);
   }
   r->vp.nmcp = dim[0];
@@ -947,9 +947,10 @@ static void launch_mlpg_all(Engine::Resident* r, bool with_pulse) {
   JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[1], r->total_frames, r->total_states, sb));
   JB_LAUNCH(jbk::launch_frame_prep(r->layout, r->vp, r->vd, r->total_frames, 1, sb));
   if (with_pulse) JB_LAUNCH(jbk::launch_pulse(r->layout, r->vp, r->vd, r->total_samples, sb));
+  // the LPF stream (static window only: a per-frame kernel) needs nothing from MCP: it fills the side stream's slack
+  JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[2], r->total_frames, r->total_states, sb));
   JB_CUDA(cudaEventRecord(c->evx[1], sb));
   JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[0], r->total_frames, r->total_states, st));
-  JB_LAUNCH(jbk::launch_mlpg(r->layout, r->streams.s[2], r->total_frames, r->total_states, st));
   launch_spectrum_prep(r, st);
   JB_CUDA(cudaStreamWaitEvent(st, c->evx[1], 0));
 }
