@@ -45,6 +45,11 @@ int jb_device_count(void); /* number of usable CUDA devices, 0 if none */
  * rate of a DFMA micro-kernel in TFLOP/s and read+write bandwidth of a plain copy in GB/s. */
 int jb_device_measure_peaks(int device, double* fp64_fma_tflops, double* hbm_copy_gbs);
 
+/* Parity tap: the pitch period the vocoder derives from a log-F0 value, rate / exp(clamp(lf0)) with 0 for
+ * NODATA (src/vocoder/mod.rs:73-77), computed by the kernel the engine runs (device `exp`); tools/exp_sweep.py
+ * compares it with the host libm over the whole lf0 range. */
+int jb_device_pitch_period(int device, const double* lf0, size_t n, double rate, double* out);
+
 /* Engine::load (src/engine.rs:257) / Engine::load_from_bytes (src/engine.rs:263). */
 int jb_engine_load(const char* const* paths, size_t n_paths, jb_engine** out);
 int jb_engine_load_from_bytes(const uint8_t* const* bufs, const size_t* lens, size_t n,

@@ -30,7 +30,7 @@ C_ABI_SYMBOLS = [
     "jb_resident_prepare", "jb_resident_prepare_tracks", "jb_resident_rows", "jb_engine_vocoder_synthesize", "jb_resident_run", "jb_resident_fetch", "jb_resident_free",
     "jb_stream_open", "jb_stream_fperiod", "jb_stream_synthesized_frames", "jb_stream_step",
     "jb_stream_close", "jb_resident_device_output", "jb_engine_synthesize_batch_device", "jb_set_host_threads",
-    "jb_trim_pools",
+    "jb_trim_pools", "jb_device_pitch_period",
 ]
 
 STATUS_NAMES = {
@@ -101,6 +101,16 @@ def measure_peaks(device: int = 0):
     t, g = C.c_double(), C.c_double()
     _check(lib.jb_device_measure_peaks(int(device), C.byref(t), C.byref(g)))
     return t.value, g.value
+
+
+def device_pitch_period(lf0: np.ndarray, rate: float = 48000.0, device: int = 0) -> np.ndarray:
+    """rate / exp(clamp(lf0)) as the vocoder's frame-prep kernel computes it (0 for NODATA)."""
+    x = np.ascontiguousarray(lf0, dtype=np.float64)
+    out = np.empty_like(x)
+    D = C.POINTER(C.c_double)
+    _check(lib.jb_device_pitch_period(int(device), x.ctypes.data_as(D), C.c_size_t(x.size), C.c_double(rate),
+                                      out.ctypes.data_as(D)))
+    return out
 
 
 def set_host_threads(n: int) -> None:

@@ -101,6 +101,34 @@ int jb_device_measure_peaks(int device, double* fp64_fma_tflops, double* hbm_cop
   JB_CATCH
 }
 
+int jb_device_pitch_period(int device, const double* lf0, size_t n, double rate, double* out) {
+  JB_TRY
+  auto ck = [](cudaError_t e) {
+    if (e != cudaSuccess) throw jb::Error(jb::kErrCuda, std::string("CUDA error: ") + cudaGetErrorString(e));
+  };
+  ck(cudaSetDevice(device));
+  double *d_in = nullptr, *d_out = nullptr;
+  if (n == 0) return JB_OK;
+  ck(cudaMalloc((void**)&d_in, n * 8));
+  if (cudaMalloc((void**)&d_out, n * 8) != cudaSuccess) {
+    cudaFree(d_in);
+    throw jb::Error(jb::kErrCuda, "cudaMalloc failed");
+  }
+  cudaError_t e = cudaMemcpy(d_in, lf0, n * 8, cudaMemcpyHostToDevice);
+  jbk::BatchLayout bl{};
+  jbk::VocoderParams vp{};
+  vp.rate = rate;
+  jbk::VocoderDev vd{};
+  vd.lf0 = d_in;
+  vd.pitch = d_out;
+  if (e == cudaSuccess) e = (cudaError_t)jbk::launch_frame_prep(bl, vp, vd, (int64_t)n, 1, nullptr);  // the kernel the engine runs
+  if (e == cudaSuccess) e = cudaMemcpy(out, d_out, n * 8, cudaMemcpyDeviceToHost);
+  cudaFree(d_in);
+  cudaFree(d_out);
+  ck(e);
+  JB_CATCH
+}
+
 int jb_engine_load(const char* const* paths, size_t n, jb_engine** out) {
   JB_TRY
   std::vector<std::string> p(paths, paths + n);

@@ -11,10 +11,13 @@
 #include <algorithm>
 
 #include "kernels.h"
+#include "cr_exp.h"
 
 namespace jbk {
 
 namespace {
+
+#include "exp_table.inc"
 
 constexpr double kNoData = -1e10;
 constexpr double kMaxLf0 = 9.903487552536127;
@@ -42,7 +45,9 @@ __global__ void k_frame_prep(VocoderParams p, VocoderDev d, int64_t total_frames
     double pitch = 0.0;
     if (lf0 != kNoData) {
       double l = lf0 < kMinLf0 ? kMinLf0 : (lf0 > kMaxLf0 ? kMaxLf0 : lf0);
-      pitch = p.rate / exp(l);
+      // exp rounded correctly (cr_exp.h): the period, and with it every pulse position, is then the one the host
+      // libm gives wherever that rounds correctly too (99.93 % of the arguments; tools/exp_sweep.py)
+      pitch = p.rate / cr_exp(l, c_exp2_64, kLn2_64_hi, kLn2_64_mid, kLn2_64_lo, k64_Ln2);
     }
     d.pitch[gf] = pitch;
   }

@@ -4,6 +4,7 @@
 //   -> oracle::mlpg_create -> oracle::Vocoder           (= Engine::synthesize, engine.rs:294-366)
 // plus kernel-granularity entry points used to generate known answers for the CUDA tests.
 #include <atomic>
+#include <cmath>
 #include <cstring>
 #include <string>
 #include <thread>
@@ -230,6 +231,19 @@ int orc_synthesize_batch(void* h, const char* const* lines, const size_t* line_o
 void orc_noise(size_t n, double* out) {
   oracle::Random r;
   for (size_t i = 0; i < n; ++i) out[i] = r.nrandom();
+}
+
+// Pitch period of a frame, rate / exp(clamp(lf0)) with the host libm (vocoder/mod.rs:73-77): what Vocoder::synthesize
+// of this oracle computes per frame.
+void orc_pitch_period(const double* lf0, size_t n, double rate, double* out) {
+  for (size_t i = 0; i < n; ++i) {
+    double p = 0.0;
+    if (lf0[i] != -1e10) {
+      const double l = lf0[i] < jb::kMinLf0 ? jb::kMinLf0 : (lf0[i] > jb::kMaxLf0 ? jb::kMaxLf0 : lf0[i]);
+      p = rate / std::exp(l);
+    }
+    out[i] = p;
+  }
 }
 
 // SpeechGenerator over caller-provided [T][dim] parameters.

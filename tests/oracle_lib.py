@@ -88,6 +88,14 @@ class Oracle:
             self.h = None
 
 
+def pitch_period(lf0, rate=48000.0):
+    x = np.ascontiguousarray(lf0, dtype=np.float64)
+    out = np.empty_like(x)
+    _L.orc_pitch_period.restype = None
+    _L.orc_pitch_period(x.ctypes.data_as(D), C.c_size_t(x.size), C.c_double(rate), out.ctypes.data_as(D))
+    return out
+
+
 def noise(n):
     out = np.zeros(n)
     _L.orc_noise(C.c_size_t(n), out.ctypes.data_as(D))
