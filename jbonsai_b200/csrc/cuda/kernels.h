@@ -119,7 +119,7 @@ struct VocoderParams {
 //   [170..176) d11, [176..182) d12, [182..188) d22   (mlsa.rs:5-10)
 //   [188..223) coefficients[35]                      (vocoder/mod.rs Stage::Zero)
 //   [223] pitch_of_curr_point [224] pitch_counter    (excitation.rs:2-10)
-//   [226..251) variant 1 only: carry-in of tap block b = 1..5 of stage s at [226 + 5 s + b - 1]
+//   [226..251) variant 2 only: carry-in of tap block b = 1..5 of stage s at [226 + 5 s + b - 1]
 //              (== d21[s][6b-1] up to rounding; kept so that chunked == whole-utterance bit for bit)
 constexpr int kVocStateDoubles = 256;
 
@@ -156,8 +156,9 @@ int launch_pulse(const BatchLayout& b, const VocoderParams& p, const VocoderDev&
                  cudaStream_t stream);
 int launch_excitation(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,
                       int64_t total_frames, cudaStream_t stream);
-// variant: 0 = reference operation order, stage-per-lane; 1 = blocked-scan warp kernel;
-// 2 (default, -1) = software-pipelined blocked scan (mlsa.cu)
+// variant: 0 = reference operation order, stage-per-lane; anything else = software-pipelined blocked scan
+// (mlsa.cu, one warp per utterance). Vector lengths other than 35, frame periods that are no multiple of 16 and
+// alpha ~ 0 run the generic-length kernel (k_mlsa_any: any 2 <= nmcp <= 128, any fperiod).
 int launch_mlsa_v2(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, cudaStream_t stream);
 int launch_mlsa(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, int variant,
                 cudaStream_t stream);

@@ -605,30 +605,36 @@ __global__ void __launch_bounds__(32 * WPB) k_mlsa_v0(BatchLayout b, VocoderPara
   }
 }
 
-// ---------------------------------------------------------------- MLSA, variant 1 (default)
-// One warp per utterance; lane = 6*s + b owns taps 6b+1 .. 6b+6 of the warped delay line of Pade
-// stage s+1 (s = 0..4, b = 0..5; taps 35/36 and lanes 30/31 are padding with zero coefficients).
-//
-// Same filter as mlsa.rs:48-163, re-associated for parallelism (waveform parity is the north-star
-// tolerance 1e-6 abs, checked in tests; variant 0 above keeps the reference's operation order):
-//   * all-pass chain in "q form":  t'_j = (t_{j-1} + a t_j) - a t'_{j-1}   (== iaa*rem_j + a*t_j of
-//     mlsa.rs:141-153), so the tap recurrence is a first-order scan over j with ratio -a;
-//   * blocked scan: every lane scans its 6 taps with zero carry-in (z), the block aggregates E are
-//     exchanged through shared memory, the true carry K_b = sum_{m<b} (-a)^(6(b-1-m)) E_m + kappa_b u
-//     is formed per lane and folded back with one FMA per tap: t'_i = z_i + (-a)^(i+1) K_b;
-//   * df1/df2 sign pattern (x += v for odd i, x -= v for even i, then x += sum v):
-//     g0 = (x + A) - B, x' = x + 2A with A = odd-stage sum, B = even-stage sum.
-// Cross-lane traffic goes through double-buffered shared memory (SHFL.64 costs 8 issue cycles per
-// SMSP on B200, an LDS.128 broadcast one wavefront).
-template <int NM>
-__global__ void __launch_bounds__(32) k_mlsa_v1(BatchLayout b, VocoderParams p, VocoderDev d) {
-  constexpr int CH = 16;  // samples per staged chunk
-  __shared__ __align__(16) double sE[2][40];
-  __shared__ __align__(16) double sYP[2][40];
-  __shared__ __align__(16) double sV[2][16];  // [0..5) y_k (df2 stage outputs), [8..13) f_k (df1 sections)
-  __shared__ __align__(16) double sIn[2][CH];
-  __shared__ __align__(16) double sOut[CH];
+// ---------------------------------------------------------------- MLSA, any vector length
+// MelLogSpectrumApproximation::new(nmcp) and fir are generic in the vector length (mlsa.rs:38-45,128-163); the
+// fast kernels keep the delay lines in registers and exist for the lengths they were instantiated for. This one
+// takes any 2 <= nmcp <= kAnyMaxNM and any fperiod: one warp per utterance, lane i - 1 owns Pade stage i, its
+// delay line lives in shared memory and the taps run one at a time in the form of the reference's tail loop
+// (mlsa.rs:155-161; the four-tap blocks of :134-153 are the same recurrence unrolled). Stage outputs are combined
+// through shuffles in the reference's order (i = 5..1) as in variant 0. Slow (one serial chain per utterance) but
+// never JB_ERR_UNSUPPORTED. Streaming state (nmcp <= 35: the layout of kernels.h with NM - 1 taps per stage).
+constexpr int kAnyMaxNM = 128;
+__device__ __forceinline__ double fir_smem(double* dl, int NM, double x, double a, double iaa, const double* c) {
+  double rem = -a * x + dl[0];
+  dl[0] = iaa * x + a * dl[0];
+  double y = 0.0;
+  for (int k = 2; k < NM; ++k) {
+    const double dv = dl[k - 1];
+    const double nd = iaa * rem + a * dv;
+    rem = -a * rem + dv;
+    dl[k - 1] = nd;
+    y += c[k] * nd;
+  }
+  return y;
+}
 
+__global__ void __launch_bounds__(32) k_mlsa_any(BatchLayout b, VocoderParams p, VocoderDev d) {
+  extern __shared__ double any_sm[];
+  const int NM = p.nmcp, NT = NM - 1;
+  double* const s_dl = any_sm;           // [5][NT]
+  double* const s_c = s_dl + 5 * NT;     // [NM] interpolated coefficients
+  double* const s_cinc = s_c + NM;
+  double* const s_cc = s_cinc + NM;
   const int lane = threadIdx.x;
   const int u = b.order ? b.order[blockIdx.x] : (int)blockIdx.x;
   const int64_t foff = b.frame_off[u];
@@ -636,191 +642,95 @@ __global__ void __launch_bounds__(32) k_mlsa_v1(BatchLayout b, VocoderParams p, 
   int f0 = d.frame_begin, f1 = f0 + d.frame_count;
   if (f1 > T || f1 < f0) f1 = T;
   if (f0 >= f1) return;
-
-  const int s = lane / 6, bb = lane - 6 * s;  // s == 5: padding lanes
-  const bool real = s < 5;
-  const int gbase = 6 * s;
-  const double a = p.alpha, ma = -a, iaa = 1.0 - a * a;
-  double P[6], W[5];
-  {
-    double pw = ma;  // (-a)^(i+1)
-#pragma unroll
-    for (int i = 0; i < 6; ++i) { P[i] = pw; pw *= ma; }
-    const double A6 = P[5];  // (-a)^6
-#pragma unroll
-    for (int m = 0; m < 5; ++m) {
-      double w = 0.0;
-      if (m < bb) { w = 1.0; for (int e = 0; e < bb - 1 - m; ++e) w *= A6; }
-      W[m] = w;
-    }
-  }
-  double kap;  // coefficient of the stage input u in K_b
-  {
-    double pw = 1.0;
-    for (int e = 0; e < 6 * bb; ++e) pw *= ma;  // (-a)^(6b)
-    kap = iaa * pw / ma;                         // iaa * (-a)^(6b-1); b = 0: -iaa/a
-  }
-  const double pp1 = c_ppade[1], pp2 = c_ppade[2], pp3 = c_ppade[3], pp4 = c_ppade[4], pp5 = c_ppade[5];
-  const double fper = (double)p.fperiod;
-
-  for (int i = lane; i < 2 * 40; i += 32) { (&sE[0][0])[i] = 0.0; (&sYP[0][0])[i] = 0.0; }
-  if (lane < 32) { (&sV[0][0])[lane] = 0.0; }
-  __syncwarp();
-
-  // ---- state
-  double t[6] = {0, 0, 0, 0, 0, 0}, tm1 = 0.0, c[6] = {0, 0, 0, 0, 0, 0}, c1 = 0.0;
-  double d11 = 0.0, gin = 0.0, uin = 0.0;
-  int jtap[6];
-  bool cvalid[6];
-#pragma unroll
-  for (int i = 0; i < 6; ++i) {
-    jtap[i] = 6 * bb + 1 + i;
-    cvalid[i] = real && jtap[i] >= 2 && jtap[i] < NM;
-  }
+  const int st = lane + 1;
+  const bool stage_lane = lane < 5;
+  const double a = p.alpha, iaa = 1.0 - a * a;
+  const double pp = stage_lane ? c_ppade[st] : 0.0;
+  double* const dl = s_dl + (stage_lane ? lane : 0) * NT;
+  for (int k = lane; k < 5 * NT; k += 32) s_dl[k] = 0.0;
+  double d11 = 0.0, d12 = 0.0, d22 = 0.0, in1 = 0.0, in2 = 0.0;
+  const int T5 = 5 * NT;  // state layout: taps, then d11[6], d12[6], d22[6], coefficients[NM]
   double* stp = d.state ? d.state + (int64_t)u * kVocStateDoubles : nullptr;
-  const bool resume = stp != nullptr && f0 > 0;
-  if (resume && real) {
-#pragma unroll
-    for (int i = 0; i < 6; ++i) {
-      t[i] = jtap[i] < NM ? stp[s * (NM - 1) + jtap[i] - 1] : 0.0;
-      c[i] = cvalid[i] ? stp[188 + jtap[i]] : 0.0;
+  if (stp != nullptr && f0 > 0) {
+    for (int k = lane; k < T5; k += 32) s_dl[k] = stp[k];
+    for (int k = lane; k < NM; k += 32) s_c[k] = stp[T5 + 18 + k];
+    if (stage_lane) {
+      d11 = stp[T5 + st];
+      d12 = stp[T5 + 6 + st];
+      d22 = stp[T5 + 12 + st];
+      in1 = stp[T5 + 6 + st - 1];
+      in2 = stp[T5 + 12 + st - 1];
     }
-    tm1 = bb > 0 ? stp[226 + 5 * s + bb - 1] : 0.0;
-    c1 = stp[188 + 1];
-    d11 = stp[170 + s + 1];
-    gin = stp[176 + s];  // d12[s]: input of section s+1
-    uin = stp[182 + s];  // d22[s]: input of stage s+1
   }
-
-  const double* bsrc = d.b + foff * NM;
-  double* wv = d.wave + (foff + f0) * (int64_t)p.fperiod;
-  const int nsamp = (f1 - f0) * p.fperiod;  // multiple of fperiod; fperiod % CH == 0 is checked by the launcher
-  // stage the first chunk
-  if (lane < CH) sIn[0][lane] = wv[lane];
   __syncwarp();
-
-  int ib = 0;  // chunk buffer
-  int pb = 0;  // exchange buffer parity
-  double cinc[6] = {0, 0, 0, 0, 0, 0}, cc[6] = {0, 0, 0, 0, 0, 0}, c1inc = 0.0, cc1 = 0.0;
-  int left_in_frame = 0, f = f0;
-  for (int i0 = 0; i0 < nsamp; i0 += CH) {
-    if (left_in_frame == 0) {  // frame prologue (mod.rs:116-125)
-      const double* bf = bsrc + (int64_t)f * NM;
-#pragma unroll
-      for (int i = 0; i < 6; ++i) cc[i] = cvalid[i] ? bf[jtap[i]] : 0.0;
-      cc1 = bf[1];
-      if (f == 0) {  // is_first: coefficients = mc2b(first frame), before the post-filter
-        const double* b1 = d.b_first ? d.b_first + (int64_t)u * NM : bf;
-#pragma unroll
-        for (int i = 0; i < 6; ++i) c[i] = cvalid[i] ? b1[jtap[i]] : 0.0;
-        c1 = b1[1];
-      }
-#pragma unroll
-      for (int i = 0; i < 6; ++i) cinc[i] = (cc[i] - c[i]) / fper;
-      c1inc = (cc1 - c1) / fper;
-      left_in_frame = p.fperiod;
-    }
-    // prefetch the next chunk while this one is filtered
-    double xnext = 0.0;
-    if (lane < CH && i0 + CH < nsamp) xnext = wv[i0 + CH + lane];
-
-#pragma unroll 1
-    for (int j = 0; j < CH; ++j) {
-      const double e = sIn[ib][j];
-      // df1 section s+1 (mlsa.rs:54-66)
-      d11 = __fma_rn(a, d11, iaa * gin);
-      const double fk = d11 * c1;
-      // all-pass chain, zero carry-in
-      const double q0 = __fma_rn(a, t[0], tm1), q1 = __fma_rn(a, t[1], t[0]), q2 = __fma_rn(a, t[2], t[1]),
-                   q3 = __fma_rn(a, t[3], t[2]), q4 = __fma_rn(a, t[4], t[3]), q5 = __fma_rn(a, t[5], t[4]);
-      const double z0 = q0, z1 = __fma_rn(ma, z0, q1), z2 = __fma_rn(ma, z1, q2), z3 = __fma_rn(ma, z2, q3),
-                   z4 = __fma_rn(ma, z3, q4), z5 = __fma_rn(ma, z4, q5);
-      sE[pb][lane] = z5;
-      if (bb == 0 && real) sV[pb][8 + s] = fk;
-      __syncwarp();
-      const double2 e01 = *reinterpret_cast<const double2*>(&sE[pb][gbase]);
-      const double2 e23 = *reinterpret_cast<const double2*>(&sE[pb][gbase + 2]);
-      const double e4 = sE[pb][gbase + 4];
-      const double ka = __fma_rn(W[4], e4, __fma_rn(W[2], e23.x, W[0] * e01.x));
-      const double kb = __fma_rn(W[3], e23.y, W[1] * e01.y);
-      const double K = __fma_rn(kap, uin, ka + kb);
-      t[0] = __fma_rn(P[0], K, z0);
-      t[1] = __fma_rn(P[1], K, z1);
-      t[2] = __fma_rn(P[2], K, z2);
-      t[3] = __fma_rn(P[3], K, z3);
-      t[4] = __fma_rn(P[4], K, z4);
-      t[5] = __fma_rn(P[5], K, z5);
-      tm1 = bb > 0 ? K : 0.0;
-      const double ya = __fma_rn(c[4], t[4], __fma_rn(c[2], t[2], c[0] * t[0]));
-      const double yb = __fma_rn(c[5], t[5], __fma_rn(c[3], t[3], c[1] * t[1]));
-      sYP[pb][lane] = ya + yb;
-      // df1 combine (independent of the fir)
-      const double2 f12 = *reinterpret_cast<const double2*>(&sV[pb][8]);
-      const double2 f34 = *reinterpret_cast<const double2*>(&sV[pb][10]);
-      const double f5 = sV[pb][12];
-      const double Af = __fma_rn(pp5, f5, __fma_rn(pp3, f34.x, pp1 * f12.x));
-      const double Bf = __fma_rn(pp4, f34.y, pp2 * f12.y);
-      const double g0 = (e + Af) - Bf;
-      const double x1 = __fma_rn(2.0, Af, e);
-#pragma unroll
-      for (int i = 0; i < 6; ++i) c[i] += cinc[i];  // mod.rs:133-135
-      c1 += c1inc;
-      __syncwarp();
-      const double2 r01 = *reinterpret_cast<const double2*>(&sYP[pb][gbase]);
-      const double2 r23 = *reinterpret_cast<const double2*>(&sYP[pb][gbase + 2]);
-      const double2 r45 = *reinterpret_cast<const double2*>(&sYP[pb][gbase + 4]);
-      const double y = ((r01.x + r01.y) + (r23.x + r23.y)) + (r45.x + r45.y);
-      if (bb == 0 && real) sV[pb][s] = y;
-      __syncwarp();
-      const double2 y12 = *reinterpret_cast<const double2*>(&sV[pb][0]);
-      const double2 y34 = *reinterpret_cast<const double2*>(&sV[pb][2]);
-      const double y5 = sV[pb][4];
-      const double Ay = __fma_rn(pp5, y5, __fma_rn(pp3, y34.x, pp1 * y12.x));
-      const double By = __fma_rn(pp4, y34.y, pp2 * y12.y);
-      const double h0 = (x1 + Ay) - By;
-      const double out = __fma_rn(2.0, Ay, x1);
-      // inputs of the next sample: stage s+1 reads d22[s], section s+1 reads d12[s]
-      uin = s == 0 ? h0 : sV[pb][s > 0 ? s - 1 : 0];
-      gin = s == 0 ? g0 : sV[pb][8 + (s > 0 ? s - 1 : 0)];
-      if (lane == 0) sOut[j] = out * p.volume;
-      pb ^= 1;
+  const int fp = p.fperiod;
+  for (int f = f0; f < f1; ++f) {
+    const int64_t gf = foff + f;
+    for (int k = lane; k < NM; k += 32) {  // frame prologue (mod.rs:116-125)
+      const double cc = d.b[gf * NM + k];
+      const double c = f == 0 ? (d.b_first ? d.b_first[(int64_t)u * NM + k] : cc) : s_c[k];  // is_first (mod.rs:79-88)
+      s_c[k] = c;
+      s_cc[k] = cc;
+      s_cinc[k] = (cc - c) / (double)fp;
     }
     __syncwarp();
-    if (lane < CH) {
-      wv[i0 + lane] = sOut[lane];
-      sIn[ib ^ 1][lane] = xnext;
-    }
-    __syncwarp();
-    ib ^= 1;
-    left_in_frame -= CH;
-    if (left_in_frame == 0) {  // *coefficients = cc (mod.rs:140)
+    double* wv = d.wave + gf * fp;
+    for (int i0 = 0; i0 < fp; i0 += 32) {
+      const int nch = min(32, fp - i0);
+      const double xin = lane < nch ? wv[i0 + lane] : 0.0;
+      double xout = 0.0;
+      for (int j = 0; j < nch; ++j) {
+        double x = __shfl_sync(0xffffffffu, xin, j);
+        d11 = iaa * in1 + a * d11;  // df1 (mlsa.rs:54-66)
+        d12 = d11 * s_c[1];
+        double v = d12 * pp;
+        double out = 0.0;
 #pragma unroll
-      for (int i = 0; i < 6; ++i) c[i] = cc[i];
-      c1 = cc1;
-      ++f;
-    }
-  }
-
-  if (stp) {  // streaming state, same layout as variant 0
-    if (real) {
-#pragma unroll
-      for (int i = 0; i < 6; ++i)
-        if (jtap[i] < NM) {
-          stp[s * (NM - 1) + jtap[i] - 1] = t[i];
-          if (s == 0 && cvalid[i]) stp[188 + jtap[i]] = c[i];
+        for (int i = 5; i >= 1; --i) {
+          const double vi = __shfl_sync(0xffffffffu, v, i - 1);
+          x += (i & 1) ? vi : -vi;
+          out += vi;
         }
-      if (bb > 0) stp[226 + 5 * s + bb - 1] = tm1;
-      if (bb == 0) {
-        stp[170 + s + 1] = d11;
-        stp[176 + s] = gin;
-        stp[182 + s] = uin;
+        {
+          const double up = __shfl_up_sync(0xffffffffu, d12, 1);
+          in1 = (lane == 0) ? x : up;
+        }
+        x += out;
+        d22 = stage_lane ? fir_smem(dl, NM, in2, a, iaa, s_c) : 0.0;  // df2 (mlsa.rs:69-79)
+        v = d22 * pp;
+        out = 0.0;
+#pragma unroll
+        for (int i = 5; i >= 1; --i) {
+          const double vi = __shfl_sync(0xffffffffu, v, i - 1);
+          x += (i & 1) ? vi : -vi;
+          out += vi;
+        }
+        {
+          const double up = __shfl_up_sync(0xffffffffu, d22, 1);
+          in2 = (lane == 0) ? x : up;
+        }
+        x += out;
+        __syncwarp();
+        for (int k = lane; k < NM; k += 32) s_c[k] += s_cinc[k];  // mod.rs:133-135
+        __syncwarp();
+        if (lane == j) xout = x * p.volume;
       }
+      if (lane < nch) wv[i0 + lane] = xout;
     }
-    if (lane == 0) {
-      stp[188 + 1] = c1;
-      stp[176 + 5] = sV[pb ^ 1][8 + 4];  // d12[5], d22[5] (not inputs of any stage; kept for layout parity)
-      stp[182 + 5] = sV[pb ^ 1][4];
-      stp[188] = bsrc[(int64_t)(f1 - 1) * NM];  // coefficients[0] = cc[0] at a frame end
+    for (int k = lane; k < NM; k += 32) s_c[k] = s_cc[k];  // *coefficients = cc (mod.rs:140)
+    __syncwarp();
+  }
+  if (stp != nullptr) {
+    for (int k = lane; k < T5; k += 32) stp[k] = s_dl[k];
+    for (int k = lane; k < NM; k += 32) stp[T5 + 18 + k] = s_c[k];
+    if (stage_lane) {
+      stp[T5 + st] = d11;
+      stp[T5 + 6 + st] = d12;
+      stp[T5 + 12 + st] = d22;
+      if (lane == 0) {
+        stp[T5 + 6] = in1;
+        stp[T5 + 12] = in2;
+      }
     }
   }
 }
@@ -925,14 +835,16 @@ int launch_excitation(const BatchLayout& b, const VocoderParams& p, const Vocode
 int launch_mlsa(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, int variant,
                 cudaStream_t stream) {
   if (b.n_utt == 0) return 0;
-  if (p.nmcp != 35) return (int)cudaErrorInvalidValue;  // delay lines are register arrays
-  // variant 1 (default): blocked-scan kernel; needs alpha != 0 (kappa_0 = -iaa/alpha) and 16 | fperiod
-  const bool v1_ok = p.alpha > 1e-3 && p.fperiod % 16 == 0;
-  if ((variant < 0 || variant == 2) && v1_ok) return launch_mlsa_v2(b, p, d, stream);
-  if (variant == 1 && v1_ok) {
-    k_mlsa_v1<35><<<b.n_utt, 32, 0, stream>>>(b, p, d);
+  if (p.nmcp != 35 || (variant != 0 && (!(p.alpha > 1e-3) || p.fperiod % 16 != 0))) {
+    // no register-resident kernel for this vector length / frame period (or alpha ~ 0: the blocked scan divides by
+    // it): the generic one. Streaming state fits the per-utterance slot up to nmcp = 35.
+    if (p.nmcp < 2 || p.nmcp > kAnyMaxNM || (d.state != nullptr && p.nmcp > 35)) return (int)cudaErrorInvalidValue;
+    const size_t smem = (size_t)(5 * (p.nmcp - 1) + 3 * p.nmcp) * sizeof(double);
+    k_mlsa_any<<<b.n_utt, 32, smem, stream>>>(b, p, d);
     return (int)cudaGetLastError();
   }
+  // variants 1 / 2 (default): blocked-scan kernel, one warp per utterance (mlsa.cu)
+  if (variant != 0) return launch_mlsa_v2(b, p, d, stream);
   constexpr int G = 8, WPB = 1;
   const int upb = (32 / G) * WPB;
   k_mlsa_v0<G, 35, WPB><<<(b.n_utt + upb - 1) / upb, 32 * WPB, 0, stream>>>(b, p, d);

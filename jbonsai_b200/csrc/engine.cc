@@ -382,8 +382,8 @@ std::vector<UtterancePack> Engine::build_packs(const std::vector<std::vector<std
     throw Error(kErrUnsupported, "stage (GAMMA option) > 8");
   if (condition.stage != 0 && voices_.stream_metadata(0).vector_length > (size_t)jbk::kMglsaMaxOrder)
     throw Error(kErrUnsupported, "stage != 0 with a spectrum vector longer than 36");
-  if (condition.stage == 0 && voices_.stream_metadata(0).vector_length != 35)
-    throw Error(kErrUnsupported, "the MLSA kernels are built for 35 mel-cepstral coefficients");
+  if (condition.stage == 0 && (voices_.stream_metadata(0).vector_length < 2 || voices_.stream_metadata(0).vector_length > 128))
+    throw Error(kErrUnsupported, "mel-cepstral vectors of 2..128 coefficients");
   if (voices_.global_metadata().num_streams < 3 || voices_.stream_metadata(2).vector_length == 0)
     throw Error(kErrUnsupported, "voices without an LPF stream are not built yet");
   std::vector<UtterancePack> packs(utts.size());
@@ -1236,8 +1236,8 @@ Engine::Resident* Engine::prepare_tracks(const VocoderConfig& cfg, size_t n_utt,
     throw Error(kErrUnsupported, "vocoder: stage <= 8, and 3 <= nmcp <= 36 when stage != 0");
   if (cfg.stage != 0 && cfg.fperiod % 16 != 0)
     throw Error(kErrUnsupported, "vocoder: stage != 0 needs fperiod % 16 == 0");
-  if (cfg.stage == 0 && cfg.nmcp != 35)
-    throw Error(kErrUnsupported, "vocoder: the MLSA kernels are built for 35 mel-cepstral coefficients");
+  if (cfg.stage == 0 && (cfg.nmcp < 2 || cfg.nmcp > 128))
+    throw Error(kErrUnsupported, "vocoder: mel-cepstral vectors of 2..128 coefficients");
   DeviceCtx* ctx = this->ctx(devices_[(size_t)device_index]);
   std::lock_guard<std::mutex> g(ctx->mu);
   JB_CUDA(cudaSetDevice(ctx->device));

@@ -77,9 +77,53 @@ def test_stage0_knobs_and_other_orders(eng):
         w = eng.vocoder_synthesize(mcp, lf0, lpf, alpha=0.5, beta=beta, volume=0.5, rate=44100)
         ref = O.vocoder_ex(mcp, lf0, lpf, alpha=0.5, beta=beta, volume=0.5, rate=44100)
         assert np.abs(w - ref).max() <= WAVE_ATOL
-    with pytest.raises(jb.JbError) as ei:  # the MLSA kernels hold 34 taps in registers: other orders are refused
-        eng.vocoder_synthesize(mcp[:, :25], lf0, lpf)
-    assert ei.value.kind == "Unsupported"
+
+
+@pytest.mark.parametrize("nmcp,fperiod,variant", [
+    (25, 240, -1),   # time-segmented kernel instantiated for 25 coefficients
+    (25, 240, 2),    # sequential request: the generic-length kernel
+    (20, 240, -1), (40, 240, -1), (50, 80, -1),  # no register-resident kernel for these lengths: generic one
+    (35, 100, -1),   # even frame period that is no multiple of 16: segmented kernel with 50-sample chunks
+    (35, 75, -1),    # odd frame period: generic kernel
+    (35, 240, 0),    # reference operation order
+])
+def test_stage0_any_vector_length_and_frame_period(nmcp, fperiod, variant):
+    # MelLogSpectrumApproximation::new(nmcp) / fir are generic in the vector length (mlsa.rs:38-45,128-163) and
+    # SpeechGenerator in fperiod (speech.rs:25-51): nothing in this range may answer JB_ERR_UNSUPPORTED
+    e = jb.Engine.load([NITECH])
+    e.set_mlsa_variant(variant)
+    orc = O.Oracle([NITECH])
+    mcp, lf0, lpf = orc.parameters(SAMPLE_SENTENCE_2)
+    orc.close()
+    if nmcp <= 35:
+        spec = mcp[:, :nmcp]
+    else:  # longer vectors: small, decaying extra coefficients keep the filter stable
+        rng = np.random.default_rng(nmcp)
+        extra = 0.02 * rng.standard_normal((len(mcp), nmcp - 35)) / np.arange(36, nmcp + 1)[None, :]
+        spec = np.concatenate([mcp, extra], axis=1)
+    w = e.vocoder_synthesize(spec, lf0, lpf, alpha=0.55, fperiod=fperiod)
+    ref = O.vocoder_ex(spec, lf0, lpf, alpha=0.55, fperiod=fperiod, fma=True)
+    assert len(w) == len(ref) == len(lf0) * fperiod
+    assert np.abs(w - ref).max() <= WAVE_ATOL
+
+
+def test_stage0_25_coefficients_long_utterances_are_segmented():
+    # long enough for dozens of time segments per utterance with the 25-coefficient instantiation
+    e = jb.Engine.load([NITECH])
+    orc = O.Oracle([NITECH])
+    from jbonsai_b200 import workload as wl
+    lab = wl.genji_labels()[:150]
+    mcp, lf0, lpf = orc.parameters(lab)
+    orc.close()
+    spec = np.ascontiguousarray(mcp[:, :25])
+    r = e.prepare_tracks([spec, spec[:900]], [lf0, lf0[:900]], [lpf, lpf[:900]], alpha=0.55)
+    t = r.run()
+    w, off = r.fetch()
+    r.close()
+    assert t["mlsa_segments"] > 20 and t["mlsa_fallback"] == 0
+    ref = O.vocoder_ex(spec, lf0, lpf, alpha=0.55, fma=True)
+    assert np.abs(w[off[0]:off[1]] - ref).max() <= WAVE_ATOL
+    assert np.abs(w[off[1]:off[2]] - ref[: 900 * 240]).max() <= WAVE_ATOL
 
 
 def oracle_rows(spec, stage, alpha, log_gain, beta=0.0):
