@@ -197,6 +197,28 @@ int jb_resident_device_output(const jb_engine* e, jb_resident* r, const double**
 int jb_engine_synthesize_batch_device(const jb_engine* e, const char* const* lines, const size_t* line_off, size_t n_utt,
                                       int device_index, jb_resident** keep, const double** d_out, size_t* out_off,
                                       double* timings);
+/* The MLPG seam below the engine: MlpgAdjust::new(gv_weight, msd_threshold, stream, gv, windows) + create(durations)
+ * (src/mlpg_adjust/mod.rs:31-95) for ONE stream of n_utt utterances. state_off[n_utt + 1] (states, ascending from
+ * 0); durations[states] (frames per state); windows as in Windows (src/model/voice/window.rs:4-56): n_windows odd
+ * widths (<= 5, the static window first) and their coefficients concatenated; mean / vari [states][n_windows * dim]
+ * with index dim * w + d (src/model/mod.rs:62); msd [states] or NULL (not an MSD stream: every frame is kept);
+ * gv_mean / gv_vari [n_utt][dim] + gv_switch [states], or all NULL (no GV). *out: [frames][dim] row-major, -1e10
+ * (NODATA) in the masked frames of an MSD stream; release with jb_free. frame_off[n_utt + 1] optional. */
+typedef struct jb_mlpg_input {
+  size_t n_utt, dim;
+  const size_t* state_off;
+  const int32_t* durations;
+  size_t n_windows;
+  const size_t* window_widths;
+  const double* window_coefficients;
+  const double *mean, *vari, *msd;
+  double msd_threshold;
+  const double *gv_mean, *gv_vari;
+  const uint8_t* gv_switch;
+  double gv_weight;
+} jb_mlpg_input;
+int jb_engine_mlpg_create(const jb_engine* e, const jb_mlpg_input* in, int device_index, double** out, size_t* frame_off);
+
 /* Process-wide knobs (no reference equivalent). jb_set_host_threads: host threads the front-end and the
  * batching layer use (0 = all cores; env JB_HOST_THREADS) - set it to cores / ranks when several processes
  * share a box. jb_trim_pools: frees the cached pinned host buffers (up to 24 GB are kept for reuse);

@@ -30,7 +30,7 @@ C_ABI_SYMBOLS = [
     "jb_resident_prepare", "jb_resident_prepare_tracks", "jb_resident_rows", "jb_engine_vocoder_synthesize", "jb_resident_run", "jb_resident_fetch", "jb_resident_free",
     "jb_stream_open", "jb_stream_fperiod", "jb_stream_synthesized_frames", "jb_stream_step",
     "jb_stream_close", "jb_resident_device_output", "jb_engine_synthesize_batch_device", "jb_set_host_threads",
-    "jb_trim_pools", "jb_device_pitch_period",
+    "jb_trim_pools", "jb_device_pitch_period", "jb_engine_mlpg_create",
 ]
 
 STATUS_NAMES = {
@@ -375,6 +375,57 @@ class Engine:
                                                      C.byref(ptr), out_off, None))
         return Resident(self, r, n), int(ptr.value or 0), np.array(list(out_off), dtype=np.int64)
 
+    # -- the MLPG seam: MlpgAdjust::new + create (src/mlpg_adjust/mod.rs:31-95) for one stream
+    def mlpg_create(self, durations, dim, windows, mean, vari, msd=None, msd_threshold=0.5, gv=None, gv_weight=1.0,
+                    device_index: int = 0):
+        """State-level parameters -> [frames, dim] trajectories. `durations`, `mean`, `vari`, `msd` are one array
+        per utterance (or a single utterance's arrays); windows: coefficient lists, static window first;
+        gv: (mean [dim], vari [dim], switch [states]) per utterance or None. Returns a list of [T, dim] arrays
+        (one array for a single utterance)."""
+        single = not isinstance(durations, (list, tuple))
+        if single:
+            durations, mean, vari = [durations], [mean], [vari]
+            msd = None if msd is None else [msd]
+            gv = None if gv is None else [gv]
+        n = len(durations)
+        dur = [np.ascontiguousarray(d, dtype=np.int32).reshape(-1) for d in durations]
+        soff = np.zeros(n + 1, dtype=np.uint64)
+        soff[1:] = np.cumsum([len(d) for d in dur])
+        S, L = int(soff[-1]), dim * len(windows)
+        cat = lambda xs, dt=np.float64: np.ascontiguousarray(np.concatenate(
+            [np.asarray(x, dtype=dt).reshape(-1) for x in xs])) if xs and S else np.zeros(1, dtype=dt)
+        d_all, m_all, v_all = cat(dur, np.int32), cat(mean), cat(vari)
+        if S and (m_all.size != S * L or v_all.size != S * L):
+            raise ValueError("mean / vari must hold states x (windows x dim) values")
+        widths = (C.c_size_t * len(windows))(*[len(w) for w in windows])
+        coef = np.ascontiguousarray(np.concatenate([np.asarray(w, dtype=np.float64) for w in windows]))
+        D = C.POINTER(C.c_double)
+        inp = MlpgInput()
+        inp.n_utt, inp.dim = n, dim
+        inp.state_off = soff.ctypes.data_as(C.POINTER(C.c_size_t))
+        inp.durations = d_all.ctypes.data_as(C.POINTER(C.c_int32))
+        inp.n_windows, inp.window_widths = len(windows), widths
+        inp.window_coefficients = coef.ctypes.data_as(D)
+        inp.mean, inp.vari = m_all.ctypes.data_as(D), v_all.ctypes.data_as(D)
+        keep = []
+        if msd is not None:
+            ms = cat(msd)
+            keep.append(ms)
+            inp.msd = ms.ctypes.data_as(D)
+        inp.msd_threshold, inp.gv_weight = float(msd_threshold), float(gv_weight)
+        if gv is not None:
+            gm, gvv, gs = cat([g[0] for g in gv]), cat([g[1] for g in gv]), cat([g[2] for g in gv], np.uint8)
+            keep += [gm, gvv, gs]
+            inp.gv_mean, inp.gv_vari = gm.ctypes.data_as(D), gvv.ctypes.data_as(D)
+            inp.gv_switch = gs.ctypes.data_as(C.POINTER(C.c_uint8))
+        out = D()
+        foff = (C.c_size_t * (n + 1))()
+        _check(lib.jb_engine_mlpg_create(self._h, C.byref(inp), int(device_index), C.byref(out), foff))
+        fo = list(foff)
+        par = _take(out, fo[-1] * dim).reshape(fo[-1], dim)
+        res = [par[fo[u]:fo[u + 1]] for u in range(n)]
+        return res[0] if single else res
+
     # -- the vocoder seam: Vocoder::new + SpeechGenerator::generate_all over parameter tracks
     @staticmethod
     def _tracks(spectrum, lf0, lpf, stage, use_log_gain, rate, alpha, beta, volume, fperiod, first_rows=None):
@@ -436,6 +487,15 @@ class Engine:
         s = C.c_void_p()
         _check(lib.jb_stream_open(self._h, arr, offs, C.c_size_t(n), int(device), C.byref(s)))
         return SpeechGenerator(self, s, n)
+
+
+class MlpgInput(C.Structure):
+    _fields_ = [("n_utt", C.c_size_t), ("dim", C.c_size_t), ("state_off", C.POINTER(C.c_size_t)),
+                ("durations", C.POINTER(C.c_int32)), ("n_windows", C.c_size_t), ("window_widths", C.POINTER(C.c_size_t)),
+                ("window_coefficients", C.POINTER(C.c_double)), ("mean", C.POINTER(C.c_double)),
+                ("vari", C.POINTER(C.c_double)), ("msd", C.POINTER(C.c_double)), ("msd_threshold", C.c_double),
+                ("gv_mean", C.POINTER(C.c_double)), ("gv_vari", C.POINTER(C.c_double)),
+                ("gv_switch", C.POINTER(C.c_uint8)), ("gv_weight", C.c_double)]
 
 
 class Resident:

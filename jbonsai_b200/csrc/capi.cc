@@ -483,6 +483,36 @@ int jb_engine_synthesize_batch_device(const jb_engine* e, const char* const* lin
   JB_CATCH
 }
 
+int jb_engine_mlpg_create(const jb_engine* e, const jb_mlpg_input* in, int device_index, double** out, size_t* frame_off) {
+  JB_TRY
+  if (!in || !out) throw jb::Error(jb::kErrArgument, "mlpg: null argument");
+  jb::Engine::MlpgInput m;
+  m.n_utt = in->n_utt;
+  m.dim = in->dim;
+  m.state_off = in->state_off;
+  m.durations = in->durations;
+  if (in->n_windows > 8) throw jb::Error(jb::kErrUnsupported, "more than 4 windows per stream");
+  size_t o = 0;
+  for (size_t w = 0; w < in->n_windows; ++w) {
+    m.windows.emplace_back(in->window_coefficients + o, in->window_coefficients + o + in->window_widths[w]);
+    o += in->window_widths[w];
+  }
+  m.mean = in->mean;
+  m.vari = in->vari;
+  m.msd = in->msd;
+  m.msd_threshold = in->msd_threshold;
+  m.gv_mean = in->gv_mean;
+  m.gv_vari = in->gv_vari;
+  m.gv_switch = in->gv_switch;
+  m.gv_weight = in->gv_weight;
+  std::vector<double> par;
+  std::vector<size_t> foff;
+  e->e->mlpg_create(m, device_index, &par, &foff);
+  *out = dup_vec(par);
+  if (frame_off) memcpy(frame_off, foff.data(), foff.size() * sizeof(size_t));
+  JB_CATCH
+}
+
 int jb_set_host_threads(int n) {
   jb::Engine::set_host_threads(n);
   return JB_OK;

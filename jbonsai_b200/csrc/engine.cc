@@ -1382,6 +1382,120 @@ Engine::Resident* Engine::prepare_tracks(const VocoderConfig& cfg, size_t n_utt,
   return r.release();
 }
 
+void Engine::mlpg_create(const MlpgInput& in, int device_index, std::vector<double>* out,
+                         std::vector<size_t>* frame_off) const {
+  if (device_index < 0 || (size_t)device_index >= devices_.size()) throw Error(kErrArgument, "device index out of range");
+  if (in.dim == 0 || in.windows.empty() || !in.state_off || !in.mean || !in.vari || (in.n_utt && !in.durations))
+    throw Error(kErrArgument, "mlpg: dim, windows, state_off, durations, mean and vari are required");
+  if (in.windows.size() > (size_t)jbk::kMaxWin) throw Error(kErrUnsupported, "more than 4 windows per stream");
+  if ((in.gv_mean != nullptr) != (in.gv_vari != nullptr) || (in.gv_mean && !in.gv_switch))
+    throw Error(kErrArgument, "mlpg: gv_mean, gv_vari and gv_switch come together");
+  jbk::WindowSet ws{};
+  ws.nwin = (int)in.windows.size();
+  for (size_t i = 0; i < in.windows.size(); ++i) {
+    const std::vector<double>& w = in.windows[i];
+    if (w.empty() || w.size() % 2 == 0 || w.size() > (size_t)jbk::kMaxWinWidth)
+      throw Error(kErrUnsupported, "window widths are odd and at most 5");
+    ws.width[i] = (int)w.size();
+    for (size_t k = 0; k < w.size(); ++k) ws.coef[i][k] = w[k];
+  }
+  const size_t U = in.n_utt, dim = in.dim, L = dim * in.windows.size();
+  if (in.state_off[0] != 0) throw Error(kErrArgument, "mlpg: state_off must ascend from 0");
+  const size_t S = in.state_off[U];
+  std::vector<int64_t> soff(U + 1), foff(U + 1, 0);
+  int64_t max_frames = 0;
+  for (size_t u = 0; u < U; ++u) {
+    if (in.state_off[u + 1] < in.state_off[u]) throw Error(kErrArgument, "mlpg: state_off must ascend from 0");
+    int64_t t = 0;
+    for (size_t i = in.state_off[u]; i < in.state_off[u + 1]; ++i) {
+      if (in.durations[i] < 0) throw Error(kErrArgument, "mlpg: negative duration");
+      t += in.durations[i];
+    }
+    foff[u + 1] = foff[u] + t;
+    max_frames = std::max(max_frames, t);
+  }
+  for (size_t u = 0; u <= U; ++u) soff[u] = (int64_t)in.state_off[u];
+  const int64_t TF = foff[U];
+  frame_off->assign(U + 1, 0);
+  for (size_t u = 0; u <= U; ++u) (*frame_off)[u] = (size_t)foff[u];
+  out->assign((size_t)TF * dim, 0.0);
+  if (TF == 0) {
+    ctx(devices_[(size_t)device_index]);  // touch the device: there is no CPU path
+    return;
+  }
+  const bool msd = in.msd != nullptr, gv = in.gv_mean != nullptr;
+  DeviceCtx* c = ctx(devices_[(size_t)device_index]);
+  std::lock_guard<std::mutex> g(c->mu);
+  JB_CUDA(cudaSetDevice(c->device));
+  Carver wk;
+  const size_t o_soff = wk.take((U + 1) * 8), o_foff = wk.take((U + 1) * 8), o_dur = wk.take(S * 4);
+  const size_t o_mean = wk.take(S * L * 8), o_vari = wk.take(S * L * 8), o_msd = msd ? wk.take(S * 8) : 0;
+  const size_t o_gm = gv ? wk.take(U * dim * 8) : 0, o_gv = gv ? wk.take(U * dim * 8) : 0, o_gs = gv ? wk.take(S) : 0;
+  const size_t in_bytes = wk.off;
+  const size_t o_fstate = wk.take((size_t)TF * 4), o_ivar = wk.take(S * L * 8);
+  const size_t o_left = msd ? wk.take((size_t)TF * 4) : 0, o_right = msd ? wk.take((size_t)TF * 4) : 0;
+  const size_t o_vidx = msd ? wk.take((size_t)TF * 4) : 0, o_nv = msd ? wk.take(U * 4) : 0;
+  const size_t o_par = wk.take((size_t)TF * dim * 8);
+  const size_t o_scratch = wk.take((size_t)jbk::mlpg_scratch_planes(ws.band_width(), gv ? 1 : 0) * (size_t)TF * dim * 8);
+  size_t cap = 0;
+  uint8_t* d = (uint8_t*)c->dalloc(wk.off, &cap);
+  std::vector<uint8_t> h(in_bytes, 0);
+  memcpy(h.data() + o_soff, soff.data(), (U + 1) * 8);
+  memcpy(h.data() + o_foff, foff.data(), (U + 1) * 8);
+  memcpy(h.data() + o_dur, in.durations, S * 4);
+  memcpy(h.data() + o_mean, in.mean, S * L * 8);
+  memcpy(h.data() + o_vari, in.vari, S * L * 8);
+  if (msd) memcpy(h.data() + o_msd, in.msd, S * 8);
+  if (gv) {
+    memcpy(h.data() + o_gm, in.gv_mean, U * dim * 8);
+    memcpy(h.data() + o_gv, in.gv_vari, U * dim * 8);
+    memcpy(h.data() + o_gs, in.gv_switch, S);
+  }
+  try {
+    JB_CUDA(cudaMemcpyAsync(d, h.data(), in_bytes, cudaMemcpyHostToDevice, c->stream));
+    jbk::BatchLayout bl{};
+    bl.n_utt = (int)U;
+    bl.state_off = (const int64_t*)(d + o_soff);
+    bl.frame_off = (const int64_t*)(d + o_foff);
+    bl.durations = (const int32_t*)(d + o_dur);
+    bl.frame_state = (int32_t*)(d + o_fstate);
+    bl.max_frames = (int)max_frames;
+    bl.order = nullptr;
+    jbk::StreamSet ss{};
+    ss.n = 1;
+    jbk::StreamDev& sd = ss.s[0];
+    sd.dim = (int)dim;
+    sd.nwin = ws.nwin;
+    sd.is_msd = msd ? 1 : 0;
+    sd.has_gv = gv ? 1 : 0;
+    sd.windows = ws;
+    sd.msd_threshold = in.msd_threshold;
+    sd.gv_weight = in.gv_weight;
+    sd.mean = (const double*)(d + o_mean);
+    sd.vari = (const double*)(d + o_vari);
+    sd.ivar = (double*)(d + o_ivar);
+    sd.msd = msd ? (const double*)(d + o_msd) : nullptr;
+    sd.gv_mean = gv ? (const double*)(d + o_gm) : nullptr;
+    sd.gv_vari = gv ? (const double*)(d + o_gv) : nullptr;
+    sd.gv_switch = gv ? (const uint8_t*)(d + o_gs) : nullptr;
+    sd.left = msd ? (int32_t*)(d + o_left) : nullptr;
+    sd.right = msd ? (int32_t*)(d + o_right) : nullptr;
+    sd.vidx = msd ? (int32_t*)(d + o_vidx) : nullptr;
+    sd.nvoiced = msd ? (int32_t*)(d + o_nv) : nullptr;
+    sd.scratch = (double*)(d + o_scratch);
+    sd.par = (double*)(d + o_par);
+    JB_LAUNCH(jbk::launch_expand(bl, ss, c->stream));
+    JB_LAUNCH(jbk::launch_mlpg(bl, sd, TF, (int64_t)S, c->stream));
+    JB_CUDA(cudaMemcpyAsync(out->data(), sd.par, (size_t)TF * dim * 8, cudaMemcpyDeviceToHost, c->stream));
+    JB_CUDA(cudaStreamSynchronize(c->stream));
+  } catch (...) {
+    cudaStreamSynchronize(c->stream);
+    c->dfree(d, cap);
+    throw;
+  }
+  c->dfree(d, cap);
+}
+
 double Engine::run_resident(Resident* r, BatchTimings* tm) const {
   DeviceCtx* c = r->ctx;
   std::lock_guard<std::mutex> g(c->mu);

@@ -133,6 +133,25 @@ class Engine {
   // (out_off[n_utt] doubles, on CUDA device *device), valid until the next run_resident / release of `r`.
   void resident_device_output(Resident* r, const double** d_out, std::vector<size_t>* out_off, int* device) const;
 
+  // The MLPG seam (MlpgAdjust::new + create, src/mlpg_adjust/mod.rs:31-95) for one stream of n_utt utterances:
+  // state-level parameters in, [frames][dim] trajectories out (NODATA = -1e10 in masked frames of an MSD stream).
+  struct MlpgInput {
+    size_t n_utt = 0, dim = 0;
+    const size_t* state_off = nullptr;  // [n_utt + 1]
+    const int32_t* durations = nullptr; // [states] frames per state (>= 0)
+    std::vector<std::vector<double>> windows;  // Windows (window.rs:4-56): coefficient lists, static window first
+    const double* mean = nullptr;       // [states][nwin * dim], index dim * w + d (model/mod.rs:62)
+    const double* vari = nullptr;
+    const double* msd = nullptr;        // [states] or nullptr (not an MSD stream)
+    double msd_threshold = 0.5;
+    const double* gv_mean = nullptr;    // [n_utt][dim] or nullptr (no GV)
+    const double* gv_vari = nullptr;
+    const uint8_t* gv_switch = nullptr; // [states]
+    double gv_weight = 1.0;
+  };
+  // out: [frames][dim] (resized); frame_off: [n_utt + 1]
+  void mlpg_create(const MlpgInput& in, int device_index, std::vector<double>* out, std::vector<size_t>* frame_off) const;
+
   static void free_output(void* p);
   // Host threads the front-end and the batching layer use (0 = all cores; also JB_HOST_THREADS).
   static void set_host_threads(int n);
