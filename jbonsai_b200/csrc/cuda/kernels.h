@@ -237,6 +237,12 @@ constexpr int mglsa_state_doubles(int stage) { return stage * kMglsaMaxOrder; }
 int launch_mglsa(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, const MlsaSegments& sg,
                  int seg_first, int seg_count, bool literal, cudaStream_t stream);
 
+// Sequential MGLSA with carried state (generate_step with stage != 0; also any frame period): filters frames
+// [d.frame_begin, + d.frame_count) of every utterance in place in d.wave. `state`: [n_utt][kMglsaMaxStage][kMglsaMaxOrder]
+// delay lines carried between launches, or nullptr (whole utterances from a zero state).
+int launch_mglsa_stream(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, double* state,
+                        cudaStream_t stream);
+
 // Streaming: copy frames [frame_begin, frame_begin+frame_count) of every utterance into
 // chunk[n_utt][frame_count*fperiod] (zero padded past the end of an utterance).
 int launch_gather_chunk(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,

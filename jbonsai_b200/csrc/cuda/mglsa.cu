@@ -449,6 +449,75 @@ int launch_row_increments(const BatchLayout& b, const VocoderParams& p, const Vo
   return (int)cudaGetLastError();
 }
 
+namespace {
+// Sequential MGLSA with carried state: SpeechGenerator::generate_step (speech.rs:65-83) driving the Stage::NonZero arm
+// (vocoder/mod.rs:142-176) a few frames at a time, and any frame period. One thread per utterance filters frames
+// [frame_begin, frame_begin + frame_count) in place in d.wave: per sample the `stage` sections of mglsa.rs:15-19 one
+// after the other in the reference's operation order (dff, mglsa.rs:21-41), then the coefficient step
+// (mod.rs:169-171). The delay lines live in `state` ([n_utt][stage][kMG], local copy while the chunk runs); the
+// coefficients need no state (they restart from the row of the frame before at every frame, mod.rs:175).
+__global__ void __launch_bounds__(64) k_mglsa_stream(BatchLayout b, VocoderParams p, VocoderDev d, double* state) {
+  int u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= b.n_utt) return;
+  if (b.order) u = b.order[u];
+  const int64_t foff = b.frame_off[u];
+  const int T = (int)(b.frame_off[u + 1] - foff);
+  int f0 = d.frame_begin, f1 = f0 + d.frame_count;
+  if (f1 > T || f1 < f0) f1 = T;
+  if (f0 >= f1) return;
+  const int M = p.nmcp, fp = p.fperiod, NS = p.stage;
+  const double a = p.alpha, aa = 1.0 - a * a;
+  double dl[kMglsaMaxStage][kMG];
+  double* const st = state ? state + (int64_t)u * kMglsaMaxStage * kMG : nullptr;
+  for (int s = 0; s < NS; ++s)
+    for (int i = 0; i < kMG; ++i) dl[s][i] = (st && f0 > 0) ? st[s * kMG + i] : 0.0;
+  double c[kMG], cinc[kMG];
+  for (int f = f0; f < f1; ++f) {
+    const double* r0 = f == 0 ? d.b_first + (int64_t)u * M : d.b + (foff + f - 1) * M;  // mod.rs:92-107 / :175
+    const double* ri = d.binc + (foff + f) * M;
+    for (int k = 0; k < M; ++k) {
+      c[k] = r0[k];
+      cinc[k] = ri[k];
+    }
+    double* wv = d.wave + (foff + f) * fp;
+    for (int n = 0; n < fp; ++n) {
+      double x = wv[n];  // excitation times coefficients[0] (k_excitation, mod.rs:163)
+      for (int s = 0; s < NS; ++s) {  // dff (mglsa.rs:21-41)
+        double* dd = dl[s];
+        const double d0 = dd[0];
+        double y = __dmul_rn(d0, c[1]);
+        double prev_new = d0, old_next = dd[1];
+        for (int i = 1; i <= M - 2; ++i) {
+          const double cur_old = old_next;
+          old_next = dd[i + 1 < kMG ? i + 1 : i];
+          const double nw = __dadd_rn(cur_old, __dmul_rn(a, __dadd_rn(old_next, -prev_new)));
+          y = __dadd_rn(y, __dmul_rn(nw, c[i + 1]));
+          dd[i] = prev_new;
+          prev_new = nw;
+        }
+        dd[M - 1] = prev_new;
+        x = __dadd_rn(x, -y);
+        dd[0] = __dadd_rn(__dmul_rn(a, d0), __dmul_rn(aa, x));
+      }
+      for (int k = 0; k < M; ++k) c[k] = __dadd_rn(c[k], cinc[k]);
+      wv[n] = x * p.volume;
+    }
+  }
+  if (st)
+    for (int s = 0; s < NS; ++s)
+      for (int i = 0; i < kMG; ++i) st[s * kMG + i] = dl[s][i];
+}
+}  // namespace
+
+int launch_mglsa_stream(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, double* state,
+                        cudaStream_t stream) {
+  if (b.n_utt == 0) return 0;
+  if (p.nmcp < 3 || p.nmcp > kMG || p.stage < 1 || p.stage > kMglsaMaxStage || d.b_first == nullptr || d.binc == nullptr)
+    return (int)cudaErrorInvalidValue;
+  k_mglsa_stream<<<(b.n_utt + 63) / 64, 64, 0, stream>>>(b, p, d, state);
+  return (int)cudaGetLastError();
+}
+
 int launch_mglsa(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, const MlsaSegments& sg,
                  int seg_first, int seg_count, bool literal, cudaStream_t stream) {
   if (seg_count <= 0) return 0;

@@ -435,6 +435,7 @@ struct Engine::Resident {
   jbk::VocoderDev vd{};
   bool streaming = false;
   double* d_chunk = nullptr;  // streaming gather buffer
+  double* mg_state = nullptr; // streaming with stage != 0: MGLSA delay lines [n_utt][8][36] carried between chunks
   size_t chunk_cap = 0;
   int64_t h2d_bytes = 0;
   // device-side gather of the state-level parameters (streams whose pdf table is resident)
@@ -795,6 +796,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   const size_t w_runs = wk.take(((size_t)TF + 1) * 4);
   const size_t w_wave = wk.take((size_t)r->total_samples * 8);
   const size_t w_state = streaming ? wk.take(n_utt * jbk::kVocStateDoubles * 8) : 0;
+  const size_t w_mgstate = (streaming && cond.stage != 0) ? wk.take(n_utt * (size_t)jbk::kMglsaMaxStage * jbk::kMglsaMaxOrder * 8) : 0;
   const size_t w_out = segs.empty() ? 0 : wk.take((size_t)r->total_samples * 8);
   const size_t seg_state_doubles =
       cond.stage != 0 ? (size_t)jbk::mglsa_state_doubles((int)cond.stage) : (size_t)jbk::kMlsaSegStateDoubles;
@@ -884,6 +886,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   r->vd.runs = (int32_t*)(dw + w_runs);
   r->vd.wave = (double*)(dw + w_wave);
   r->vd.state = streaming ? (double*)(dw + w_state) : nullptr;
+  r->mg_state = (streaming && cond.stage != 0) ? (double*)(dw + w_mgstate) : nullptr;
   r->vd.out = segs.empty() ? nullptr : (double*)(dw + w_out);
   r->segs.n_seg = (int)segs.size();
   r->segs.seg = (const jbk::MlsaSegment*)(di + o_segs);
@@ -984,8 +987,12 @@ static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_exc
   r->cut_tol = cut_tol;
   if (stop_after_excitation) return;
   const bool mg = r->vp.stage != 0;  // MGLSA (mglsa.cu): segmented unless the sequential variant is forced
-  if (mg && (r->vd.out == nullptr || r->vp.fperiod % 16 != 0))
-    throw Error(kErrUnsupported, "stage != 0: streaming synthesis / fperiod not a multiple of 16 are not built");
+  if (mg && (r->vd.out == nullptr || r->vp.fperiod % 16 != 0 || r->streaming)) {
+    // generate_step with stage != 0 (state carried in mg_state), or a frame period the segmented kernel does not
+    // take: the sequential kernel, in place
+    JB_LAUNCH(jbk::launch_mglsa_stream(r->layout, r->vp, r->vd, r->streaming ? r->mg_state : nullptr, st));
+    return;
+  }
   const bool v3 = mg ? (variant < 0 || variant == 3) && r->segs.n_seg > 0
                      : (variant < 0 || variant == 3) && r->segs.n_seg > 0 && jbk::mlsa_v3_supports(r->vp.nmcp) &&
                            jbk::mlsa_v3_chunk(r->vp.fperiod) > 0 && r->vd.frame_begin == 0 && r->vd.frame_count < 0;
@@ -1234,8 +1241,6 @@ Engine::Resident* Engine::prepare_tracks(const VocoderConfig& cfg, size_t n_utt,
     throw Error(kErrArgument, "The number of low-pass filter coefficient must be odd numbers.");  // speech.rs:38-40
   if (cfg.stage > (size_t)jbk::kMglsaMaxStage || (cfg.stage != 0 && (cfg.nmcp > (size_t)jbk::kMglsaMaxOrder || cfg.nmcp < 3)))
     throw Error(kErrUnsupported, "vocoder: stage <= 8, and 3 <= nmcp <= 36 when stage != 0");
-  if (cfg.stage != 0 && cfg.fperiod % 16 != 0)
-    throw Error(kErrUnsupported, "vocoder: stage != 0 needs fperiod % 16 == 0");
   if (cfg.stage == 0 && (cfg.nmcp < 2 || cfg.nmcp > 128))
     throw Error(kErrUnsupported, "vocoder: mel-cepstral vectors of 2..128 coefficients");
   DeviceCtx* ctx = this->ctx(devices_[(size_t)device_index]);

@@ -208,11 +208,34 @@ def test_unsupported_is_loud():
     with pytest.raises(jb.JbError) as ei:
         e.synthesize(SAMPLE_SENTENCE_1)
     assert ei.value.kind == "Unsupported"
-    e.set("stage", 2)  # streaming with stage != 0 is not built either
-    with pytest.raises(jb.JbError) as ei:
-        g = e.generator([SAMPLE_SENTENCE_1])
-        g.generate_step(1)
-    assert ei.value.kind == "Unsupported"
+
+
+def test_generate_step_with_stage_nonzero():
+    # SpeechGenerator::generate_step drives any stage frame by frame (speech.rs:65-83, vocoder/mod.rs:142-176): the
+    # MGLSA delay lines are carried between chunks. No shipped voice holds line spectral pairs, so nitech's
+    # mel-cepstra are read as such and the filter is unstable (the oracle's output explodes within a few frames):
+    # the chunked and the whole-utterance run are compared on the frames where the signal is still finite, both in
+    # the reference's operation order.
+    e = jb.Engine.load([NITECH])
+    e.set("stage", 2)
+    e.set_mlsa_variant(0)
+    whole = e.synthesize(SAMPLE_SENTENCE_1)
+    g = e.generator([SAMPLE_SENTENCE_1])
+    fp = g.fperiod()
+    got = []
+    for n in (1, 1, 2, 3):
+        buf, written, _ = g.generate_step(n)
+        assert written[0] == n * fp
+        got.append(buf[0, : written[0]].copy())
+    g.close()
+    got = np.concatenate(got)
+    ref = whole[: len(got)]
+    ok = np.isfinite(ref) & (np.abs(ref) < 1e150)
+    assert ok[: 2 * fp].all() and np.abs(ref[ok]).max() > 1.0
+    assert np.abs(got[ok] - ref[ok]).max() <= 1e-9 * np.abs(ref[ok]).max()
+    # (against the oracle the whole-utterance path is covered by test_engine_stage_option_takes_the_lsp_arm and, on
+    # stable synthetic LSP tracks, by tests/test_gpu_vocoder_seam.py; an exploding filter amplifies the 1e-8 of the
+    # LSP transform's conditioning without bound, so it is no yardstick here)
 
 
 def test_pcm16_is_the_reference_clamp_of_the_f64_waveform(eng):

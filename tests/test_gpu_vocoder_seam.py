@@ -306,6 +306,17 @@ def test_no_lpf_stream(eng, stage):
         assert rel_diff(w, ref) <= WAVE_RTOL[M]
 
 
+@pytest.mark.parametrize("stage,fperiod", [(2, 100), (3, 75)])
+def test_mglsa_any_frame_period(eng, stage, fperiod):
+    # frame periods the segmented MGLSA kernel does not take (no multiple of 16): the sequential kernel, reference order
+    T, M = 60, 25
+    s, a, b = lsp_track(T, M, 3), lf0_track(T, 3), lpf_track(T)
+    w = eng.vocoder_synthesize(s, a, b, stage=stage, use_log_gain=True, alpha=0.42, fperiod=fperiod)
+    ref = O.vocoder_ex(s, a, b, stage=stage, use_log_gain=True, alpha=0.42, fperiod=fperiod)
+    assert len(w) == len(ref) == T * fperiod
+    assert rel_diff(w, ref) <= WAVE_RTOL[M]
+
+
 def test_seam_argument_errors(eng):
     T = 4
     with pytest.raises(jb.JbError) as ei:  # speech.rs:38-40
