@@ -1,20 +1,16 @@
 #!/bin/bash
-# One GPU-box visit: parity tests, bench (both arms), ncu launch list, ncu --set full of the MLSA kernel.
+# One GPU-box visit: parity tests, smoke, bench (both arms), ncu launch list, ncu --set full of the MLSA kernel.
 # Usage (from the repo root on the box): bash tools/gpu_round.sh [tag]
-TAG=${1:-r1}
+TAG=${1:-r2}
 O=gpurun_out
 mkdir -p $O
 nvidia-smi --query-gpu=name,clocks.max.sm,clocks.max.mem,power.limit --format=csv > $O/${TAG}_gpu.txt 2>&1
 timeout 900 python -m pytest tests -m gpu -x -q > $O/${TAG}_pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a $O/${TAG}_pytest_gpu.log
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > $O/${TAG}_smoke.log 2>&1; echo "smoke rc=$?" | tee -a $O/${TAG}_smoke.log
-timeout 600 python bench.py --steps 5 --warmup 3 > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo "bench rc=$?"
-timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $O/${TAG}_bench_ref.json 2> $O/${TAG}_bench_ref.err; echo "ref rc=$?"
+timeout 900 python bench.py --steps 20 --warmup 5 > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err; echo "bench rc=$?"
+timeout 900 python bench.py --impl reference --steps 5 --warmup 1 > $O/${TAG}_bench_ref.json 2> $O/${TAG}_bench_ref.err; echo "ref rc=$?"
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches.csv \
   python bench.py --steps 2 --warmup 3 --no-e2e --no-cpu-baseline > $O/${TAG}_ncu_launch.log 2>&1; echo "ncu launches rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_mlsa -c 1 -o $O/${TAG}_mlsa_full -f \
   python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline > $O/${TAG}_ncu_full.log 2>&1; echo "ncu full rc=$?"
-tail -3 $O/${TAG}_pytest_gpu.log; cat $O/${TAG}_smoke.log | tail -2; cat $O/${TAG}_bench.json | cut -c1-1500
-timeout 900 python tools/bench_configs.py > $O/${TAG}_configs.jsonl 2> $O/${TAG}_configs.err; echo "configs rc=$?"
-timeout 600 python tools/bench_mglsa.py > $O/${TAG}_mglsa.jsonl 2> $O/${TAG}_mglsa.err; echo "mglsa rc=$?"
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $O/${TAG}_mglsa_launches.csv \
-  python tools/bench_mglsa.py --utts 256 --stages 2 --reps 1 > $O/${TAG}_mglsa_ncu.log 2>&1; echo "ncu mglsa rc=$?"
+tail -3 $O/${TAG}_pytest_gpu.log; tail -2 $O/${TAG}_smoke.log; cut -c1-600 $O/${TAG}_bench.json
