@@ -219,6 +219,29 @@ typedef struct jb_mlpg_input {
 } jb_mlpg_input;
 int jb_engine_mlpg_create(const jb_engine* e, const jb_mlpg_input* in, int device_index, double** out, size_t* frame_off);
 
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The MLPG solve of jb_engine_mlpg_create (calc_wuw_and_wum + ldl_factorization + substitutions, same operation
+ * order, same results) for ONE utterance of a stream that is not MSD and has no GV, with NO allocation: the
+ * work planes live in a fixed 6 MiB `static __device__` array that every GPU loading this library holds until exit.
+ * The call makes no cudaMalloc / cudaFree / allocating library call and needs no engine.
+ *   device            CUDA device ordinal (not an index into an engine's device list); the caller's current
+ *                     device is restored before returning
+ *   d_mean, d_vari    DEVICE pointers, [n_frames][n_windows * dim], index dim * w + d: the state-level rows of
+ *                     jb_mlpg_input repeated by their durations
+ *   window_widths / window_coefficients   HOST pointers, as in jb_mlpg_input (n_windows <= 4, odd widths <= 5)
+ *   d_out             DEVICE pointer, [n_frames][dim]
+ *   stream            the caller's cudaStream_t (NULL: the default stream). The two kernels are only ENQUEUED on
+ *                     it; the call does not synchronise.
+ * Limit: n_frames * dim <= JB_MLPG_NOALLOC_MAX_CELLS, else JB_ERR_ARGUMENT (jb_last_error names the limit).
+ * The array is shared by all calls on a device and keeps the last call's contents (every cell a call reads it
+ * has written itself first, nothing needs clearing): calls whose kernels can overlap on one GPU - different
+ * streams, or several host threads - race on it and must be serialised by the caller. */
+#define JB_MLPG_NOALLOC_MAX_CELLS 131072
+int jb_mlpg_solve_noalloc(int device, const double* d_mean, const double* d_vari, size_t n_frames, size_t dim,
+                          size_t n_windows, const size_t* window_widths, const double* window_coefficients,
+                          double* d_out, void* stream);
+
 /* Process-wide knobs (no reference equivalent). jb_set_host_threads: host threads the front-end and the
  * batching layer use (0 = all cores; env JB_HOST_THREADS) - set it to cores / ranks when several processes
  * share a box. jb_trim_pools: frees the cached pinned host buffers (up to 24 GB are kept for reuse);

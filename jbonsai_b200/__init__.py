@@ -30,7 +30,7 @@ C_ABI_SYMBOLS = [
     "jb_resident_prepare", "jb_resident_prepare_tracks", "jb_resident_rows", "jb_engine_vocoder_synthesize", "jb_resident_run", "jb_resident_fetch", "jb_resident_free",
     "jb_stream_open", "jb_stream_fperiod", "jb_stream_synthesized_frames", "jb_stream_step",
     "jb_stream_close", "jb_resident_device_output", "jb_engine_synthesize_batch_device", "jb_set_host_threads",
-    "jb_trim_pools", "jb_device_pitch_period", "jb_engine_mlpg_create",
+    "jb_trim_pools", "jb_device_pitch_period", "jb_engine_mlpg_create", "jb_mlpg_solve_noalloc",
 ]
 
 STATUS_NAMES = {
@@ -111,6 +111,25 @@ def device_pitch_period(lf0: np.ndarray, rate: float = 48000.0, device: int = 0)
     _check(lib.jb_device_pitch_period(int(device), x.ctypes.data_as(D), C.c_size_t(x.size), C.c_double(rate),
                                       out.ctypes.data_as(D)))
     return out
+
+
+MLPG_NOALLOC_MAX_CELLS = 131072  # JB_MLPG_NOALLOC_MAX_CELLS (include/jbonsai_b200.h)
+
+
+def mlpg_solve_noalloc(device: int, d_mean: int, d_vari: int, n_frames: int, dim: int, windows, d_out: int,
+                       stream: int = 0) -> None:
+    """jb_mlpg_solve_noalloc: MLPG solve of one non-MSD, non-GV utterance with no allocation (the work planes are a
+    fixed __device__ array of the library). `d_mean`, `d_vari` ([n_frames][len(windows) * dim]) and `d_out`
+    ([n_frames][dim]) are DEVICE addresses as integers, `stream` a cudaStream_t as an integer (0: default stream);
+    the kernels are only enqueued. n_frames * dim <= MLPG_NOALLOC_MAX_CELLS. Calls that can overlap on one GPU
+    race on the shared scratch."""
+    widths = (C.c_size_t * len(windows))(*[len(w) for w in windows])
+    coef = np.ascontiguousarray(np.concatenate([np.asarray(w, dtype=np.float64) for w in windows]))
+    lib.jb_mlpg_solve_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t,
+                                          C.POINTER(C.c_size_t), C.POINTER(C.c_double), C.c_void_p, C.c_void_p]
+    _check(lib.jb_mlpg_solve_noalloc(int(device), C.c_void_p(int(d_mean)), C.c_void_p(int(d_vari)), int(n_frames),
+                                     int(dim), len(windows), widths, coef.ctypes.data_as(C.POINTER(C.c_double)),
+                                     C.c_void_p(int(d_out)), C.c_void_p(int(stream))))
 
 
 def set_host_threads(n: int) -> None:

@@ -513,6 +513,45 @@ int jb_engine_mlpg_create(const jb_engine* e, const jb_mlpg_input* in, int devic
   JB_CATCH
 }
 
+// No exceptions and no containers on this path: nothing here may allocate on the device, and the host side keeps
+// to static strings as well.
+int jb_mlpg_solve_noalloc(int device, const double* d_mean, const double* d_vari, size_t n_frames, size_t dim,
+                          size_t n_windows, const size_t* window_widths, const double* window_coefficients,
+                          double* d_out, void* stream) {
+  static_assert(JB_MLPG_NOALLOC_MAX_CELLS == jbk::kMlpgNoAllocMaxCells, "header and kernel limit differ");
+  auto bad = [](const char* msg) {
+    g_err = msg;
+    return (int)JB_ERR_ARGUMENT;
+  };
+  if (dim == 0 || n_windows == 0 || !window_widths || !window_coefficients) return bad("mlpg_solve_noalloc: dim, n_windows and the windows must be given");
+  if (n_windows > (size_t)jbk::kMaxWin) return bad("mlpg_solve_noalloc: more than 4 windows");
+  jbk::WindowSet ws{};
+  ws.nwin = (int)n_windows;
+  size_t o = 0;
+  for (size_t w = 0; w < n_windows; ++w) {
+    const size_t width = window_widths[w];
+    if (width == 0 || width % 2 == 0 || width > (size_t)jbk::kMaxWinWidth) return bad("mlpg_solve_noalloc: window widths must be odd and <= 5");
+    ws.width[w] = (int)width;
+    for (size_t k = 0; k < width; ++k) ws.coef[w][k] = window_coefficients[o + k];
+    o += width;
+  }
+  if (n_frames == 0) return JB_OK;
+  if (dim > (size_t)JB_MLPG_NOALLOC_MAX_CELLS || n_frames > (size_t)JB_MLPG_NOALLOC_MAX_CELLS / dim)
+    return bad("mlpg_solve_noalloc: n_frames * dim exceeds JB_MLPG_NOALLOC_MAX_CELLS (131072), the size of the static device scratch");
+  if (!d_mean || !d_vari || !d_out) return bad("mlpg_solve_noalloc: null device pointer");
+  const char* what = "";
+  const int ce = jbk::mlpg_solve_noalloc(device, d_mean, d_vari, (long long)n_frames, (int)dim, ws, d_out,
+                                         (cudaStream_t)stream, &what);
+  if (ce != 0) {
+    g_err = "mlpg_solve_noalloc: CUDA error in ";
+    g_err += what;
+    g_err += ": ";
+    g_err += cudaGetErrorString((cudaError_t)ce);
+    return (int)JB_ERR_CUDA;
+  }
+  return JB_OK;
+}
+
 int jb_set_host_threads(int n) {
   jb::Engine::set_host_threads(n);
   return JB_OK;

@@ -252,6 +252,12 @@ int launch_gather_chunk(const BatchLayout& b, const VocoderParams& p, const Voco
 // truncate toward zero; examples/genji/main.rs:34-35). n must be a multiple of 4.
 int launch_pcm16(const double* in, int16_t* out, int64_t n, cudaStream_t stream);
 
+// mlpg_noalloc.cu: MLPG solve of one non-MSD stream with its work planes in a fixed __device__ array (no
+// allocation of any kind). frames x dim of one call is bounded by kMlpgNoAllocMaxCells (JB_MLPG_NOALLOC_MAX_CELLS).
+constexpr long long kMlpgNoAllocMaxCells = 131072;
+int mlpg_solve_noalloc(int device, const double* d_mean, const double* d_vari, long long n_frames, int dim,
+                       const WindowSet& ws, double* d_out, cudaStream_t stream, const char** what);
+
 // Roofline denominators measured on the current device (peaks.cu); not on the synthesis path.
 int measure_peaks(double* fp64_fma_tflops, double* hbm_copy_gbs);
 
