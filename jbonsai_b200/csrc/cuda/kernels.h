@@ -147,6 +147,10 @@ struct VocoderDev {
 // what: bit 0 = pitch period from lf0, bit 1 = b = mc2b(mcp)
 int launch_frame_prep(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d,
                       int64_t total_frames, int what, cudaStream_t stream);
+// what = 2 and launch_row_increments (no b_first) in one pass; stage 0, rows of up to 47 coefficients.
+bool coef_rows_supported(const VocoderParams& p);
+int launch_coef_rows(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, int64_t total_frames,
+                     cudaStream_t stream);
 // beta > 0 (MelCepstrum::postfilter_mcp, cepstrum.rs:23-37): first copies row 0 of every utterance
 // of d.b (= mc2b of the raw first frame) to b_first[n_utt][nmcp], then rewrites every row of d.b as
 // mc2b(postfilter_mcp(c)). Runs after launch_frame_prep(what & 2). No-op when beta <= 0 or nmcp <= 2.

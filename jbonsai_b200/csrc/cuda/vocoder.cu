@@ -63,6 +63,54 @@ __global__ void k_frame_prep(VocoderParams p, VocoderDev d, int64_t total_frames
   }
 }
 
+// ---------------------------------------------------------------- frame prep + increments, fused
+// b = mc2b(mcp) (cepstrum.rs:139-149) and binc[f] = (b[f] - b[f-1]) / fperiod (vocoder/mod.rs:118-127) in one
+// pass over the spectrum: k_frame_prep (a thread walks its own 280-byte row: 1 TB/s) + k_row_increments (reads b
+// back, one binary search per element) cost 0.57 + 0.29 ms on the bench batch. Here a block stages the rows of
+// kCoefFrames frames and of the frame before them in shared memory with coalesced loads, a thread runs the mc2b
+// recurrence on a row (odd row stride: no bank conflicts), and rows and increments leave coalesced. Same
+// operations per element as the two kernels, so the same bits. Stage 0 without post-filter only (no b_first: the
+// first frame of an utterance starts from its own row, i.e. a zero increment).
+constexpr int kCoefFrames = 128;
+__global__ void __launch_bounds__(kCoefFrames) k_coef_rows(BatchLayout b, VocoderParams p, VocoderDev d,
+                                                           int64_t total_frames) {
+  extern __shared__ double tile[];  // [kCoefFrames + 1][M | 1]: row 0 = the frame before the block's first
+  __shared__ unsigned char first[kCoefFrames];
+  const int M = p.nmcp, RS = M | 1;
+  const int64_t f0 = (int64_t)blockIdx.x * kCoefFrames;
+  const int nf = (int)min((int64_t)kCoefFrames, total_frames - f0);
+  const int tid = threadIdx.x;
+  const int64_t base = (f0 > 0 ? f0 - 1 : 0) * M;  // first element staged
+  const int r0 = f0 > 0 ? 0 : 1;                   // its row in the tile
+  const int n_in = (nf + 1 - r0) * M;
+  for (int e = tid; e < n_in; e += kCoefFrames) {
+    const int row = e / M;
+    tile[(row + r0) * RS + (e - row * M)] = d.mcp[base + e];
+  }
+  if (tid < nf) {
+    const int64_t gf = f0 + tid;
+    first[tid] = gf == b.frame_off[find_utt(b.frame_off, b.n_utt, gf)];
+  }
+  __syncthreads();
+  for (int row = r0 + tid; row <= nf; row += kCoefFrames) {  // nf + 1 rows over 128 threads: thread 0 takes two
+    double* c = tile + row * RS;
+    double nxt = c[M - 1];
+    for (int i = M - 2; i >= 0; --i) {
+      nxt = (p.alpha != 0.0) ? c[i] - p.alpha * nxt : c[i];
+      c[i] = nxt;
+    }
+  }
+  __syncthreads();
+  const double fp = (double)p.fperiod;
+  for (int e = tid; e < nf * M; e += kCoefFrames) {
+    const int fr = e / M, k = e - fr * M;
+    const double cur = tile[(fr + 1) * RS + k];
+    const double prev = first[fr] ? cur : tile[fr * RS + k];
+    d.b[f0 * M + e] = cur;
+    d.binc[f0 * M + e] = (cur - prev) / fp;
+  }
+}
+
 // ---------------------------------------------------------------- pulse train
 // One thread per utterance walks the pitch counter sample by sample (the additions must round
 // exactly like excitation.rs:72-86, so the walk is sequential) but only WRITES the pulses: the
@@ -787,6 +835,20 @@ int launch_frame_prep(const BatchLayout& b, const VocoderParams& p, const Vocode
   const int threads = 128;
   const int blocks = (int)((total_frames + threads - 1) / threads);
   k_frame_prep<<<blocks, threads, 0, stream>>>(p, d, total_frames, what);
+  return (int)cudaGetLastError();
+}
+
+bool coef_rows_supported(const VocoderParams& p) {
+  return p.stage == 0 && p.nmcp >= 2 && (size_t)(kCoefFrames + 1) * (p.nmcp | 1) * 8 <= 48 * 1024;
+}
+// d.b and d.binc from d.mcp in one kernel: launch_frame_prep(what = 2) + launch_row_increments without b_first.
+int launch_coef_rows(const BatchLayout& b, const VocoderParams& p, const VocoderDev& d, int64_t total_frames,
+                     cudaStream_t stream) {
+  if (total_frames == 0) return 0;
+  if (d.binc == nullptr || d.b_first != nullptr || !coef_rows_supported(p)) return (int)cudaErrorInvalidValue;
+  const size_t smem = (size_t)(kCoefFrames + 1) * (p.nmcp | 1) * 8;
+  k_coef_rows<<<(unsigned)((total_frames + kCoefFrames - 1) / kCoefFrames), kCoefFrames, smem, stream>>>(b, p, d,
+                                                                                                         total_frames);
   return (int)cudaGetLastError();
 }
 

@@ -929,6 +929,10 @@ static void launch_spectrum_prep(Engine::Resident* r, cudaStream_t st) {
     JB_LAUNCH(jbk::launch_row_increments(r->layout, r->vp, r->vd, r->total_frames, st));
     return;
   }
+  if (r->beta <= 0.0 && r->vd.binc && r->vd.b_first == nullptr && jbk::coef_rows_supported(r->vp)) {
+    JB_LAUNCH(jbk::launch_coef_rows(r->layout, r->vp, r->vd, r->total_frames, st));  // rows and increments fused
+    return;
+  }
   JB_LAUNCH(jbk::launch_frame_prep(r->layout, r->vp, r->vd, r->total_frames, 2, st));
   if (r->beta > 0.0)  // MelCepstrum::postfilter_mcp (cepstrum.rs:23-37): rewrites vd.b in place
     JB_LAUNCH(jbk::launch_postfilter(r->layout, r->vp, r->vd, r->beta, const_cast<double*>(r->vd.b_first),
