@@ -10,6 +10,8 @@
 // reference's FMA flavour of `fir` has them (mlsa.rs:82-115,147-153).
 #include <algorithm>
 
+#include <cstdlib>
+
 #include "kernels.h"
 #include "cr_exp.h"
 
@@ -250,6 +252,143 @@ __global__ void __launch_bounds__(128) k_pulse_runs(BatchLayout b, VocoderParams
     pitch = pitch_next;
     inc = (pitch - p_cur) / fper;  // Excitation::start with both pitches non-zero
   }
+}
+
+// ---------------------------------------------------------------- pulse walks, one warp per run
+// k_pulse_runs gives a run to one lane, and that lane pays, per sample, a dependent addition for the pitch chain and
+// one for the counter: ~3500 cycles per frame, so the longest voiced run of the batch (hundreds of frames) sets the
+// kernel's time (2.7 ms on the bench batch with 6 % of the warps active). Two things are not serial, though:
+//  * the pitch chain restarts at every frame (Excitation::end snaps p to the frame's pitch), so the 32 lanes run
+//    the chains of 32 frames side by side and keep every eighth value in shared memory;
+//  * between two pulses the counter moves by exact steps: "+= 1.0" is exact while the sum stays in the binade of the
+//    counter and rounds only on the step that crosses into the next one (cnt_advance replays exactly those steps),
+//    so the counter at the start of any 8-sample block is known WITHOUT walking, as long as no pulse lies before it.
+// So a warp tests 32 blocks (256 samples) at once, each lane replaying its own block sample by sample with the
+// reference's operations (excitation.rs:72-86); the first lane that sees a pulse is right (nothing precedes it), it
+// writes its pulses and hands its counter to the lanes behind it, which start over from there. About two rounds
+// per 256 samples instead of 256 dependent steps; same bits.
+__device__ __forceinline__ double cnt_advance(double cnt, int m) {  // cnt after m times "cnt += 1.0"
+  while (m > 0) {
+    if (!(cnt >= 1.0)) {  // below 1 the sum may need more bits than it has: a plain step, rounded like the reference
+      cnt += 1.0;
+      --m;
+      continue;
+    }
+    const double limit = __hiloint2double((__double2hiint(cnt) & 0x7ff00000) + 0x00100000, 0);  // next power of two
+    const double room = limit - cnt;       // exact
+    const int kmax = (int)ceil(room) - 1;  // steps that stay below the limit: all exact
+    if (kmax >= m) {
+      cnt += (double)m;
+      m = 0;
+    } else {
+      cnt += (double)kmax;
+      cnt += 1.0;  // the crossing step rounds to the coarser grid, as in the reference
+      m -= kmax + 1;
+    }
+  }
+  return cnt;
+}
+
+constexpr int kPwWarps = 4;
+constexpr int kPwMaxBlocks = 32;  // 8-sample blocks per frame: fperiod <= 256
+struct PulseWarpShared {
+  double pk8[32][kPwMaxBlocks + 1];  // [frame of the batch][block]: the pitch chain at the block's first sample
+  double inc[32];
+};
+
+// Persistent grid: a warp fetches the next run from the counter `next` (zeroed by the launcher) until the list is done.
+__global__ void __launch_bounds__(32 * kPwWarps) k_pulse_warp(BatchLayout b, VocoderParams p, VocoderDev d, int* next) {
+  __shared__ PulseWarpShared sh[kPwWarps];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  PulseWarpShared& S = sh[wib];
+  const unsigned full = 0xffffffffu;
+  const int n_runs = d.runs[0];
+ for (;;) {
+  int run = 0;
+  if (lane == 0) run = atomicAdd(next, 1);
+  run = __shfl_sync(full, run, 0);
+  if (run >= n_runs) return;
+  __syncwarp();  // the tables of the run before are free
+  const int64_t gf0 = d.runs[1 + run];
+  const int u = find_utt(b.frame_off, b.n_utt, gf0);
+  const int64_t foff = b.frame_off[u];
+  const int T = (int)(b.frame_off[u + 1] - foff);
+  const int f0 = (int)(gf0 - foff);
+  const int fp = p.fperiod, NB = fp >> 3;
+  const double fper = (double)fp;
+  const double* const pitch = d.pitch + foff;
+  double cnt = pitch[f0];  // Excitation::start from an unvoiced frame: the counter starts at the period
+  for (int fb = f0;; fb += 32) {
+    // ---- frames fb .. fb + nvalid - 1 of this batch belong to the run
+    const int f = fb + lane;
+    const double pf = f < T ? pitch[f] : 0.0;
+    const unsigned unv = __ballot_sync(full, pf == 0.0);
+    const int nvalid = unv ? __ffs(unv) - 1 : 32;
+    if (nvalid == 0) break;
+    if (lane < nvalid) {
+      const bool first = f == f0;
+      double pc = first ? pf : pitch[f - 1];  // Excitation::end left p at the pitch of the frame before
+      const double inc = first ? 0.0 : (pf - pc) / fper;
+      S.inc[lane] = inc;
+      for (int i = 0; i < NB; ++i) {
+        S.pk8[lane][i] = pc;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) pc += inc;
+      }
+    }
+    __syncwarp();
+    // ---- 32 blocks per step
+    const int nblk = nvalid * NB;
+    for (int g = 0; g < nblk; g += 32) {
+      const int blk = g + lane;
+      const bool act = blk < nblk;
+      const int fl = act ? blk / NB : 0, bi = act ? blk - fl * NB : 0;
+      const double pk0 = S.pk8[fl][bi], inc = S.inc[fl];
+      const int nact = min(32, nblk - g);
+      int base = 0;
+      while (base < nact) {
+        const bool mine = act && lane >= base;
+        double c = cnt, pk[8];
+        unsigned mask = 0;
+        if (mine) {
+          c = cnt_advance(cnt, 8 * (lane - base));
+          const double lb = inc < 0.0 ? pk0 + 8.0 * inc : pk0;  // no sample of the block has a period below this
+          if (c + 8.0 < lb - 1e-3) {
+            c = cnt_advance(c, 8);
+          } else {
+            pk[0] = pk0;
+#pragma unroll
+            for (int k = 1; k < 8; ++k) pk[k] = pk[k - 1] + inc;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {  // voiced_frame (excitation.rs:72-86)
+              c += 1.0;
+              if (c >= pk[k]) {
+                c -= pk[k];
+                mask |= 1u << k;
+              }
+            }
+          }
+        }
+        const unsigned hit = __ballot_sync(full, mask != 0);
+        if (hit == 0) {
+          cnt = __shfl_sync(full, c, nact - 1);
+          break;
+        }
+        const int L = __ffs(hit) - 1;
+        if (lane == L) {
+          double* out = d.pulse + ((foff + fb + fl) * fp + bi * 8);
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            if (mask >> k & 1u) out[k] = sqrt(pk[k]);
+        }
+        cnt = __shfl_sync(full, c, L);
+        base = L + 1;
+      }
+    }
+    if (nvalid < 32) break;
+    __syncwarp();  // the tables are rewritten for the next batch of frames
+  }
+ }
 }
 
 // ---------------------------------------------------------------- excitation + gain
@@ -868,9 +1007,23 @@ int launch_pulse(const BatchLayout& b, const VocoderParams& p, const VocoderDev&
     if (d.runs == nullptr) return (int)cudaErrorInvalidValue;
     cudaError_t e = cudaMemsetAsync(d.runs, 0, sizeof(int32_t), stream);
     if (e != cudaSuccess) return (int)e;
-    k_pulse_list<<<(unsigned)((total_frames + 255) / 256), 256, 0, stream>>>(b, d, total_frames);
     // at most every other frame starts a run
-    const int64_t max_threads = (total_frames / 2 + b.n_utt + 1) * (32 / kRunLanes);
+    const int64_t max_runs = total_frames / 2 + b.n_utt + 1;
+    static const bool lane_walks = getenv("JB_X_PULSE_LANES") != nullptr;  // experiments only: the round-1 kernel
+    if (p.fperiod % 8 == 0 && p.fperiod <= 8 * kPwMaxBlocks && !lane_walks) {
+      int* next = d.runs + total_frames + 1;  // the spare slot behind the list (the arena holds total_frames + 2 ints)
+      e = cudaMemsetAsync(next, 0, sizeof(int32_t), stream);
+      if (e != cudaSuccess) return (int)e;
+      k_pulse_list<<<(unsigned)((total_frames + 255) / 256), 256, 0, stream>>>(b, d, total_frames);
+      int dev = 0, sms = 148;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      const int64_t blocks = std::min<int64_t>((max_runs + kPwWarps - 1) / kPwWarps, (int64_t)sms * 6);
+      k_pulse_warp<<<(unsigned)blocks, 32 * kPwWarps, 0, stream>>>(b, p, d, next);
+      return (int)cudaGetLastError();
+    }
+    k_pulse_list<<<(unsigned)((total_frames + 255) / 256), 256, 0, stream>>>(b, d, total_frames);
+    const int64_t max_threads = max_runs * (32 / kRunLanes);
     k_pulse_runs<<<(unsigned)((max_threads + 127) / 128), 128, 0, stream>>>(b, p, d, total_frames);
     return (int)cudaGetLastError();
   }

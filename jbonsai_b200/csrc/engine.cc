@@ -793,7 +793,7 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   const size_t w_b = wk.take((size_t)TF * dim[0] * 8);
   const size_t w_pitch = wk.take((size_t)TF * 8);
   const size_t w_pulse = wk.take((size_t)r->total_samples * 8);
-  const size_t w_runs = wk.take(((size_t)TF + 1) * 4);
+  const size_t w_runs = wk.take(((size_t)TF + 2) * 4);
   const size_t w_wave = wk.take((size_t)r->total_samples * 8);
   const size_t w_state = streaming ? wk.take(n_utt * jbk::kVocStateDoubles * 8) : 0;
   const size_t w_mgstate = (streaming && cond.stage != 0) ? wk.take(n_utt * (size_t)jbk::kMglsaMaxStage * jbk::kMglsaMaxOrder * 8) : 0;
@@ -1315,7 +1315,7 @@ Engine::Resident* Engine::prepare_tracks(const VocoderConfig& cfg, size_t n_utt,
 
   Carver wk;
   const size_t w_b = wk.take((size_t)TF * M * 8), w_pitch = wk.take((size_t)TF * 8);
-  const size_t w_pulse = wk.take((size_t)r->total_samples * 8), w_runs = wk.take(((size_t)TF + 1) * 4);
+  const size_t w_pulse = wk.take((size_t)r->total_samples * 8), w_runs = wk.take(((size_t)TF + 2) * 4);
   const size_t w_wave = wk.take((size_t)r->total_samples * 8), w_out = wk.take((size_t)r->total_samples * 8);
   const size_t seg_state_doubles =
       cfg.stage != 0 ? (size_t)jbk::mglsa_state_doubles((int)cfg.stage) : (size_t)jbk::kMlsaSegStateDoubles;
