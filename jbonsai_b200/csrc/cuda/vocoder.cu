@@ -268,6 +268,13 @@ __global__ void __launch_bounds__(128) k_pulse_runs(BatchLayout b, VocoderParams
 // writes its pulses and hands its counter to the lanes behind it, which start over from there. About two rounds
 // per 256 samples instead of 256 dependent steps; same bits.
 __device__ __forceinline__ double cnt_advance(double cnt, int m) {  // cnt after m times "cnt += 1.0"
+  {
+    // If cnt + m is exact, every partial sum cnt + j is too (it lies in the same or a lower binade, on a finer
+    // grid), so the m single steps round nowhere. After a pulse the counter is a difference of two values near the
+    // period, a multiple of the period's ulp: for periods above 256 samples that covers nearly every call.
+    const double dm = (double)m, r = cnt + dm, bb = r - cnt;
+    if ((cnt - (r - bb)) + (dm - bb) == 0.0) return r;  // TwoSum: the rounding error of cnt + m
+  }
   while (m > 0) {
     if (!(cnt >= 1.0)) {  // below 1 the sum may need more bits than it has: a plain step, rounded like the reference
       cnt += 1.0;
@@ -346,32 +353,31 @@ __global__ void __launch_bounds__(32 * kPwWarps) k_pulse_warp(BatchLayout b, Voc
       const double pk0 = S.pk8[fl][bi], inc = S.inc[fl];
       const int nact = min(32, nblk - g);
       int base = 0;
+      const double lb = (inc < 0.0 ? pk0 + 8.0 * inc : pk0) - 1e-3;  // no sample of the block has a period below this
       while (base < nact) {
-        const bool mine = act && lane >= base;
+        // Cheap test first: the counter at the end of this block is cnt + 8 (lane - base + 1) up to a few ulps of
+        // rounding; a block that stays a safe distance below its smallest period holds no pulse, and its lane
+        // needs no exact counter. Only the other lanes (one or two per round) replay their block.
+        const bool mine = act && lane >= base && !(cnt + (double)(8 * (lane - base + 1)) < lb);
         double c = cnt, pk[8];
         unsigned mask = 0;
         if (mine) {
           c = cnt_advance(cnt, 8 * (lane - base));
-          const double lb = inc < 0.0 ? pk0 + 8.0 * inc : pk0;  // no sample of the block has a period below this
-          if (c + 8.0 < lb - 1e-3) {
-            c = cnt_advance(c, 8);
-          } else {
-            pk[0] = pk0;
+          pk[0] = pk0;
 #pragma unroll
-            for (int k = 1; k < 8; ++k) pk[k] = pk[k - 1] + inc;
+          for (int k = 1; k < 8; ++k) pk[k] = pk[k - 1] + inc;
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {  // voiced_frame (excitation.rs:72-86)
-              c += 1.0;
-              if (c >= pk[k]) {
-                c -= pk[k];
-                mask |= 1u << k;
-              }
+          for (int k = 0; k < 8; ++k) {  // voiced_frame (excitation.rs:72-86)
+            c += 1.0;
+            if (c >= pk[k]) {
+              c -= pk[k];
+              mask |= 1u << k;
             }
           }
         }
         const unsigned hit = __ballot_sync(full, mask != 0);
         if (hit == 0) {
-          cnt = __shfl_sync(full, c, nact - 1);
+          cnt = cnt_advance(cnt, 8 * (nact - base));  // no pulse in the rest of the step
           break;
         }
         const int L = __ffs(hit) - 1;

@@ -2,6 +2,7 @@
 import sys
 import numpy as np
 sys.path.insert(0, "tests")
+sys.path.insert(0, ".")
 import jbonsai_b200 as jb
 from jbonsai_b200 import workload as wl
 from conftest import NITECH
