@@ -85,8 +85,11 @@ class Engine {
   std::vector<double> output_fractions = default_output_fractions();
   // Sub-batches of one synthesize_batch call on one device (large batches only): the stream-parameter
   // look-ups of chunk k + 1 run on the host while the GPU works on chunk k, and chunk k's waveform
-  // crosses PCIe under chunk k + 1's kernels. 1 = the whole batch in one pass.
-  int pipeline_chunks = 2;
+  // crosses PCIe under chunk k + 1's kernels. 1 = the whole batch in one pass; 2 = the first output share as a
+  // sub-batch of its own, the other shares as waves of the second; 3 and 4 = equal sub-batches of one wave each.
+  // Measured e2e, 1024 x 5 s on one B200 (tools/e2e_probe.py, p50 of 8 calls): 1 -> 66 ms, 2 -> 60.2, 3 -> 57.8,
+  // 4 -> 62.9 (every sub-batch pays the warm-up of a chip-filling set of segments over fewer frames).
+  int pipeline_chunks = 3;
 
   // Engine::synthesize for a batch: utterance u = lines[line_off[u] .. line_off[u+1]).
   // `out` is a pinned host buffer owned by the engine's pool: release with free_output().

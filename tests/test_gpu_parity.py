@@ -260,9 +260,14 @@ def test_output_waves_equal_single_copy():
     # to the host under the next one): same samples as one launch + one copy, to rounding of the cuts
     e = jb.Engine.load([TOHOKU_NEUTRAL])
     utts = wl.timed_batch(e, 720, wl.SEED_TOHOKU)
+    tm3 = {}
+    w3, off3 = e.synthesize_batch(utts, tm3)  # default: three equal sub-batches of one wave each
+    assert tm3["mlsa_fallback"] == 0 and tm3["launches"] >= 30
+    e.set_pipeline_chunks(2)  # the first output share as a sub-batch of its own, the others as waves of the second
     tm = {}
     w, off = e.synthesize_batch(utts, tm)
     assert tm["mlsa_fallback"] == 0 and tm["launches"] >= 20
+    assert list(off) == list(off3) and np.abs(w - w3).max() <= SCHED_ATOL
     e.set_output_mode(0)
     tm0 = {}
     w0, off0 = e.synthesize_batch(utts, tm0)
@@ -279,7 +284,7 @@ def test_output_waves_equal_single_copy():
     w1, off1 = e.synthesize_batch(utts, tm1)
     assert tm1["launches"] < tm0["launches"]
     assert list(off1) == list(off0) and np.abs(w1 - w0).max() <= SCHED_ATOL
-    e.set_pipeline_chunks(2)
+    e.set_pipeline_chunks(3)
     e.set_output_mode(1)
     q, _ = e.synthesize_batch_pcm16(utts)
     assert np.array_equal(q, np.trunc(np.clip(w0, -32768.0, 32767.0)).astype(np.int16))
