@@ -69,6 +69,8 @@ def parse_args():
     ap.add_argument("--mlsa-variant", type=int, default=-1)
     ap.add_argument("--mlsa-warm", type=int, default=-1, help="A/B: warm-up frames of the time-segmented filter")
     ap.add_argument("--mlsa-cut-tolerance", type=float, default=5e-7)
+    ap.add_argument("--mlsa-loud-warm", type=int, default=-1, help="A/B: warm-up of cuts behind loud frames (0 = rule off)")
+    ap.add_argument("--mlsa-loud-threshold", type=float, default=2.0)
     ap.add_argument("--beta", type=float, default=0.0, help="post-filter coefficient (default off, as the reference)")
     ap.add_argument("--output-mode", type=int, default=-1,
                     help="A/B: 0 one D2H copy, 1 two filter waves, 2 zero-copy stores (library default)")
@@ -294,6 +296,8 @@ def run_b200(args, rank, world, local):
         eng.set("beta", args.beta)
     if args.mlsa_warm >= 0:
         eng.set_mlsa_segmenting(args.mlsa_warm, args.mlsa_cut_tolerance)
+    if args.mlsa_loud_warm >= 0:
+        eng.set_mlsa_loud_warm(args.mlsa_loud_warm, args.mlsa_loud_threshold)
     eng.set_device_gather(bool(args.device_gather))
 
     fp64_peak, hbm_live = jb.measure_peaks(devs[0])

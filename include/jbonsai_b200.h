@@ -85,6 +85,13 @@ int jb_engine_set_device_gather(jb_engine* e, int enabled);
  * exceeds `cut_tolerance` (default 5e-7, half the 1e-6 bar) is repaired: the head of the segment behind it is
  * filtered again from the exact state; if that does not settle it the sequential kernel redoes the batch. */
 int jb_engine_set_mlsa_segmenting(jb_engine* e, int warm_frames, double cut_tolerance);
+/* Warm-up by loudness (variant 3, stage 0): a cut whose last `loud_frames` frames have a mean log gain (coefficient 0
+ * of the filter rows) above `threshold` filters only `loud_frames` frames ahead (default 24, threshold 2.0); the
+ * others keep `warm_frames` (the filter forgets its start twice as fast behind speech as in a pause). The gain is
+ * estimated on the host from the state-level spectrum means; the cuts of an utterance are placed so that all its
+ * segments still filter equally many frames. loud_frames = 0 turns the rule off. Cuts are checked and repaired as
+ * above whatever the rule says. */
+int jb_engine_set_mlsa_loud_warm(jb_engine* e, int loud_frames, double threshold);
 /* How jb_engine_synthesize_batch brings the waveform (8 B per sample, the Vec<f64> of
  * engine.rs:294) to the host. 1 (default): the batch is filtered in three launches, each part copied
  * under the next launch (10 + w selects w equal launches instead); 2: the filter kernel stores straight into

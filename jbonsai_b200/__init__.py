@@ -31,6 +31,7 @@ C_ABI_SYMBOLS = [
     "jb_stream_open", "jb_stream_fperiod", "jb_stream_synthesized_frames", "jb_stream_step",
     "jb_stream_close", "jb_resident_device_output", "jb_engine_synthesize_batch_device", "jb_set_host_threads",
     "jb_trim_pools", "jb_device_pitch_period", "jb_engine_mlpg_create", "jb_mlpg_solve_noalloc",
+    "jb_engine_set_mlsa_loud_warm",
 ]
 
 STATUS_NAMES = {
@@ -237,6 +238,10 @@ class Engine:
 
     def set_mlsa_segmenting(self, warm_frames: int = 40, cut_tolerance: float = 1e-7) -> None:
         _check(lib.jb_engine_set_mlsa_segmenting(self._h, int(warm_frames), C.c_double(cut_tolerance)))
+
+    def set_mlsa_loud_warm(self, loud_frames: int = 24, threshold: float = 2.0) -> None:
+        """Warm-up of cuts that lie behind loud frames (0 = every cut gets warm_frames)."""
+        _check(lib.jb_engine_set_mlsa_loud_warm(self._h, int(loud_frames), C.c_double(threshold)))
 
     def set_output_mode(self, mode: int) -> None:
         """1 (default): three filter waves, each copied under the next (10 + w: w equal waves); 2: zero-copy stores; 0: one copy."""

@@ -225,6 +225,14 @@ int jb_engine_set_mlsa_segmenting(jb_engine* e, int warm_frames, double cut_tole
   JB_CATCH
 }
 
+int jb_engine_set_mlsa_loud_warm(jb_engine* e, int loud_frames, double threshold) {
+  JB_TRY
+  if (loud_frames < 0) throw jb::Error(jb::kErrArgument, "loud_frames must be non-negative");
+  e->e->mlsa_warm_loud = loud_frames;
+  e->e->mlsa_loud_threshold = threshold;
+  JB_CATCH
+}
+
 int jb_engine_synthesize_batch(const jb_engine* e, const char* const* lines, const size_t* line_off,
                                size_t n_utt, double** out, size_t* out_off, double* timings) {
   JB_TRY

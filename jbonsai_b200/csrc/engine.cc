@@ -6,6 +6,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <functional>
 #include <thread>
 
 #include <cuda_runtime.h>
@@ -195,6 +196,7 @@ class DeviceCtx {
   int sm_count = 148;
   double* h_worst_base = nullptr;
   double* h_worst = nullptr;  // pinned: MLSA variant 3 cut-check result (of the current slot)
+  int loud_strikes = 0;       // batches whose loudness-sized warm-up left many cuts to repair (2: rule off for this device)
   int* h_fail_base = nullptr;
   int* h_fail = nullptr;      // pinned: number of cuts that failed the check (of the current slot)
   // leaf pdf tables of the engine's voices, resident for the life of the context (device gather)
@@ -456,6 +458,7 @@ struct Engine::Resident {
   int repaired_segments = 0;       // the last pass re-filtered this many segments with a longer warm-up
   std::vector<jbk::MlsaSegment> seg_table;  // host copy of segs.seg (for the repair pass)
   int warm_frames = 0;             // warm-up the segments were cut with
+  int warm_loud = 0;               // > 0: cuts behind loud frames were given this warm-up instead (mlsa_warm_loud)
   bool copied_by_waves = false;    // the last pass already queued its device-to-host copies
   cudaEvent_t kernels_end = nullptr;  // recorded after the last kernel of the last pass (variant 3)
   double* h_worst = nullptr;          // pinned word the last pass copies its cut-check result to
@@ -502,8 +505,12 @@ struct SegmentPlan {
 
 // Cuts every utterance into segments with W warm-up frames; `target` = how many segments fill the chip
 // once (warps per scheduler x segments per warp x schedulers).
+// `warm_at(u, begin)` (optional): warm-up of a cut at frame `begin` of utterance u when it is not W for all
+// (Engine::mlsa_warm_loud); the cuts of an utterance are then placed so that all its segments still filter the same
+// number of frames.
+using WarmAt = std::function<int64_t(size_t, int64_t)>;
 static SegmentPlan cut_segments(const std::vector<int64_t>& frame_off, size_t n_utt, int64_t W, int64_t target,
-                                const std::vector<double>& wave_weights) {
+                                const std::vector<double>& wave_weights, const WarmAt& warm_at = WarmAt()) {
   SegmentPlan pl;
   std::vector<jbk::MlsaSegment>& segs = pl.segs;
   pl.wave_seg_first.assign(1, 0);
@@ -548,6 +555,40 @@ static SegmentPlan cut_segments(const std::vector<int64_t>& frame_off, size_t n_
           int64_t G = std::max<int64_t>(1, (T + S / 2) / S);
           // equal filtered length L for every segment: the first owns L frames, the others L - W
           while (G > 1 && (T + (G - 1) * W) / G - W < kSegMinFrames / 2) --G;
+          if (warm_at && G > 1) {
+            // the share of a cut depends on where it falls and where it falls on the shares before it: iterate
+            std::vector<int64_t> beg((size_t)G + 1, 0), wk((size_t)G, 0);
+            int64_t sum_w = (G - 1) * W;
+            bool ok = false;
+            for (int it = 0; it < 6 && !ok; ++it) {
+              const int64_t L = (T + sum_w + G - 1) / G;
+              int64_t pos = std::min(L, T), sw = 0;
+              for (int64_t k = 1; k < G; ++k) {
+                const int64_t w = std::min(warm_at(u, pos), pos);
+                beg[(size_t)k] = pos;
+                wk[(size_t)k] = w;
+                sw += w;
+                pos = std::min(T, pos + std::max<int64_t>(L - w, kSegMinFrames / 2));
+              }
+              beg[(size_t)G] = T;
+              ok = sw == sum_w;
+              sum_w = sw;
+            }
+            bool fits = true;  // converged or not, the cuts are valid as long as every segment owns enough frames
+            for (int64_t k = 0; k < G; ++k) fits = fits && beg[(size_t)k + 1] - beg[(size_t)k] >= kSegMinFrames / 2;
+            if (fits) {
+              for (int64_t k = 0; k < G; ++k) {
+                jbk::MlsaSegment sg;
+                sg.utt = (int32_t)u;
+                sg.begin = (int32_t)beg[(size_t)k];
+                sg.end = (int32_t)beg[(size_t)k + 1];
+                sg.warm = (int32_t)(beg[(size_t)k] - wk[(size_t)k]);
+                sg.prev = k == 0 ? -1 : (int32_t)(ws.size() - 1);
+                ws.push_back(sg);
+              }
+              continue;
+            }
+          }
           const int64_t L = (T + (G - 1) * W + G - 1) / G;
           int64_t begin = 0;
           for (int64_t k = 0; k < G && begin < T; ++k) {
@@ -605,6 +646,23 @@ static SegmentPlan cut_segments(const std::vector<int64_t>& frame_off, size_t n_
 
 // Batching layer: pack the state-level parameters of `packs` into one pinned blob, copy it to
 // the device, and lay out every work array of the pipeline in one arena.
+const std::vector<double>& Engine::row_gain(double alpha) const {
+  std::lock_guard<std::mutex> g(row_gain_mu_);
+  if (row_gain_alpha_ != alpha || row_gain_.empty()) {
+    const StreamTable& t = tables_[0];
+    const size_t D = voices_.stream_metadata(0).vector_length;
+    row_gain_.assign(t.rows, 0.0);
+    for (size_t r = 0; r < t.rows; ++r) {
+      const double* c = t.mean.data() + r * t.width;
+      double b = c[D - 1];  // mc2b (cepstrum.rs:139-149), coefficient 0 only
+      for (size_t d = D - 1; d-- > 0;) b = c[d] - alpha * b;
+      row_gain_[r] = b;
+    }
+    row_gain_alpha_ = alpha;
+  }
+  return row_gain_;
+}
+
 Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const UtterancePack* packs,
                                         size_t n_utt, bool streaming, const Condition& cond,
                                         const std::vector<double>& wave_weights) {
@@ -645,9 +703,64 @@ Engine::Resident* Engine::make_resident(const Engine& e, DeviceCtx* ctx, const U
   plan.wave_seg_first.assign(2, 0);
   plan.wave_utt_first = {0, (int32_t)n_utt};
   const int seg_slots = cond.stage != 0 ? 32 / (int)cond.stage : 6;  // segments per warp of the filter kernel
+  // Warm-up by loudness (engine.h: mlsa_warm_loud). The host has no spectra yet, but it has what they are made of:
+  // the static mean of every state's spectrum pdf. Its log gain (coefficient 0 after mc2b) per frame, as prefix
+  // sums per utterance, tells speech from pauses well enough to size the warm-up of a cut; the device check and the
+  // repair pass stay in charge of correctness.
+  std::vector<std::vector<double>> loud_cum;
+  r->warm_loud = 0;
+  if (!streaming && TF > 0 && cond.stage == 0 && e.mlsa_warm_loud > 0 && e.mlsa_warm_loud < e.mlsa_warm_frames &&
+      ctx->loud_strikes < 2) {
+    const StreamModelMetadata& md0 = vs.stream_metadata(0);
+    const size_t D = md0.vector_length, L0 = D * vs.stream_windows(0).size();
+    const bool by_rows = e.device_gather && !e.tables_.empty() && e.tables_[0].regular;
+    const std::vector<double>& wgt = cond.interporation_weight.parameter[0];
+    const size_t nv = std::min(vs.size(), wgt.size());
+    loud_cum.resize(n_utt);
+    bool usable = D >= 2;
+    for (size_t u = 0; u < n_utt && usable; ++u) {
+      const UtterancePack& p = packs[u];
+      if (p.streams.empty()) usable = false;
+      else if (by_rows ? p.streams[0].rows.size() != p.nstates * nv : p.streams[0].mean.size() != p.nstates * L0) usable = false;
+    }
+    if (usable) {
+      // mc2b is linear, so the gain of an interpolated mean is the interpolation of the rows' gains
+      const std::vector<double>* rg = by_rows ? &e.row_gain(cond.alpha) : nullptr;
+      parallel_for(n_utt, [&](size_t u) {
+        const UtterancePack& p = packs[u];
+        std::vector<double>& cum = loud_cum[u];
+        cum.assign(p.nframes + 1, 0.0);
+        size_t f = 0;
+        for (size_t i = 0; i < p.nstates; ++i) {
+          double b = 0.0;
+          if (by_rows) {
+            const int32_t* rr = p.streams[0].rows.data() + i * nv;
+            for (size_t q = 0; q < nv; ++q) b += wgt[q] * (*rg)[(size_t)rr[q]];
+          } else {
+            const double* c = p.streams[0].mean.data() + i * L0;
+            b = c[D - 1];  // mc2b (cepstrum.rs:139-149), coefficient 0 only
+            for (size_t d = D - 1; d-- > 0;) b = c[d] - cond.alpha * b;
+          }
+          for (int32_t k = 0; k < p.durations[i] && f < p.nframes; ++k, ++f) cum[f + 1] = cum[f] + b;
+        }
+        for (; f < p.nframes; ++f) cum[f + 1] = cum[f];
+      });
+      r->warm_loud = e.mlsa_warm_loud;
+    }
+  }
+  WarmAt warm_at;
+  if (r->warm_loud > 0) {
+    const int64_t wl = r->warm_loud, wq = e.mlsa_warm_frames;
+    const double thr = e.mlsa_loud_threshold * (double)wl;
+    warm_at = [&loud_cum, wl, wq, thr](size_t u, int64_t begin) -> int64_t {
+      if (begin <= wl) return begin;  // reaches the start of the utterance, where the zero state is the true one
+      const std::vector<double>& cum = loud_cum[u];
+      return cum[(size_t)begin] - cum[(size_t)(begin - wl)] > thr ? wl : wq;
+    };
+  }
   if (!streaming && TF > 0)
     plan = cut_segments(r->frame_off, n_utt, e.mlsa_warm_frames * (cond.stage != 0 ? kMglsaWarmFactor : 1),
-                        (int64_t)ctx->sm_count * 4 * kSegWarpsPerSmsp * seg_slots, wave_weights);
+                        (int64_t)ctx->sm_count * 4 * kSegWarpsPerSmsp * seg_slots, wave_weights, warm_at);
   const std::vector<jbk::MlsaSegment>& segs = plan.segs;
   r->wave_seg_first = plan.wave_seg_first;
   r->wave_utt_first = plan.wave_utt_first;
@@ -1089,6 +1202,7 @@ static bool mlsa_repair_segments(Engine::Resident* r, double tol, std::vector<Re
   const int n = r->segs.n_seg;
   if (n == 0 || r->segs.fail_list == nullptr || (int)r->seg_table.size() != n || r->h_fail == nullptr) return false;
   const int nfail = *r->h_fail;
+  if (r->warm_loud > 0 && nfail > std::max(4, n / 200) && c->loud_strikes < 2) ++c->loud_strikes;  // the rule does not fit this voice
   if (nfail <= 0 || nfail > r->segs.fail_cap || nfail > std::max(16, n / 16)) return false;
   std::vector<int32_t> ids((size_t)nfail);
   JB_CUDA(cudaMemcpyAsync(ids.data(), r->segs.fail_list, (size_t)nfail * 4, cudaMemcpyDeviceToHost, st));

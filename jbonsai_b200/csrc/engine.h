@@ -70,6 +70,20 @@ class Engine {
   // ~3e-8 in the delay-line taps (measured floor: nitech 4e-9, tohoku-f01 3e-8), i.e. ~2e-7 in this measure.
   // Stage != 0 (MGLSA): the state mismatch relative to the state's scale is held to 1e-9 instead.
   double mlsa_cut_tolerance = 5e-7;
+  // Variant 3, stage 0: warm-up of a cut whose last `mlsa_warm_loud` frames have a mean log gain (coefficient 0 of
+  // the filter rows, estimated on the host from the static means of the states' spectrum pdfs) above
+  // `mlsa_loud_threshold`; every other cut keeps mlsa_warm_frames. The filter forgets its start twice as fast
+  // behind speech as in a pause (tools/decay_predictor.py: output error after W frames from a zero state, 1542
+  // cuts of nitech: mean log gain of the last 20 frames > 1 -> 4.4e-11 at W = 20 on every one of them, 74 % of
+  // all cuts; the others: up to 5.3e-5 at W = 20, 3.5e-10 at W = 32; tohoku-f01: 1.3e-10 at W = 20 everywhere).
+  // The planner places the cuts of an utterance so that its segments still filter equally many frames. 0 = off.
+  // Every cut is still checked on the device and repaired if need be; a device that had to repair more than
+  // 0.5 % of the cuts of two batches planned this way turns the rule off for itself.
+  int mlsa_warm_loud = 24;
+  // Threshold 2.0: on the eight 1024-utterance batches of the scaling run (tools/loud_sweep.py, B200) thresholds
+  // 1.5-2.5 leave no cut to repair with either voice, 1.0 one or two cuts in three of the eight nitech batches
+  // (windows that are half pause), 3.0 moves enough cuts into pauses that one of them fails even with 40 frames.
+  double mlsa_loud_threshold = 2.0;
   // How synthesize_batch brings the waveform to the host: 0 = one copy after the filter, 1 = several
   // filter waves (output_waves), each copied under the next one (default), 2 = the filter stores
   // straight into the pinned output buffer (zero-copy; measured slower: SM stores reach ~34 GB/s
@@ -171,6 +185,12 @@ class Engine {
   explicit Engine(VoiceSet v);
   VoiceSet voices_;
   std::vector<StreamTable> tables_;  // flattened leaf pdfs per stream (device gather)
+  // log gain (coefficient 0 after mc2b) of the static mean of every spectrum pdf row, for the alpha it was built
+  // with: the loudness estimate of the segment planner (mlsa_warm_loud)
+  mutable std::mutex row_gain_mu_;
+  mutable std::vector<double> row_gain_;
+  mutable double row_gain_alpha_ = -1e300;
+  const std::vector<double>& row_gain(double alpha) const;
   std::vector<int> devices_{0};
   mutable std::mutex ctx_mu_;
   mutable std::map<int, std::unique_ptr<DeviceCtx>> ctx_;

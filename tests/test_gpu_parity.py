@@ -290,6 +290,30 @@ def test_output_waves_equal_single_copy():
     assert np.array_equal(q, np.trunc(np.clip(w0, -32768.0, 32767.0)).astype(np.int16))
 
 
+def test_warm_up_by_loudness_filters_fewer_frames_same_samples():
+    # Engine.set_mlsa_loud_warm (default on): cuts that lie behind speech get 24 frames of warm-up instead of 40
+    # (the filter forgets its start faster there), the planner keeps the segments of an utterance equally long.
+    # Fewer frames filtered, every cut still checked on the device, same samples to rounding of the cuts.
+    e = jb.Engine.load([NITECH])
+    utts = wl.timed_batch(e, 192, wl.SEED_NITECH, first=5 * 1024)
+    e.set_output_mode(0)
+    e.set_pipeline_chunks(1)
+    tm = {}
+    w, off = e.synthesize_batch(utts, tm)
+    # (a cut whose bound exceeds the tolerance is repaired from the exact state: rare, with or without the rule)
+    assert tm["mlsa_fallback"] == 0 and tm["mlsa_segments"] > 1000 and tm["mlsa_repaired"] <= 2
+    e.set_mlsa_loud_warm(0)
+    tm0 = {}
+    w0, off0 = e.synthesize_batch(utts, tm0)
+    assert tm0["mlsa_segments"] == tm["mlsa_segments"]  # same number of segments, shorter warm-ups
+    assert tm["mlsa_seg_frames"] < 0.96 * tm0["mlsa_seg_frames"]
+    assert list(off) == list(off0) and np.abs(w - w0).max() <= SCHED_ATOL
+    e.set_mlsa_loud_warm(24, 1e9)  # nothing is loud enough: the plan of the rule switched off
+    tm1 = {}
+    w1, _ = e.synthesize_batch(utts, tm1)
+    assert tm1["mlsa_seg_frames"] == tm0["mlsa_seg_frames"] and np.array_equal(w1, w0)
+
+
 # ---- resident batch and streaming
 def test_resident_equals_batch(eng):
     utts = wl.synthetic_batch(5, wl.SEED_NITECH, lmin=4, lmax=10)
