@@ -127,10 +127,14 @@ size_t host_threads() {
   return (size_t)n;
 }
 
+// A thread that shares the host with `t_host_share - 1` peers doing the same (one host thread per GPU of a
+// multi-device synthesize_batch call) takes its share of the cores only.
+thread_local size_t t_host_share = 1;
+
 // Runs fn(0..n-1) on all host cores; rethrows the first jb::Error.
 template <class F>
 void parallel_for(size_t n, F fn) {
-  size_t nthreads = std::min<size_t>(host_threads(), n / 8 + 1);
+  size_t nthreads = std::min<size_t>(std::max<size_t>(1, host_threads() / t_host_share), n / 8 + 1);
   if (nthreads <= 1) {
     for (size_t i = 0; i < n; ++i) fn(i);
     return;
@@ -1753,11 +1757,11 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
   for (int d : devices_) ctxs.push_back(ctx(d));
   const size_t ndev = dbg ? 1 : std::min(ctxs.size(), std::max<size_t>(n, 1));
 
-  // ---- frames per utterance -> output offsets. One device and a large batch: only the label and
-  // duration part of the front-end runs here (utterance_frames); the stream parameters are looked
-  // up chunk by chunk below, so that the host works on chunk k + 1 while the GPU filters chunk k.
-  // Otherwise the whole front-end runs now.
-  const bool pipelined = !dbg && ndev == 1 && n >= 64 && pipeline_chunks > 1;
+  // ---- frames per utterance -> output offsets. A large batch: only the label and duration part of the
+  // front-end runs here (utterance_frames); the stream parameters are looked up chunk by chunk below (by the host
+  // thread of each device, on its share of the cores), so that the host works on chunk k + 1 while the GPU
+  // filters chunk k. Otherwise the whole front-end runs now.
+  const bool pipelined = !dbg && n >= 64 * ndev && pipeline_chunks > 1;
   std::vector<UtterancePack> all_packs;
   std::vector<size_t> nframes(n, 0);
   if (pipelined) {
@@ -1813,8 +1817,13 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
     int slot = 0;
     double pack_ms = 0;
   };
+  std::vector<double> front_first(ndev, 0.0);  // exposed front-end of every device's first chunk
   auto work = [&](size_t k) {
     DeviceCtx* c = ctxs[k];
+    t_host_share = ndev;
+    struct Restore {
+      ~Restore() { t_host_share = 1; }
+    } restore_share;
     std::vector<Chunk> chunks;
     auto free_chunks = [&]() {
       cudaStreamSynchronize(c->stream);
@@ -1910,7 +1919,7 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
           for (size_t u = ch.u0; u < ch.u1; ++u)
             if (local[u - ch.u0].nframes != nframes[u]) throw Error(kErrArgument, "front-end frame count changed");
           packs = local.data();
-          if (q == 0) front_ms += now_ms() - f0;
+          if (q == 0) front_first[k] = now_ms() - f0;
         } else {
           packs = all_packs.data() + ch.u0;
         }
@@ -2039,6 +2048,7 @@ void Engine::synthesize_batch_impl(const std::vector<std::vector<std::string>>& 
       pinned().release(host_raw);
       throw *e;
     }
+  front_ms += *std::max_element(front_first.begin(), front_first.end());
   if (tm) {
     *tm = BatchTimings();
     tm->host_frontend_ms = front_ms;
