@@ -350,18 +350,19 @@ def run_b200(args, rank, world, local):
     if not args.no_e2e:
         from jbonsai_b200 import _flatten
         flat = _flatten(utts)
-        # pinned pools, device arenas and host page tables settle over several calls (at N = 8 every rank pins
-        # gigabytes at once): warm up until two consecutive calls agree to 5 %, at least max(W, 5), at most 16 calls
-        n_warm, prev_ms = 0, None
+        # pinned pools, device arenas and host page tables settle over several calls, and at N = 8 the ranks, which
+        # all start their 2 GB copies at the same moment after a barrier, drift into an interleaving that shares the
+        # host's 121 GB/s better (250 -> 105 ms per call over ~14 calls): warm up until the last three calls agree to
+        # 5 %, at least max(W, 5) calls, at most 40
+        n_warm, hist = 0, []
         while True:
             t1 = time.perf_counter()
             out, _, tm = eng.synthesize_batch_raw(flat)
             jb.lib.jb_free(out)
-            ms = max_over_ranks((time.perf_counter() - t1) * 1e3)
+            hist.append(max_over_ranks((time.perf_counter() - t1) * 1e3))
             n_warm += 1
-            settled = prev_ms is not None and abs(ms - prev_ms) <= 0.05 * prev_ms
-            prev_ms = ms
-            if n_warm >= 16 or (n_warm >= max(args.warmup, 5) and settled):
+            settled = len(hist) >= 3 and max(hist[-3:]) <= 1.05 * min(hist[-3:])
+            if n_warm >= 40 or (n_warm >= max(args.warmup, 5) and settled):
                 break
         barrier()
         per_step = []
@@ -387,7 +388,7 @@ def run_b200(args, rank, world, local):
                "d2h_bytes_per_step": int(sum_over_ranks(d2h)),
                "ms_per_step": p50, "ms_per_step_mean": mean_ms, "ms_per_step_p99": max_over_ranks(percentile(per_step, 0.99)),
                "ms_per_step_rank0": [round(x, 3) for x in per_step],
-               "timing": f"p50 of {args.steps} calls after {n_warm} warm-up calls (until two agree to 5 %), max over ranks",
+               "timing": f"p50 of {args.steps} calls after {n_warm} warm-up calls (until three in a row agree to 5 %), max over ranks",
                "mlsa_repaired_rank0": int(tm["mlsa_repaired"]), "mlsa_fallback_rank0": int(tm["mlsa_fallback"]),
                "breakdown_ms_rank0": {k: round(tm[k], 3) for k in
                                       ("host_frontend_ms", "pack_ms", "h2d_ms", "kernels_ms", "d2h_ms")}}
