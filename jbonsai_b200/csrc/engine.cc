@@ -1388,9 +1388,38 @@ Engine::Resident* Engine::prepare_tracks(const VocoderConfig& cfg, size_t n_utt,
   SegmentPlan plan;
   plan.wave_seg_first.assign(2, 0);
   plan.wave_utt_first = {0, (int32_t)n_utt};
+  // Warm-up by loudness (make_resident): here the host holds the spectra themselves, so the log gain of a frame is
+  // coefficient 0 of mc2b of its own vector. (Not with coefficient rows given: that is the test seam.)
+  std::vector<std::vector<double>> loud_cum;
+  WarmAt warm_at;
+  r->warm_loud = 0;
+  if (TF > 0 && cfg.stage == 0 && !cfg.coefficient_rows && M >= 2 && mlsa_warm_loud > 0 && mlsa_warm_loud < mlsa_warm_frames &&
+      ctx->loud_strikes < 2) {
+    loud_cum.resize(n_utt);
+    const double alpha = cfg.alpha;
+    parallel_for(n_utt, [&](size_t u) {
+      const int64_t f0 = r->frame_off[u], T = r->frame_off[u + 1] - f0;
+      std::vector<double>& cum = loud_cum[u];
+      cum.assign((size_t)T + 1, 0.0);
+      for (int64_t f = 0; f < T; ++f) {
+        const double* c = spectrum + (size_t)(f0 + f) * M;
+        double b = c[M - 1];  // mc2b (cepstrum.rs:139-149), coefficient 0 only
+        for (size_t d = M - 1; d-- > 0;) b = c[d] - alpha * b;
+        cum[(size_t)f + 1] = cum[(size_t)f] + b;
+      }
+    });
+    r->warm_loud = mlsa_warm_loud;
+    const int64_t wl = mlsa_warm_loud, wq = mlsa_warm_frames;
+    const double thr = mlsa_loud_threshold * (double)wl;
+    warm_at = [&loud_cum, wl, wq, thr](size_t u, int64_t begin) -> int64_t {
+      if (begin <= wl) return begin;
+      const std::vector<double>& cum = loud_cum[u];
+      return cum[(size_t)begin] - cum[(size_t)(begin - wl)] > thr ? wl : wq;
+    };
+  }
   if (TF > 0)
     plan = cut_segments(r->frame_off, n_utt, mlsa_warm_frames * (cfg.stage != 0 ? kMglsaWarmFactor : 1),
-                        (int64_t)ctx->sm_count * 4 * kSegWarpsPerSmsp * seg_slots, {});
+                        (int64_t)ctx->sm_count * 4 * kSegWarpsPerSmsp * seg_slots, {}, warm_at);
   r->wave_seg_first = plan.wave_seg_first;
   r->wave_utt_first = plan.wave_utt_first;
   r->seg_frames = plan.seg_frames;
