@@ -268,6 +268,10 @@ size_t jb_stream_synthesized_frames(const jb_stream* s); /* SpeechGenerator::syn
  * reference panics). written[u] = samples produced for utterance u, 0 once it has ended. */
 int jb_stream_step(jb_stream* s, size_t n_frames, double* buf, size_t cap, size_t* written,
                    double* device_ms);
+/* Page-locked host memory from the library's pool (no reference equivalent): a `buf` for jb_stream_step that the
+ * GPU can write directly. With a pageable buffer every step's waveform is staged through the driver (4096 streams,
+ * one frame: 0.71 ms per step instead of 0.47). Release with jb_free. */
+int jb_alloc_pinned(size_t bytes, void** out);
 void jb_stream_close(jb_stream* s);
 
 #ifdef __cplusplus

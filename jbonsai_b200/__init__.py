@@ -31,7 +31,7 @@ C_ABI_SYMBOLS = [
     "jb_stream_open", "jb_stream_fperiod", "jb_stream_synthesized_frames", "jb_stream_step",
     "jb_stream_close", "jb_resident_device_output", "jb_engine_synthesize_batch_device", "jb_set_host_threads",
     "jb_trim_pools", "jb_device_pitch_period", "jb_engine_mlpg_create", "jb_mlpg_solve_noalloc",
-    "jb_engine_set_mlsa_loud_warm",
+    "jb_engine_set_mlsa_loud_warm", "jb_alloc_pinned",
 ]
 
 STATUS_NAMES = {
@@ -131,6 +131,33 @@ def mlpg_solve_noalloc(device: int, d_mean: int, d_vari: int, n_frames: int, dim
     _check(lib.jb_mlpg_solve_noalloc(int(device), C.c_void_p(int(d_mean)), C.c_void_p(int(d_vari)), int(n_frames),
                                      int(dim), len(windows), widths, coef.ctypes.data_as(C.POINTER(C.c_double)),
                                      C.c_void_p(int(d_out)), C.c_void_p(int(stream))))
+
+
+class _PinnedOwner:
+    def __init__(self, ptr):
+        self.ptr = ptr
+
+    def __del__(self):
+        try:
+            if self.ptr:
+                lib.jb_free(C.c_void_p(self.ptr))
+                self.ptr = None
+        except Exception:
+            pass
+
+
+def pinned_array(shape, dtype=np.float64) -> np.ndarray:
+    """A zeroed numpy array in page-locked host memory of the library's pool (jb_alloc_pinned), e.g. the buffer of
+    Generator.generate_step; returned to the pool when the array is garbage-collected."""
+    n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+    p = C.c_void_p()
+    _check(lib.jb_alloc_pinned(C.c_size_t(max(n, 8)), C.byref(p)))
+    owner = _PinnedOwner(p.value)
+    raw = (C.c_char * max(n, 8)).from_address(p.value)
+    raw._jb_owner = owner  # the ctypes view keeps the allocation alive, numpy keeps the view
+    arr = np.frombuffer(raw, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+    arr[...] = 0
+    return arr
 
 
 def set_host_threads(n: int) -> None:
@@ -583,7 +610,7 @@ class SpeechGenerator:
         """Returns (buf [n_utt, n_frames*fperiod], written [n_utt], device_ms)."""
         fp = self.fperiod()
         if buf is None:
-            buf = np.zeros((self.n_utt, n_frames * fp), dtype=np.float64)
+            buf = pinned_array((self.n_utt, n_frames * fp))  # page-locked: the GPU writes it directly
         written = (C.c_size_t * max(self.n_utt, 1))()
         ms = C.c_double()
         _check(lib.jb_stream_step(self._h, C.c_size_t(n_frames), buf.ctypes.data_as(C.POINTER(C.c_double)),

@@ -263,6 +263,13 @@ int jb_engine_synthesize(const jb_engine* e, const char* const* lines, size_t n_
   return rc;
 }
 
+int jb_alloc_pinned(size_t bytes, void** out) {
+  JB_TRY
+  if (!out) throw jb::Error(jb::kErrArgument, "alloc_pinned: null argument");
+  *out = jb::Engine::alloc_output(bytes);
+  JB_CATCH
+}
+
 void jb_free(void* p) {
   // pool-owned pinned buffers are recycled; anything else came from malloc
   if (!p) return;

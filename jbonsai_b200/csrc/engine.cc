@@ -332,6 +332,7 @@ DeviceCtx* Engine::ctx(int device) const {
 }
 
 void Engine::free_output(void* p) { pinned().release(p); }
+void* Engine::alloc_output(size_t bytes) { return pinned().alloc(bytes ? bytes : 8); }
 void Engine::set_host_threads(int n) { g_host_threads.store(n > 0 ? n : 0); }
 size_t Engine::trim_pools() { return pinned_trim(); }
 

@@ -170,6 +170,7 @@ class Engine {
   void mlpg_create(const MlpgInput& in, int device_index, std::vector<double>* out, std::vector<size_t>* frame_off) const;
 
   static void free_output(void* p);
+  static void* alloc_output(size_t bytes);  // pinned host memory from the same pool (jb_alloc_pinned)
   // Host threads the front-end and the batching layer use (0 = all cores; also JB_HOST_THREADS).
   static void set_host_threads(int n);
   // Frees the cached pinned host buffers of the process-wide pool; returns the bytes released.
