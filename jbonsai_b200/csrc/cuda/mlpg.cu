@@ -11,6 +11,8 @@
 // makes the generated parameters bit-identical to the CPU restatement.
 #include <climits>
 
+#include <cstdlib>
+
 #include "kernels.h"
 
 namespace jbk {
@@ -990,6 +992,152 @@ __global__ void __launch_bounds__(256, 3) k_mlpg_gv(BatchLayout b, StreamDev s, 
   }
   for (int k = tid; k < Tp; k += nt) out[(int64_t)(msd ? vidx[k] : k) * dim] = PAR[k * st];
 }
+
+// The same adjustment in straight-line code, for systems of up to 128 E frames (split path, band width 3).
+// k_mlpg_gv is bound by how many systems an SM holds (58 KB of shared memory each: three) and by what a thread does
+// between two of its 17 block barriers (four elements, wrapped in index arithmetic and branches around the optional
+// terms: 235 warp instructions per element and Newton step; profiles/r2_small_kernels_full_summary.txt). Here a
+// system gets four warps, every thread owns E elements (tid + 128 j) for good and keeps their diagonal, W'U^-1 mu,
+// gradient and switch in registers; only what a neighbour reads - the track and the two off-diagonals - lives in
+// shared memory (31 KB), with a zero halo so that the terms the reference skips at the ends of the system become
+// "+ 0 * 0" (an exact no-op) instead of a branch; a switched-off frame adds 0.0 to the GV sums the same way.
+// Measured on the bench batch (35840 systems of ~1000 frames): 2.07 -> 1.82 ms with 0.74 G instructions instead of
+// 1.34 G; eight warps x five elements 2.06 ms, two x twenty 2.32 ms, and with all six arrays in shared memory
+// (58 KB per system again) 6.1 / 3.2 / 2.2 / 1.9 ms for one / two / four / eight warps: the kernel lives on the
+// number of warps an SM can hold, registers and shared memory both count. Arithmetic per element as in k_mlpg_gv;
+// the sums of a Newton step are taken over other groupings of the elements, so they differ from that kernel's (and
+// from the reference's left-to-right sums) in rounding only.
+template <int NW, int E>
+__global__ void __launch_bounds__(32 * NW) k_mlpg_gv_lin(BatchLayout b, StreamDev s, int64_t plane) {
+  constexpr int BW = 3, H = 2, NT = 32 * NW, N = NT * E + 2 * H;
+  __shared__ double Ps[N], O1s[N], O2s[N];
+  __shared__ double red3[48];
+  int phase = 0;
+  double* const P = Ps + H;
+  double* const O1 = O1s + H;
+  double* const O2 = O2s + H;
+  const int sys = blockIdx.x, tid = threadIdx.x;
+  const int u = sys / s.dim, d = sys - u * s.dim;
+  const int64_t soff = b.state_off[u], foff = b.frame_off[u];
+  const int T = (int)(b.frame_off[u + 1] - foff);
+  const int dim = s.dim;
+  const bool msd = s.is_msd != 0;
+  const int Tp = msd ? s.nvoiced[u] : T;
+  const int32_t* const fstate = b.frame_state + foff;
+  const int32_t* const vidx = msd ? s.vidx + foff : nullptr;
+  double* out = s.par + foff * dim + d;
+  if (msd)
+    for (int t = tid; t < T; t += NT)
+      if (s.left[foff + t] < 0) out[(int64_t)t * dim] = kNoData;  // Mask::fill (mask.rs:34-49)
+  if (Tp == 0) return;
+  const double* const gbase = s.scratch + foff * dim + (int64_t)d * T;  // system-major planes of this system
+  double o0[E], wum[E], gr[E];
+  unsigned swm = 0;
+  if (tid < H) {
+    Ps[tid] = 0.0; O1s[tid] = 0.0; O2s[tid] = 0.0;
+    Ps[N - 1 - tid] = 0.0; O1s[N - 1 - tid] = 0.0; O2s[N - 1 - tid] = 0.0;
+  }
+#pragma unroll
+  for (int j = 0; j < E; ++j) {
+    const int k = tid + j * NT;
+    const bool in = k < Tp;
+    P[k] = in ? gbase[(int64_t)(2 * BW + 2) * plane + k] : 0.0;
+    wum[j] = in ? gbase[(int64_t)(BW + 1) * plane + k] : 0.0;
+    o0[j] = in ? gbase[(int64_t)(BW + 2) * plane + k] : 1.0;  // a pivot of 1 keeps the padding finite
+    O1[k] = in ? gbase[(int64_t)(BW + 3) * plane + k] : 0.0;  // the builder left 0 where k + i >= Tp
+    O2[k] = in ? gbase[(int64_t)(BW + 4) * plane + k] : 0.0;
+    if (in && s.gv_switch[soff + fstate[msd ? vidx[k] : k]] != 0) swm |= 1u << j;
+    gr[j] = 0.0;
+  }
+  __syncthreads();
+  double cnt = 0.0, a = 0.0, dummy = 0.0;
+#pragma unroll
+  for (int j = 0; j < E; ++j) {
+    const bool on = swm >> j & 1u;
+    cnt += on ? 1.0 : 0.0;
+    a += on ? P[tid + j * NT] : 0.0;
+  }
+  block_sum3(cnt, a, dummy, red3, phase);
+  const int gv_length = (int)cnt;
+  if (gv_length > 0) {
+    const double gv_mean = s.gv_mean[(int64_t)u * dim + d] * s.gv_weight;  // mlpg.rs:137-138
+    const double gv_vari = s.gv_vari[(int64_t)u * dim + d];
+    const double n = (double)gv_length;
+    double m0;
+    {  // calc_gv (mlpg.rs:168-188) + conv_gv (:191-199)
+      const double mean = a / n;
+      double v = 0.0, d1 = 0.0, d2 = 0.0;
+#pragma unroll
+      for (int j = 0; j < E; ++j) {
+        const double pk = P[tid + j * NT];
+        v += (swm >> j & 1u) ? (pk - mean) * (pk - mean) : 0.0;
+      }
+      block_sum3(v, d1, d2, red3, phase);
+      const double vari = v / n;
+      m0 = mean;
+      const double ratio = sqrt(gv_mean / vari);
+#pragma unroll
+      for (int j = 0; j < E; ++j)
+        if (swm >> j & 1u) P[tid + j * NT] = ratio * (P[tid + j * NT] - mean) + mean;
+      __syncthreads();
+    }
+    const double wnorm = 1.0 / (double)((int64_t)s.nwin * (int64_t)Tp);
+    const double len = (double)Tp;
+    const double len2 = (double)((int64_t)Tp * (int64_t)Tp);
+    const double lenm1 = (double)(Tp - 1);
+    double step = 0.1, prevobj = 0.0;
+    for (int it = 1; it <= 5; ++it) {
+      double a1 = 0.0, a2 = 0.0, h = 0.0;
+#pragma unroll
+      for (int j = 0; j < E; ++j) {
+        const int k = tid + j * NT;
+        const double pk = P[k];
+        const double dp = pk - m0;
+        const bool on = swm >> j & 1u;
+        a1 += on ? dp : 0.0;
+        a2 += on ? dp * dp : 0.0;
+        double g = o0[j] * pk;  // calc_hmmobj_derivative (mlpg.rs:200-226), same order of terms
+        g += O1[k] * P[k + 1];
+        g += O1[k - 1] * P[k - 1];
+        g += O2[k] * P[k + 2];
+        g += O2[k - 2] * P[k - 2];
+        gr[j] = g;
+        h += 1.0 * wnorm * pk * (wum[j] - 0.5 * g);
+      }
+      block_sum3(a1, a2, h, red3, phase);  // its barrier also separates the reads of P above from the writes below
+      const double dm = a1 / n;
+      const double mean = m0 + dm, vari = a2 / n - dm * dm;
+      m0 = mean;
+      const double gvobj = -0.5 * 1.0 * vari * gv_vari * (vari - 2.0 * gv_mean);
+      const double obj = -(h + gvobj);
+      if (it > 1) {
+        if (obj > prevobj)
+          step *= 0.5;
+        else if (obj < prevobj)
+          step *= 1.2;
+      }
+      const double dv = -2.0 * gv_vari * (vari - gv_mean) / len;  // next_step (mlpg.rs:227-256)
+      const double c2 = 1.0 * 2.0 / len2, c3 = lenm1 * gv_vari * (vari - gv_mean);
+#pragma unroll
+      for (int j = 0; j < E; ++j) {
+        const int k = tid + j * NT;
+        const double pk = P[k];
+        const double hh = -1.0 * wnorm * o0[j] - c2 * (c3 + 2.0 * gv_vari * (pk - mean) * (pk - mean));
+        const double base = 1.0 * wnorm * (-gr[j] + wum[j]);
+        const double next_g = 1.0 / hh * ((swm >> j & 1u) ? base + 1.0 * dv * (pk - mean) : base);
+        if (k < Tp) P[k] = pk + step * next_g;
+      }
+      __syncthreads();
+      prevobj = obj;
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < E; ++j) {
+    const int k = tid + j * NT;
+    if (k < Tp) out[(int64_t)(msd ? vidx[k] : k) * dim] = P[k];
+  }
+}
+
 }  // namespace
 
 namespace {
@@ -1072,8 +1220,13 @@ int launch_mlpg(const BatchLayout& b, const StreamDev& s, int64_t total_frames, 
     // per device and cheap, so set on every launch
     cudaFuncSetAttribute(k_mlpg_gv<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap);
     cudaFuncSetAttribute(k_mlpg_gv<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap);
-    if (bw == 1) k_mlpg_gv<1, false><<<(unsigned)nthreads, 256, smem, stream>>>(b, s, plane, smem_frames);
-    else k_mlpg_gv<3, true><<<(unsigned)nthreads, 256, smem, stream>>>(b, s, plane, smem_frames);
+    static const bool gv_block = getenv("JB_X_GV_BLOCK") != nullptr;  // experiments only: the block-per-system kernel
+    const unsigned g = (unsigned)nthreads;
+    if (bw == 1) k_mlpg_gv<1, false><<<g, 256, smem, stream>>>(b, s, plane, smem_frames);
+    else if (!gv_block && b.max_frames <= 128 * 8) k_mlpg_gv_lin<4, 8><<<g, 128, 0, stream>>>(b, s, plane);
+    else if (!gv_block && b.max_frames <= 128 * 10) k_mlpg_gv_lin<4, 10><<<g, 128, 0, stream>>>(b, s, plane);
+    else if (!gv_block && b.max_frames <= 128 * 12) k_mlpg_gv_lin<4, 12><<<g, 128, 0, stream>>>(b, s, plane);
+    else k_mlpg_gv<3, true><<<g, 256, smem, stream>>>(b, s, plane, smem_frames);
     return (int)cudaGetLastError();
   }
   switch (s.windows.band_width()) {  // other window shapes: the general kernel
