@@ -996,7 +996,7 @@ __global__ void __launch_bounds__(256, 3) k_mlpg_gv(BatchLayout b, StreamDev s, 
 // The same adjustment in straight-line code, for systems of up to 128 E frames (split path, band width 3).
 // k_mlpg_gv is bound by how many systems an SM holds (58 KB of shared memory each: three) and by what a thread does
 // between two of its 17 block barriers (four elements, wrapped in index arithmetic and branches around the optional
-// terms: 235 warp instructions per element and Newton step; profiles/r2_small_kernels_full_summary.txt). Here a
+// terms: 235 warp instructions per element and Newton step; profiles/r2_small_kernels_before_full_summary.txt). Here a
 // system gets four warps, every thread owns E elements (tid + 128 j) for good and keeps their diagonal, W'U^-1 mu,
 // gradient and switch in registers; only what a neighbour reads - the track and the two off-diagonals - lives in
 // shared memory (31 KB), with a zero halo so that the terms the reference skips at the ends of the system become
