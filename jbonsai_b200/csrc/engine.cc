@@ -552,6 +552,7 @@ static SegmentPlan cut_segments(const std::vector<int64_t>& frame_off, size_t n_
       const int64_t TFw = frame_off[ub] - frame_off[ua];
       if (TFw <= 0) continue;
       std::vector<jbk::MlsaSegment> ws;
+      bool sized = false;  // the search for S below only counts segments: the warm-up shares are placed once, at the end
       auto cut = [&](int64_t S) {
         ws.clear();
         for (size_t u = ua; u < ub; ++u) {
@@ -560,7 +561,7 @@ static SegmentPlan cut_segments(const std::vector<int64_t>& frame_off, size_t n_
           int64_t G = std::max<int64_t>(1, (T + S / 2) / S);
           // equal filtered length L for every segment: the first owns L frames, the others L - W
           while (G > 1 && (T + (G - 1) * W) / G - W < kSegMinFrames / 2) --G;
-          if (warm_at && G > 1) {
+          if (warm_at && sized && G > 1) {
             // the share of a cut depends on where it falls and where it falls on the shares before it: iterate
             std::vector<int64_t> beg((size_t)G + 1, 0), wk((size_t)G, 0);
             int64_t sum_w = (G - 1) * W;
@@ -615,6 +616,10 @@ static SegmentPlan cut_segments(const std::vector<int64_t>& frame_off, size_t n_
       // (target segments) would leave a second, nearly empty wave as long as the first.
       for (int it = 0; it < 64 && (int64_t)ws.size() > target && (int64_t)ws.size() < 2 * target; ++it) {
         S += std::max<int64_t>(1, S / 50);
+        cut(S);
+      }
+      if (warm_at) {
+        sized = true;
         cut(S);
       }
       // six consecutive segments share a warp and run as long as the longest of them
