@@ -1001,14 +1001,16 @@ __global__ void __launch_bounds__(256, 3) k_mlpg_gv(BatchLayout b, StreamDev s, 
 // gradient and switch in registers; only what a neighbour reads - the track and the two off-diagonals - lives in
 // shared memory (31 KB), with a zero halo so that the terms the reference skips at the ends of the system become
 // "+ 0 * 0" (an exact no-op) instead of a branch; a switched-off frame adds 0.0 to the GV sums the same way.
-// Measured on the bench batch (35840 systems of ~1000 frames): 2.07 -> 1.82 ms with 0.74 G instructions instead of
-// 1.34 G; eight warps x five elements 2.06 ms, two x twenty 2.32 ms, and with all six arrays in shared memory
+// Measured on the bench batch (35840 systems of ~1000 frames): 2.07 -> 1.58 ms with 0.74 G instructions instead of
+// 1.34 G (1.82 ms at three CTAs per SM); eight warps x five elements 2.06 ms, two x twenty 2.32 ms, and with all six arrays in shared memory
 // (58 KB per system again) 6.1 / 3.2 / 2.2 / 1.9 ms for one / two / four / eight warps: the kernel lives on the
 // number of warps an SM can hold, registers and shared memory both count. Arithmetic per element as in k_mlpg_gv;
 // the sums of a Newton step are taken over other groupings of the elements, so they differ from that kernel's (and
 // from the reference's left-to-right sums) in rounding only.
+// Six CTAs per SM (80 registers, ~140 bytes of spills outside the element loops): measured 2.54 / 1.82 / 1.81 /
+// 1.74 / 1.58 / 1.57 ms for at least 1 / 3 / 4 / 5 / 6 / 7 CTAs per SM - occupancy is worth more than the spills.
 template <int NW, int E>
-__global__ void __launch_bounds__(32 * NW) k_mlpg_gv_lin(BatchLayout b, StreamDev s, int64_t plane) {
+__global__ void __launch_bounds__(32 * NW, 6) k_mlpg_gv_lin(BatchLayout b, StreamDev s, int64_t plane) {
   constexpr int BW = 3, H = 2, NT = 32 * NW, N = NT * E + 2 * H;
   __shared__ double Ps[N], O1s[N], O2s[N];
   __shared__ double red3[48];
