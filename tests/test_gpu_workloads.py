@@ -84,3 +84,25 @@ def test_config5_4096_streams_chunked_subset_vs_oracle():
         assert len(got) == len(want) and len(got) % fp == 0
         worst = max(worst, float(np.abs(got - want).max(initial=0.0)))
     assert worst <= parity_lib.WAVE_ATOL
+
+
+def test_config3_full_size_properties():
+    # BASELINE config 3 at its FULL size (1024 utterances, 248.7 M samples), where the oracle would take minutes:
+    # properties that do not need it. (a) the time-segmented filter (default: ~7000 cuts, warm-up by loudness) against
+    # the sequential kernel, which has no cuts at all; (b) sample counts = frames x fperiod per utterance; (c) the
+    # same call again returns the same bits; (d) 16-bit delivery = the reference examples' clamp of the f64 samples.
+    e = jb.Engine.load([NITECH])
+    utts = wl.timed_batch(e, 1024, wl.SEED_NITECH)
+    tm = {}
+    w, off = e.synthesize_batch(utts, tm)
+    assert tm["mlsa_fallback"] == 0 and tm["mlsa_segments"] > 7000
+    assert len(w) == off[-1] == int(tm["samples"]) == 240 * int(tm["frames"]) and np.all(np.diff(off) % 240 == 0) and np.isfinite(w).all()
+    w_again, _ = e.synthesize_batch(utts)
+    assert np.array_equal(w, w_again)
+    q, _ = e.synthesize_batch_pcm16(utts)
+    assert np.array_equal(q, np.trunc(np.clip(w, -32768.0, 32767.0)).astype(np.int16))
+    del w_again, q
+    e.set_mlsa_variant(2)
+    w_seq, off_seq = e.synthesize_batch(utts)
+    assert list(off_seq) == list(off)
+    assert np.abs(w - w_seq).max() <= 1e-8  # the cuts cost rounding only; against the oracle: the tests above
