@@ -1024,7 +1024,8 @@ int launch_pulse(const BatchLayout& b, const VocoderParams& p, const VocoderDev&
       int dev = 0, sms = 148;
       cudaGetDevice(&dev);
       cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-      const int64_t blocks = std::min<int64_t>((max_runs + kPwWarps - 1) / kPwWarps, (int64_t)sms * 6);
+      static const int per_sm = getenv("JB_X_PW_BLOCKS") ? atoi(getenv("JB_X_PW_BLOCKS")) : 2;  // experiments only
+      const int64_t blocks = std::min<int64_t>((max_runs + kPwWarps - 1) / kPwWarps, (int64_t)sms * per_sm);
       k_pulse_warp<<<(unsigned)blocks, 32 * kPwWarps, 0, stream>>>(b, p, d, next);
       return (int)cudaGetLastError();
     }
