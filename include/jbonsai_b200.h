@@ -93,17 +93,19 @@ int jb_engine_set_mlsa_segmenting(jb_engine* e, int warm_frames, double cut_tole
  * above whatever the rule says. */
 int jb_engine_set_mlsa_loud_warm(jb_engine* e, int loud_frames, double threshold);
 /* How jb_engine_synthesize_batch brings the waveform (8 B per sample, the Vec<f64> of
- * engine.rs:294) to the host. 1 (default): the batch is filtered in three launches, each part copied
- * under the next launch (10 + w selects w equal launches instead); 2: the filter kernel stores straight into
+ * engine.rs:294) to the host. 1 (default): every filter launch's part of the batch is copied under the
+ * next launch (sub-batches: jb_engine_set_pipeline_chunks; 10 + w selects w equal launches instead); 2: the filter kernel stores straight into
  * the pinned, device-visible output buffer (measured slower); 0: one copy after the filter. Same
  * samples (to rounding of the segment cuts) either way. */
 int jb_engine_set_output_mode(jb_engine* e, int mode);
 /* Output mode 1 with explicit shares of the batch (by frames) for the successive filter launches
  * (default 0.35, 0.40, 0.25). */
 int jb_engine_set_output_fractions(jb_engine* e, const double* fractions, size_t n);
-/* Sub-batches of one jb_engine_synthesize_batch call on one device (default 2, used for batches of
- * 64+ utterances that fill the chip more than once): the host looks up the stream parameters of
- * chunk k + 1 while the GPU works on chunk k. 1 = the whole batch in one pass. Same samples. */
+/* Sub-batches of one jb_engine_synthesize_batch call per device (default 3, used for batches of
+ * 64+ utterances per device that fill the chip more than once): the host looks up the stream parameters of
+ * chunk k + 1 while the GPU works on chunk k, and chunk k's waveform crosses PCIe under chunk k + 1's kernels.
+ * 1 = the whole batch in one pass (three copy-overlapped filter launches, jb_engine_set_output_fractions);
+ * 2 = the first of those launches as a sub-batch of its own; 3, 4 = equal sub-batches. Same samples. */
 int jb_engine_set_pipeline_chunks(jb_engine* e, int chunks);
 
 /* Engine::synthesize (src/engine.rs:294-296): labels -> raw f64 samples (not clipped).
