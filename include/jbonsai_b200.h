@@ -256,6 +256,12 @@ int jb_mlpg_solve_noalloc(int device, const double* d_mean, const double* d_vari
  * share a box. jb_trim_pools: frees the cached pinned host buffers (up to 24 GB are kept for reuse);
  * returns the bytes released. */
 int jb_set_host_threads(int n);
+/* Test hook (host only, needs no GPU): the time segments the planner would cut for utterances of the given frame
+ * counts with `warm` frames of warm-up, `target` segments per filter launch and - when `gain` (one log-gain value per
+ * frame, utterances concatenated) is given - the warm-up by loudness (jb_engine_set_mlsa_loud_warm). out: rows of
+ * {utt, begin, end, warm, prev}; *n_segments rows exist (call with out = NULL to size the buffer). */
+int jb_debug_plan_segments(const int64_t* frames, size_t n_utt, int warm, int warm_loud, double threshold,
+                           const double* gain, int64_t target, int32_t* out, size_t cap, size_t* n_segments);
 size_t jb_trim_pools(void);
 
 /* Engine::generator + SpeechGenerator (src/engine.rs:301, src/speech.rs:25-96), batched:

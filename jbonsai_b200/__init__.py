@@ -31,7 +31,7 @@ C_ABI_SYMBOLS = [
     "jb_stream_open", "jb_stream_fperiod", "jb_stream_synthesized_frames", "jb_stream_step",
     "jb_stream_close", "jb_resident_device_output", "jb_engine_synthesize_batch_device", "jb_set_host_threads",
     "jb_trim_pools", "jb_device_pitch_period", "jb_engine_mlpg_create", "jb_mlpg_solve_noalloc",
-    "jb_engine_set_mlsa_loud_warm", "jb_alloc_pinned",
+    "jb_engine_set_mlsa_loud_warm", "jb_alloc_pinned", "jb_debug_plan_segments",
 ]
 
 STATUS_NAMES = {
@@ -158,6 +158,21 @@ def pinned_array(shape, dtype=np.float64) -> np.ndarray:
     arr = np.frombuffer(raw, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
     arr[...] = 0
     return arr
+
+
+def plan_segments(frames, warm: int = 40, warm_loud: int = 0, threshold: float = 2.0, gain=None, target: int = 7104):
+    """jb_debug_plan_segments: [n_segments, 5] rows of (utt, begin, end, warm, prev) - the planner's time segments for
+    utterances of `frames` frames each; `gain`: per-frame log gain (concatenated) for the warm-up by loudness."""
+    fr = np.ascontiguousarray(frames, dtype=np.int64)
+    g = None if gain is None else np.ascontiguousarray(gain, dtype=np.float64)
+    gp = None if g is None else g.ctypes.data_as(C.POINTER(C.c_double))
+    n = C.c_size_t()
+    args = (fr.ctypes.data_as(C.POINTER(C.c_int64)), C.c_size_t(len(fr)), int(warm), int(warm_loud), C.c_double(threshold), gp,
+            C.c_int64(int(target)))
+    _check(lib.jb_debug_plan_segments(*args, None, C.c_size_t(0), C.byref(n)))
+    out = np.zeros((n.value, 5), dtype=np.int32)
+    _check(lib.jb_debug_plan_segments(*args, out.ctypes.data_as(C.POINTER(C.c_int32)), C.c_size_t(out.size), C.byref(n)))
+    return out
 
 
 def set_host_threads(n: int) -> None:

@@ -567,6 +567,17 @@ int jb_mlpg_solve_noalloc(int device, const double* d_mean, const double* d_vari
   return JB_OK;
 }
 
+int jb_debug_plan_segments(const int64_t* frames, size_t n_utt, int warm, int warm_loud, double threshold,
+                           const double* gain, int64_t target, int32_t* out, size_t cap, size_t* n_segments) {
+  JB_TRY
+  if (!frames || !n_segments || target <= 0 || warm < 0) throw jb::Error(jb::kErrArgument, "plan_segments: bad argument");
+  const std::vector<int32_t> rows =
+      jb::Engine::plan_segments_debug(std::vector<int64_t>(frames, frames + n_utt), warm, warm_loud, threshold, gain, target);
+  *n_segments = rows.size() / 5;
+  if (out && cap >= rows.size()) memcpy(out, rows.data(), rows.size() * sizeof(int32_t));
+  JB_CATCH
+}
+
 int jb_set_host_threads(int n) {
   jb::Engine::set_host_threads(n);
   return JB_OK;

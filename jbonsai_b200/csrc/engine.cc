@@ -654,6 +654,33 @@ static SegmentPlan cut_segments(const std::vector<int64_t>& frame_off, size_t n_
   return pl;
 }
 
+std::vector<int32_t> Engine::plan_segments_debug(const std::vector<int64_t>& frames, int warm, int warm_loud,
+                                                 double threshold, const double* gain, int64_t target) {
+  const size_t n = frames.size();
+  std::vector<int64_t> frame_off(n + 1, 0);
+  for (size_t u = 0; u < n; ++u) frame_off[u + 1] = frame_off[u] + frames[u];
+  std::vector<std::vector<double>> cum(n);
+  WarmAt warm_at;
+  if (gain && warm_loud > 0 && warm_loud < warm) {
+    for (size_t u = 0; u < n; ++u) {
+      cum[u].assign((size_t)frames[u] + 1, 0.0);
+      for (int64_t f = 0; f < frames[u]; ++f) cum[u][(size_t)f + 1] = cum[u][(size_t)f] + gain[frame_off[u] + f];
+    }
+    const int64_t wl = warm_loud, wq = warm;
+    const double thr = threshold * (double)wl;
+    warm_at = [&cum, wl, wq, thr](size_t u, int64_t begin) -> int64_t {  // the rule of make_resident
+      if (begin <= wl) return begin;
+      return cum[u][(size_t)begin] - cum[u][(size_t)(begin - wl)] > thr ? wl : wq;
+    };
+  }
+  const SegmentPlan pl = cut_segments(frame_off, n, warm, target, {}, warm_at);
+  std::vector<int32_t> out;
+  for (const jbk::MlsaSegment& s : pl.segs) {
+    out.push_back(s.utt); out.push_back(s.begin); out.push_back(s.end); out.push_back(s.warm); out.push_back(s.prev);
+  }
+  return out;
+}
+
 // Batching layer: pack the state-level parameters of `packs` into one pinned blob, copy it to
 // the device, and lay out every work array of the pipeline in one arena.
 const std::vector<double>& Engine::row_gain(double alpha) const {

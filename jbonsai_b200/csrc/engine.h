@@ -175,6 +175,11 @@ class Engine {
   static void set_host_threads(int n);
   // Frees the cached pinned host buffers of the process-wide pool; returns the bytes released.
   static size_t trim_pools();
+  // Test hook (host only, no device): the time segments the planner cuts for utterances of the given frame counts -
+  // `gain` (per frame, all utterances concatenated) stands for the log-gain estimate of the warm-up by loudness,
+  // nullptr = one warm-up for every cut. Rows of `out`: utt, begin, end, warm, prev.
+  static std::vector<int32_t> plan_segments_debug(const std::vector<int64_t>& frames, int warm, int warm_loud,
+                                                  double threshold, const double* gain, int64_t target);
 
   std::vector<double> noise_prefix(size_t n) const;  // first n Gaussians (host table)
 
