@@ -13,6 +13,7 @@
 #include <cstdlib>
 
 #include "kernels.h"
+#include "cnt_advance.h"
 #include "cr_exp.h"
 
 namespace jbk {
@@ -267,34 +268,7 @@ __global__ void __launch_bounds__(128) k_pulse_runs(BatchLayout b, VocoderParams
 // reference's operations (excitation.rs:72-86); the first lane that sees a pulse is right (nothing precedes it), it
 // writes its pulses and hands its counter to the lanes behind it, which start over from there. About two rounds
 // per 256 samples instead of 256 dependent steps; same bits.
-__device__ __forceinline__ double cnt_advance(double cnt, int m) {  // cnt after m times "cnt += 1.0"
-  {
-    // If cnt + m is exact, every partial sum cnt + j is too (it lies in the same or a lower binade, on a finer
-    // grid), so the m single steps round nowhere. After a pulse the counter is a difference of two values near the
-    // period, a multiple of the period's ulp: for periods above 256 samples that covers nearly every call.
-    const double dm = (double)m, r = cnt + dm, bb = r - cnt;
-    if ((cnt - (r - bb)) + (dm - bb) == 0.0) return r;  // TwoSum: the rounding error of cnt + m
-  }
-  while (m > 0) {
-    if (!(cnt >= 1.0)) {  // below 1 the sum may need more bits than it has: a plain step, rounded like the reference
-      cnt += 1.0;
-      --m;
-      continue;
-    }
-    const double limit = __hiloint2double((__double2hiint(cnt) & 0x7ff00000) + 0x00100000, 0);  // next power of two
-    const double room = limit - cnt;       // exact
-    const int kmax = (int)ceil(room) - 1;  // steps that stay below the limit: all exact
-    if (kmax >= m) {
-      cnt += (double)m;
-      m = 0;
-    } else {
-      cnt += (double)kmax;
-      cnt += 1.0;  // the crossing step rounds to the coarser grid, as in the reference
-      m -= kmax + 1;
-    }
-  }
-  return cnt;
-}
+// cnt_advance (cnt_advance.h): the counter after m steps, without walking; host-testable (tests/test_cnt_advance.py).
 
 constexpr int kPwWarps = 4;
 constexpr int kPwMaxBlocks = 32;  // 8-sample blocks per frame: fperiod <= 256
