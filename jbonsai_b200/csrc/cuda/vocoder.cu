@@ -998,7 +998,9 @@ int launch_pulse(const BatchLayout& b, const VocoderParams& p, const VocoderDev&
       int dev = 0, sms = 148;
       cudaGetDevice(&dev);
       cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-      static const int per_sm = getenv("JB_X_PW_BLOCKS") ? atoi(getenv("JB_X_PW_BLOCKS")) : 2;  // experiments only
+      // six blocks per SM: with two the bench batch gains 0.05 ms of the MLPG phase (less crowding of the MCP kernels)
+      // but a batch of twice the runs (config 4: 2048 utterances of a higher voice) loses 0.7 ms to the walks
+      static const int per_sm = getenv("JB_X_PW_BLOCKS") ? atoi(getenv("JB_X_PW_BLOCKS")) : 6;  // (env: experiments only)
       const int64_t blocks = std::min<int64_t>((max_runs + kPwWarps - 1) / kPwWarps, (int64_t)sms * per_sm);
       k_pulse_warp<<<(unsigned)blocks, 32 * kPwWarps, 0, stream>>>(b, p, d, next);
       return (int)cudaGetLastError();
