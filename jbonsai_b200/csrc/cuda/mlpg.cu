@@ -1233,12 +1233,11 @@ int launch_mlpg(const BatchLayout& b, const StreamDev& s, int64_t total_frames, 
     // per device and cheap, so set on every launch
     cudaFuncSetAttribute(k_mlpg_gv<1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap);
     cudaFuncSetAttribute(k_mlpg_gv<3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cap);
-    static const bool gv_block = getenv("JB_X_GV_BLOCK") != nullptr;  // experiments only: the block-per-system kernel
     const unsigned g = (unsigned)nthreads;
     if (bw == 1) k_mlpg_gv<1, false><<<g, 256, smem, stream>>>(b, s, plane, smem_frames);
-    else if (!gv_block && b.max_frames <= 128 * 8) k_mlpg_gv_lin<4, 8><<<g, 128, 0, stream>>>(b, s, plane);
-    else if (!gv_block && b.max_frames <= 128 * 10) k_mlpg_gv_lin<4, 10><<<g, 128, 0, stream>>>(b, s, plane);
-    else if (!gv_block && b.max_frames <= 128 * 12) k_mlpg_gv_lin<4, 12><<<g, 128, 0, stream>>>(b, s, plane);
+    else if (b.max_frames <= 128 * 8) k_mlpg_gv_lin<4, 8><<<g, 128, 0, stream>>>(b, s, plane);
+    else if (b.max_frames <= 128 * 10) k_mlpg_gv_lin<4, 10><<<g, 128, 0, stream>>>(b, s, plane);
+    else if (b.max_frames <= 128 * 12) k_mlpg_gv_lin<4, 12><<<g, 128, 0, stream>>>(b, s, plane);
     else k_mlpg_gv<3, true><<<g, 256, smem, stream>>>(b, s, plane, smem_frames);
     return (int)cudaGetLastError();
   }

@@ -989,8 +989,7 @@ int launch_pulse(const BatchLayout& b, const VocoderParams& p, const VocoderDev&
     if (e != cudaSuccess) return (int)e;
     // at most every other frame starts a run
     const int64_t max_runs = total_frames / 2 + b.n_utt + 1;
-    static const bool lane_walks = getenv("JB_X_PULSE_LANES") != nullptr;  // experiments only: the round-1 kernel
-    if (p.fperiod % 8 == 0 && p.fperiod <= 8 * kPwMaxBlocks && !lane_walks) {
+    if (p.fperiod % 8 == 0 && p.fperiod <= 8 * kPwMaxBlocks) {
       int* next = d.runs + total_frames + 1;  // the spare slot behind the list (the arena holds total_frames + 2 ints)
       e = cudaMemsetAsync(next, 0, sizeof(int32_t), stream);
       if (e != cudaSuccess) return (int)e;
@@ -1000,7 +999,7 @@ int launch_pulse(const BatchLayout& b, const VocoderParams& p, const VocoderDev&
       cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
       // six blocks per SM: with two the bench batch gains 0.05 ms of the MLPG phase (less crowding of the MCP kernels)
       // but a batch of twice the runs (config 4: 2048 utterances of a higher voice) loses 0.7 ms to the walks
-      static const int per_sm = getenv("JB_X_PW_BLOCKS") ? atoi(getenv("JB_X_PW_BLOCKS")) : 6;  // (env: experiments only)
+      constexpr int per_sm = 6;
       const int64_t blocks = std::min<int64_t>((max_runs + kPwWarps - 1) / kPwWarps, (int64_t)sms * per_sm);
       k_pulse_warp<<<(unsigned)blocks, 32 * kPwWarps, 0, stream>>>(b, p, d, next);
       return (int)cudaGetLastError();

@@ -32,7 +32,7 @@ namespace jb {
 namespace {
 
 // resident warps per scheduler of k_mlsa_v3 (255 registers: two fit)
-static const int kSegWarpsPerSmsp = getenv("JB_X_WPS") ? atoi(getenv("JB_X_WPS")) : 2;
+constexpr int kSegWarpsPerSmsp = 2;
 constexpr int kRepairWarmFactor = 2;
 constexpr double kMglsaCutRelTolerance = 1e-9;
 constexpr int kMglsaWarmFactor = 2;  // stage != 0: the all-pole MGLSA filter of an LSP frame forgets more slowly than the
@@ -1210,8 +1210,6 @@ static void launch_vocoder(Engine::Resident* r, int variant, bool stop_after_exc
 // Returns true when it did; the caller then repeats whatever it had queued behind the filter.
 static bool mlsa_cut_check_failed(Engine::Resident* r, double tol) {
   if (r->result != r->vd.out || r->vd.out == nullptr || r->kernels_end == nullptr) return false;
-  static const bool off = getenv("JB_X_NOCHECK") != nullptr;  // timing experiments with deliberately wrong kernels
-  if (off) return false;
   // MGLSA: the mismatch is relative to the state's scale (launch_mlsa_seg_check); held to 1e-9, an order
   // below what the LSP transform's conditioning leaves of the coefficient rows themselves
   if (r->vp.stage != 0) tol = std::min(tol, kMglsaCutRelTolerance);
