@@ -557,7 +557,8 @@ __global__ void __launch_bounds__(128) k_mlpg_solve(BatchLayout b, StreamDev s, 
 //   k_mlpg_gv      CTA per system, reads the system-major planes with unit stride
 // Every floating-point operation and its order is the one of k_mlpg_solve / the reference; only
 // where it runs changed, so the parameters stay bit-identical.
-// Plane map (each plane = total_frames * dim doubles): [0, BW) factorised band, BW: g, then
+// Plane map (each plane = total_frames * dim doubles): [1, BW) off-diagonals of the factorised band (plane 0, its
+// diagonal, is not stored: k_ldl keeps g / diagonal instead of g), BW: g / diagonal, then
 // system-major: BW+1: W'U^-1 mu, BW+2+j: un-factorised band j, 2BW+2: solution (GV input),
 // 2BW+3: GV gradient (only when a system does not fit in shared memory).
 __global__ void __launch_bounds__(256) k_state_ivar(const double* __restrict__ vari, double* __restrict__ ivar,
@@ -718,9 +719,11 @@ __global__ void __launch_bounds__(128) k_ldl(BatchLayout b, StreamDev s, int64_t
 #pragma unroll
       for (int i = 1; i < BW; ++i)
         if (i < k + 1) g -= prev[i][i] * gprev[i];
+      // what the backward pass needs of frame k: g / row[0] (the division of mlpg.rs:108, same operands, done here
+      // off the recurrence's chain) and the two off-diagonals: three planes instead of four, both ways
 #pragma unroll
-      for (int j = 0; j < BW; ++j) base[(int64_t)j * plane + (int64_t)k * dim] = row[j];
-      pg[(int64_t)k * dim] = g;
+      for (int j = 1; j < BW; ++j) base[(int64_t)j * plane + (int64_t)k * dim] = row[j];
+      pg[(int64_t)k * dim] = g / row[0];
 #pragma unroll
       for (int i = BW - 1; i >= 2; --i) {
         gprev[i] = gprev[i - 1];
@@ -749,11 +752,11 @@ __global__ void __launch_bounds__(128) k_ldl(BatchLayout b, StreamDev s, int64_t
       const int k = k0 - q;
       w[q] = 0.0;
 #pragma unroll
-      for (int j = 0; j < BW; ++j) a[q][j] = 1.0;
+      for (int j = 0; j < BW; ++j) a[q][j] = 0.0;
       if (k >= 0) {
         w[q] = pg[(int64_t)k * dim];
 #pragma unroll
-        for (int j = 0; j < BW; ++j) a[q][j] = base[(int64_t)j * plane + (int64_t)k * dim];
+        for (int j = 1; j < BW; ++j) a[q][j] = base[(int64_t)j * plane + (int64_t)k * dim];
       }
     }
   };
@@ -770,7 +773,7 @@ __global__ void __launch_bounds__(128) k_ldl(BatchLayout b, StreamDev s, int64_t
     for (int q = 0; q < U; ++q) {
       const int k = k0 - q;
       if (k < 0) break;
-      double par = fg[q] / f[q][0];
+      double par = fg[q];  // g / row[0], divided in the forward pass
 #pragma unroll
       for (int i = 1; i < BW; ++i)
         if (i < Tp - k) par -= f[q][i] * pn[i];
