@@ -446,6 +446,11 @@ UtterancePack build_utterance(const VoiceSet& voices, const Condition& cond,
     pack.nframes += durations[i];
   }
   size_t nstream = voices.global_metadata().num_streams;
+  std::vector<uint64_t> label_hashes;
+  if (tables) {
+    label_hashes.resize(labels.labels.size());
+    for (size_t l = 0; l < labels.labels.size(); ++l) label_hashes[l] = label_hash(labels.labels[l]);
+  }
   for (size_t s = 0; s < nstream; ++s) {
     const StreamModelMetadata& md = voices.stream_metadata(s);
     StreamPack sp;
@@ -460,16 +465,29 @@ UtterancePack build_utterance(const VoiceSet& voices, const Condition& cond,
       const size_t ns = models.nstate();
       const size_t S = std::min(pack.nstates, labels.labels.size() * ns);
       sp.rows.resize(S * nv);
-      for (size_t i = 0; i < S; ++i) {
-        const std::string& label = labels.labels[i / ns];
-        const size_t st = 2 + i % ns;
-        for (size_t v = 0; v < nv; ++v) {
-          const Model& m = voices.voices[v]->stream_models[s].stream_model;
-          long ti, pi;
-          m.get_index(st, label, &ti, &pi);
-          if (ti < 0 || pi < 1 || (size_t)(ti - 2) >= m.pdf.size() || (size_t)(pi - 1) >= m.pdf[ti - 2].size())
-            throw Error(kErrIndex, "tree/pdf index not found for label: " + label);
-          sp.rows[i * nv + v] = (int32_t)(tb.voice_base[v] + tb.tree_base[v][(size_t)ti - 2] + (size_t)pi - 1);
+      // one cache lookup per (label, voice) answers all `ns` states (Model::get_all), with the label hashed once
+      // for all streams (label_hashes above)
+      std::vector<int32_t> leaf;
+      for (size_t v = 0; v < nv; ++v) {
+        const Model& m = voices.voices[v]->stream_models[s].stream_model;
+        std::vector<long> tpos(ns, -1);  // tree of state 2 + k (Model::get_index's search, voice/model.rs:50-67)
+        for (size_t k = 0; k < ns; ++k)
+          for (size_t t = 0; t < m.trees.size(); ++t)
+            if (m.trees[t].state == 2 + k) {
+              tpos[k] = (long)t;
+              break;
+            }
+        leaf.assign(m.trees.size(), 0);
+        for (size_t l = 0; l * ns < S; ++l) {
+          const std::string& label = labels.labels[l];
+          m.get_all(label, label_hashes[l], leaf.data());
+          for (size_t k = 0; k < ns && l * ns + k < S; ++k) {
+            const long ti = tpos[k];
+            const long pi = ti < 0 ? -1 : (long)leaf[(size_t)ti];
+            if (ti < 0 || pi < 1 || (size_t)ti >= m.pdf.size() || (size_t)(pi - 1) >= m.pdf[(size_t)ti].size())
+              throw Error(kErrIndex, "tree/pdf index not found for label: " + label);
+            sp.rows[(l * ns + k) * nv + v] = (int32_t)(tb.voice_base[v] + tb.tree_base[v][(size_t)ti] + (size_t)pi - 1);
+          }
         }
       }
       std::vector<MeanVari> gvp;

@@ -82,6 +82,16 @@ bool Pattern::match(const char* s, size_t n) const {
 }
 
 // ---------------------------------------------------------------- tree lookup
+long Model::walk(const Tree& tree, const std::string& label) const {
+  size_t node = 0;
+  while (node < tree.nodes.size()) {
+    const TreeNode& nd = tree.nodes[node];
+    if (nd.leaf) return (long)nd.pdf_index;
+    node = questions[(size_t)nd.question].test(label) ? nd.yes : nd.no;
+  }
+  return -1;
+}
+
 void Model::get_index(size_t state_index, const std::string& label, long* tree_index,
                       long* pdf_index) const {
   long ti = -1;
@@ -93,36 +103,67 @@ void Model::get_index(size_t state_index, const std::string& label, long* tree_i
   const size_t tsel = ti < 0 ? 0 : (size_t)ti;
   const Tree& tree = trees[tsel];
   *tree_index = ti < 0 ? -1 : ti + 2;
-  // cache: 0 = not resolved yet, -1 = no leaf, else the 1-based pdf index
-  LabelCache::Shard& sh = cache->shards[std::hash<std::string>()(label) % LabelCache::kShards];
+  const uint64_t h = label_hash(label);
+  LabelCache::Shard& sh = cache->shards[h % LabelCache::kShards];
+  bool foreign = false;  // the slot of this hash belongs to another label: no caching
   {
     std::lock_guard<std::mutex> g(sh.mu);
-    auto it = sh.map.find(label);
-    if (it != sh.map.end() && it->second[tsel] != 0) {
-      *pdf_index = it->second[tsel];
-      return;
+    auto it = sh.map.find(h);
+    if (it != sh.map.end()) {
+      if (it->second.label != label) foreign = true;
+      else if (it->second.pdf[tsel] != 0) {
+        *pdf_index = it->second.pdf[tsel];
+        return;
+      }
     }
   }
-  long pi = -1;
-  size_t node = 0;
-  while (node < tree.nodes.size()) {
-    const TreeNode& nd = tree.nodes[node];
-    if (nd.leaf) {
-      pi = (long)nd.pdf_index;
-      break;
-    }
-    node = questions[(size_t)nd.question].test(label) ? nd.yes : nd.no;
-  }
+  const long pi = walk(tree, label);
   *pdf_index = pi;
+  if (foreign) return;
+  std::lock_guard<std::mutex> g(sh.mu);
+  auto it = sh.map.find(h);
+  if (it == sh.map.end()) {
+    if (sh.map.size() >= LabelCache::kMaxPerShard) return;
+    it = sh.map.emplace(h, LabelCache::Entry{label, std::vector<int32_t>(trees.size(), 0)}).first;
+  } else if (it->second.label != label) {
+    return;
+  }
+  it->second.pdf[tsel] = (int32_t)pi;
+}
+
+void Model::get_all(const std::string& label, uint64_t h, int32_t* out) const {
+  const size_t nt = trees.size();
+  LabelCache::Shard& sh = cache->shards[h % LabelCache::kShards];
+  bool have = false, foreign = false;
   {
     std::lock_guard<std::mutex> g(sh.mu);
-    auto it = sh.map.find(label);
-    if (it == sh.map.end()) {
-      if (sh.map.size() >= LabelCache::kMaxPerShard) return;
-      it = sh.map.emplace(label, std::vector<int32_t>(trees.size(), 0)).first;
+    auto it = sh.map.find(h);
+    if (it != sh.map.end()) {
+      if (it->second.label != label) foreign = true;
+      else {
+        have = true;
+        for (size_t t = 0; t < nt; ++t) out[t] = it->second.pdf[t];
+      }
     }
-    it->second[tsel] = (int32_t)pi;
   }
+  bool complete = have;
+  if (!have)
+    for (size_t t = 0; t < nt; ++t) out[t] = 0;
+  else
+    for (size_t t = 0; t < nt; ++t) complete = complete && out[t] != 0;
+  if (complete) return;
+  for (size_t t = 0; t < nt; ++t)
+    if (out[t] == 0) out[t] = (int32_t)walk(trees[t], label);
+  if (foreign) return;
+  std::lock_guard<std::mutex> g(sh.mu);
+  auto it = sh.map.find(h);
+  if (it == sh.map.end()) {
+    if (sh.map.size() >= LabelCache::kMaxPerShard) return;
+    it = sh.map.emplace(h, LabelCache::Entry{label, std::vector<int32_t>(nt, 0)}).first;
+  } else if (it->second.label != label) {
+    return;
+  }
+  for (size_t t = 0; t < nt; ++t) it->second.pdf[t] = out[t];
 }
 
 const ModelParameter& Model::get_parameter(size_t state_index, const std::string& label) const {

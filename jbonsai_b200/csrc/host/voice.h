@@ -89,16 +89,27 @@ struct Tree {
 // Leaf indices already resolved for a label string, per tree (host front-end cache: a decision
 // tree walk costs a few hundred wildcard matches, and batches repeat labels). Bounded; sharded
 // so that the front-end threads of a batch do not serialise on it. Results are exactly the tree
-// walk's (Model::get_index computes on a miss).
+// walk's (the Model computes on a miss). Keyed by the 64-bit hash of the label, which the caller
+// computes ONCE per label and hands to every model it asks (a 200-byte label hashed 32 times was
+// 40 % of the index-mode front-end); the entry keeps the label, and a second label with the same
+// hash is simply not cached.
 struct LabelCache {
   static constexpr size_t kShards = 64;
   static constexpr size_t kMaxPerShard = 4096;
+  struct Entry {
+    std::string label;
+    std::vector<int32_t> pdf;  // per tree: 0 = not resolved yet, -1 = no leaf, else the 1-based pdf index
+  };
+  struct Identity {
+    size_t operator()(uint64_t h) const { return (size_t)h; }
+  };
   struct Shard {
     std::mutex mu;
-    std::unordered_map<std::string, std::vector<int32_t>> map;
+    std::unordered_map<uint64_t, Entry, Identity> map;
   };
   Shard shards[kShards];
 };
+inline uint64_t label_hash(const std::string& label) { return (uint64_t)std::hash<std::string>()(label); }
 
 struct Model {
   std::vector<Question> questions;
@@ -109,7 +120,13 @@ struct Model {
   // (tree_index + 2, pdf_index) like Model::get_index (voice/model.rs:50-67); -1 = None.
   void get_index(size_t state_index, const std::string& label, long* tree_index,
                  long* pdf_index) const;
+  // The pdf index of `label` in EVERY tree of the model (pdf_index[t] for trees[t]; -1 = no leaf), one cache
+  // lookup: what five get_index calls (one per state) return. `hash` = label_hash(label).
+  void get_all(const std::string& label, uint64_t hash, int32_t* pdf_index) const;
   const ModelParameter& get_parameter(size_t state_index, const std::string& label) const;
+
+ private:
+  long walk(const Tree& tree, const std::string& label) const;
 };
 
 struct Window {
